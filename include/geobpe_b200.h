@@ -1,0 +1,170 @@
+/* geobpe_b200 -- C ABI of the B200-native GeoBPE learn/induce hot path.
+ *
+ * The reference (shiningsunnyday/PT-BPE @ f032fa4) has NO FFI / plugin interface on this path:
+ * it is pure Python.  The entry points below are therefore the boundary a
+ * maintainer of the reference would bind with ctypes from foldingdiff/bpe.py; each one names the
+ * reference Python code it replaces (file:line relative to the reference repo).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - `stream` is a cudaStream_t passed as void* (0 = default stream); nothing here allocates,
+ *     synchronises or owns memory -- buffers are owned by the caller (PyTorch tensors);
+ *   - return value 0 = ok, anything else = failure, message in gb_last_error();
+ *   - internal-coordinate input layout: `vals` is float64 [9][ld] type-major, row order
+ *     0C:1N, N:CA, CA:C, phi, psi, omega, tau, CA:C:1N, C:1N:1CA (datasets.py:175-186),
+ *     `offsets` int64 [S+1] is the CSR of backbones over residues;
+ *   - "residue-major" slot order used by rbins / edges / class geometry:
+ *       0 N:CA(r) 1 CA:C(r) 2 0C:1N(r) 3 tau(r) 4 CA:C:1N(r) 5 psi(r) 6 omega(r) 7 C:1N:1CA(r) 8 phi(r+1)
+ *     (slots 0,1,3 of the first residue of a backbone are the NeRF init constants, tokenizer.py:74-77);
+ *   - token arrays (one entry per live token, ordered by backbone then position):
+ *       cls  u32  geometry class of the motif (medoid mode)        hsh u64  content hash (histogram mode)
+ *       glue u32  packed glue bins to the right neighbour: omega | C:1N:1CA<<10 | phi<<20, bit31 = last token
+ *       pos  u32  global residue index of the first residue         len u32  residues covered
+ *       tid  u32  position of the token id in BPE._tokens
+ */
+#ifndef GEOBPE_B200_H
+#define GEOBPE_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GB_EMPTY_KEY 0xFFFFFFFFFFFFFFFFull
+#define GB_LAST_FLAG 0x80000000u
+#define GB_NOBIN 0x3FFu
+#define GB_P61 0x1FFFFFFFFFFFFFFFull
+
+const char* gb_last_error(void);
+int gb_abi_version(void);
+/* number of SMs of the current device (grid sizing; 148 on B200) */
+int gb_sm_count(void);
+
+/* ---- plumbing ------------------------------------------------------------------------------- */
+/* bb[r] = backbone index of residue r (binary search in offsets).  Replaces the per-structure
+ * Python loops `for ti, t in enumerate(self.tokenizers)` (bpe.py:229, 1440). */
+int gb_residue_backbone(const int64_t* offsets, int64_t S, int64_t R, uint32_t* bb, void* stream);
+
+/* ordered stream compaction: out_idx[0..total) = ascending i in [0,n) with (flags[i] & mask) != 0.
+ * scratch: u32 [gb_select_scratch_elems(n)].  total is a device u32. */
+int64_t gb_select_scratch_elems(int64_t n);
+int gb_select_flagged(const uint8_t* flags, int64_t n, uint32_t mask, uint32_t* out_idx,
+                      uint32_t* total, uint32_t* scratch, void* stream);
+/* same, predicate keys[i] == key (filters the occurrence-set op log, bpe.py:1744 list(set)) */
+int gb_select_eq_u64(const uint64_t* keys, int64_t n, uint64_t key, uint32_t* out_idx,
+                     uint32_t* total, uint32_t* scratch, void* stream);
+
+/* ---- K3: thresholds + value->bin (bpe.py:820-876 _init_thresholds, plotting.py:305-337
+ *          save_histogram, bpe.py:1165-1189 get_ind, 1513-1526 quant_geo, 715-737 bond lengths) -- */
+/* per column c: min / max / count over entries that are not NaN and not 0.0 (bpe.py:844), angle
+ * columns (3..8) wrapped (v+2pi)%2pi first (plotting.py:318).  minmax f64 [9][2], cnt u64 [9]. */
+int gb_col_minmax(const double* vals, int64_t R, int64_t ld, double* minmax, unsigned long long* cnt,
+                  void* stream);
+/* per column histogram against edges f64 [9][estride] with nb_host[c] bins (np.histogram semantics:
+ * left-closed bins, last bin closed).  counts u64 [9][estride] is zeroed here. */
+int gb_col_hist(const double* vals, int64_t R, int64_t ld, const double* edges, int estride,
+                const int* nb_host, unsigned long long* counts, void* stream);
+/* residue-major quantisation.  edges f64 [9][estride] in RESIDUE-MAJOR slot order, nb_host[9];
+ * bond_mode 0: std_bonds (bond bins = 0), 1: free bonds strict, 2: free bonds clamped (strict=False,
+ * bpe.py:726-729).  Outputs: rbins u16 [9][R] (GB_NOBIN = absent), glue u32 [R], sym u64 [R]
+ * (1 + tau | CA:C:1N<<10 | psi<<20: the histogram-mode residue symbol), status i32 [S]
+ * (bit0: value below first bin, bit1: value in no bin -- get_ind's two ValueErrors). */
+int gb_quantize_residues(const double* vals, int64_t R, int64_t ld, const uint32_t* bb,
+                         const int64_t* offsets, int64_t S, const double* edges, int estride,
+                         const int* nb_host, int bond_mode, double init_nca, double init_cac,
+                         double init_tau, uint16_t* rbins, uint32_t* glue, uint64_t* sym,
+                         int32_t* status, void* stream);
+
+/* ---- K1: adjacent-pair histogram + argmax (bpe.py:1431-1474 bin, 1192-1299 compute_geo_key,
+ *          1796 peekitem, 2077-2138 recount) ------------------------------------------------------ */
+/* table = open-addressing hash table of M (power of two) slots: keys u64, cnt u32, minpos u32 */
+int gb_table_clear(uint64_t* tkeys, uint32_t* tcnt, uint32_t* tmin, int64_t M, void* stream);
+/* medoid mode: key = cls[j]<<45 | cls[j+1]<<27 | glue27(j).  overflow (device i32) set if the table is full */
+int gb_pair_count_m(const uint32_t* cls, const uint32_t* glue, int64_t T, uint64_t* tkeys,
+                    uint32_t* tcnt, uint32_t* tmin, int64_t M, int32_t* overflow, void* stream);
+/* histogram mode: key = polynomial hash (mod 2^61-1, base P) of the concatenated window content
+ * hsh[j] . gluesym(j) . hsh[j+1]; powtab u64 [>= 2*maxlen] holds P^m */
+int gb_pair_count_h(const uint64_t* hsh, const uint32_t* glue, const uint32_t* len, int64_t T,
+                    const uint64_t* powtab, uint64_t P, uint64_t* tkeys, uint32_t* tcnt,
+                    uint32_t* tmin, int64_t M, int32_t* overflow, void* stream);
+/* generic: histogram of an explicit key array (residue-token interning, bpe.py:243-247) */
+int gb_key_count(const uint64_t* keys, int64_t n, uint64_t* tkeys, uint32_t* tcnt, uint32_t* tmin,
+                 int64_t M, int32_t* overflow, void* stream);
+/* out u32 [4]: {max count, number of keys tied at max, distinct keys, 0}; ties (first `cap`) in
+ * tie_keys / tie_minpos (unordered: the host applies the reference's json-string tie-break) */
+int gb_table_argmax(const uint64_t* tkeys, const uint32_t* tcnt, const uint32_t* tmin, int64_t M,
+                    uint32_t* out4, uint64_t* tie_keys, uint32_t* tie_minpos, int cap, void* stream);
+/* counts of Q given keys (recurring-key priority, bpe.py:2121-2127,2164-2166) */
+int gb_table_lookup(const uint64_t* tkeys, const uint32_t* tcnt, const uint32_t* tmin, int64_t M,
+                    const uint64_t* qkeys, int Q, uint32_t* out_cnt, uint32_t* out_min, void* stream);
+/* dump all (key,count,minpos) with count>0 compacted (unordered); total device u32 */
+int gb_table_dump(const uint64_t* tkeys, const uint32_t* tcnt, const uint32_t* tmin, int64_t M,
+                  uint64_t* out_keys, uint32_t* out_cnt, uint32_t* out_min, uint32_t* total, void* stream);
+/* multi-GPU: fold the table into a key-less direct-mapped counter array slots u32 [NS] (NS power of 2)
+ * for the NCCL allreduce; and list the local keys that fall into slot `s` */
+int gb_table_to_slots(const uint64_t* tkeys, const uint32_t* tcnt, int64_t M, uint32_t* slots,
+                      int64_t NS, void* stream);
+
+/* ---- K2: merge (bpe.py:1895-2017) --------------------------------------------------------------- */
+/* flags[j] bit0 = pair (j,j+1) has key `key` */
+int gb_flag_pairs_m(const uint32_t* cls, const uint32_t* glue, int64_t T, uint64_t key, uint8_t* flags,
+                    void* stream);
+int gb_flag_pairs_h(const uint64_t* hsh, const uint32_t* glue, const uint32_t* len, int64_t T,
+                    const uint64_t* powtab, uint64_t P, uint64_t key, uint8_t* flags, void* stream);
+/* left-to-right overlap rule (bpe.py:1909-1914): within each maximal run of flagged pairs keep the
+ * 1st, 3rd, ...: sets bit1 of flags on kept occurrences */
+int gb_resolve_overlaps(uint8_t* flags, int64_t T, void* stream);
+/* aux[occ[q]] = val[q] */
+int gb_scatter_u32(const uint32_t* occ, const uint32_t* val, int64_t Q, uint32_t* aux, void* stream);
+/* stream compaction of the token arrays.  A token survives unless its left neighbour pair was kept;
+ * a kept left token j becomes the merged token: glue <- glue[j+1], len <- len[j]+len[j+1],
+ * medoid mode: cls <- p2cls[aux[j]], tid <- p2tid[aux[j]]; histogram mode: hsh <- key, tid <- new_tid.
+ * Any of cls/hsh may be NULL.  newT is a device u32.  scratch as gb_select_scratch_elems(T). */
+int gb_merge_compact(const uint8_t* flags, int64_t T,
+                     const uint32_t* cls, const uint64_t* hsh, const uint32_t* glue, const uint32_t* pos,
+                     const uint32_t* len, const uint32_t* tid,
+                     uint32_t* cls_o, uint64_t* hsh_o, uint32_t* glue_o, uint32_t* pos_o,
+                     uint32_t* len_o, uint32_t* tid_o,
+                     const uint32_t* aux, const uint32_t* p2cls, const uint32_t* p2tid,
+                     uint64_t key, uint32_t new_tid, uint32_t* newT, uint32_t* scratch, void* stream);
+/* merge-event log for the merge tree (data_structures.py:217-226): for kept occurrence q (token
+ * kept[q]): ev_left[q]=pos[j], ev_right[q]=pos[j+1], ev_p[q]=aux? aux[j] : 0 */
+int gb_write_events(const uint32_t* kept, int64_t Q, const uint32_t* pos, const uint32_t* aux,
+                    uint32_t* ev_left, uint32_t* ev_right, uint32_t* ev_p, void* stream);
+/* medoid mode: occurrence-set op log (SURVEY 7.2 hard part 1).  For kept occurrence q writes 4
+ * records at log_key/log_pos[4q..4q+3]: remove left key, remove right key, add new left key, add
+ * new right key (bpe.py:1924-1950,1992-2006), GB_EMPTY_KEY when the neighbour does not exist */
+int gb_oplog_m(const uint32_t* kept, int64_t Q, const uint8_t* flags, const uint32_t* cls,
+               const uint32_t* glue, const uint32_t* pos, int64_t T, const uint32_t* aux,
+               const uint32_t* p2cls, uint64_t* log_key, uint32_t* log_pos, void* stream);
+/* initial op-log segment = every adjacent pair in order (bpe.py:1441-1453): log_key[j], log_pos[j]=pos[j+1] */
+int gb_pair_keys_m(const uint32_t* cls, const uint32_t* glue, const uint32_t* pos, int64_t T,
+                   uint64_t* log_key, uint32_t* log_pos, void* stream);
+/* histogram mode: exact check that every flagged occurrence has the same window bins as the window
+ * at ref_r0 (guards the 61-bit content hash).  mismatches: device u32 counter */
+int gb_verify_windows_h(const uint32_t* occ, int64_t Q, const uint32_t* pos, const uint32_t* len,
+                        const uint16_t* rbins, int64_t R, uint32_t ref_r0, uint32_t nres,
+                        uint32_t* mismatches, void* stream);
+
+/* ---- K4/K5/K6: NeRF windows, Kabsch RMSD, medoid assignment (tokenizer.py:347-363, nerf.py:84-210,
+ *      angles_and_coords.py:238-317, algo.py:8-65,170-181, bpe.py:646-657) -------------------------- */
+/* coords f64 [Q][A][3] for windows starting at residue r0[q] spanning nres residues; A = atoms kept
+ * (3*nres+1, or 3*nres when the window ends a backbone).  If the window starts a backbone the first
+ * N:CA, CA:C, tau are f3tab[f3cls[q]] when f3cls != NULL and f3cls[q] != 0xFFFFFFFF, else (d_nca,d_cac,d_tau)
+ * (the reference keeps them in Tokenizer._init_*; tokenizer.py:131-167).
+ * bondc (nullable) f64 [3][nbmax]: bin centres for 0C:1N / N:CA / CA:C with brow u16 [3][R] bins --
+ * when given, bond lengths are taken quantised (induce, bpe.py:1061,1085). */
+int gb_window_coords(const double* vals, int64_t R, int64_t ld, const uint32_t* bb, const int64_t* offsets,
+                     const uint32_t* r0, int64_t Q, int nres, int A,
+                     const uint32_t* f3cls, const double* f3tab, double d_nca, double d_cac, double d_tau,
+                     const uint16_t* rbins, const double* bond_centres, int bc_stride,
+                     double* coords, void* stream);
+/* assign[q] = argmin_m rmsd(P_q, M_m) (first index on ties, np.argmin), best[q] = that rmsd */
+int gb_kabsch_assign(const double* P, int64_t Q, int A, const double* Mq, int K, uint32_t* assign,
+                     double* best, void* stream);
+/* D f32 [N][N] all-pairs Kabsch RMSD (float64 math, rounded to float32 like algo.py:170) */
+int gb_rmsd_matrix(const double* P, int N, int A, float* D, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,325 @@
+// K1: adjacent motif-pair frequency counting + argmax.
+// Replaces BPE.bin (bpe.py:1431-1474), the per-step recount (bpe.py:2077-2138) and the
+// SortedDict.peekitem(0) pop (bpe.py:1796) by a full recount every iteration:
+//   packed 64-bit pair keys -> warp-aggregated (match.any) insertion into a per-CTA shared-memory
+//   hash table -> one global atomic per distinct key per CTA -> table scan for the max count and the
+//   tie list.  HBM-bound: cls + glue = 8 B per live token (medoid mode), hsh+glue+len = 16 B (histogram mode),
+//   read once with 128-bit coalesced loads.
+#include "common.cuh"
+
+#define K1_THREADS 512
+#define K1_VEC 4
+#define K1_TILE (K1_THREADS * K1_VEC)
+#define K1_SLOTS 4096           // shared-memory table slots per CTA (64 KB)
+#define K1_SPROBES 12
+#define K1_FLUSH_AT ((K1_SLOTS * 5) / 8)
+
+struct STable {
+  u64* k; u32* c; u32* m; u32* n_used;
+};
+
+__device__ __forceinline__ void stable_reset(const STable& s) {
+  for (int i = threadIdx.x; i < K1_SLOTS; i += blockDim.x) { s.k[i] = GB_EMPTY_KEY; s.c[i] = 0; s.m[i] = 0xFFFFFFFFu; }
+  if (threadIdx.x == 0) *s.n_used = 0;
+}
+
+__device__ __forceinline__ bool stable_add(const STable& s, u64 key, u32 c, u32 mn) {
+  u32 slot = (u32)(gb_mix64(key) >> 20) & (K1_SLOTS - 1);
+#pragma unroll 1
+  for (int p = 0; p < K1_SPROBES; ++p) {
+    u64 prev = s.k[slot];
+    if (prev == GB_EMPTY_KEY) {
+      prev = atomicCAS(&s.k[slot], (u64)GB_EMPTY_KEY, key);
+      if (prev == GB_EMPTY_KEY) atomicAdd(s.n_used, 1u);
+    }
+    if (prev == GB_EMPTY_KEY || prev == key) {
+      atomicAdd(&s.c[slot], c);
+      atomicMin(&s.m[slot], mn);
+      return true;
+    }
+    slot = (slot + 1) & (K1_SLOTS - 1);
+  }
+  return false;
+}
+
+struct GTable { u64* k; u32* c; u32* m; u64 mask; int32_t* overflow; };
+
+__device__ __forceinline__ void stable_flush(const STable& s, const GTable& g) {
+  for (int i = threadIdx.x; i < K1_SLOTS; i += blockDim.x) {
+    u64 key = s.k[i];
+    if (key != GB_EMPTY_KEY) {
+      if (!gb_gtable_add(g.k, g.c, g.m, g.mask, key, s.c[i], s.m[i])) atomicExch(g.overflow, 1);
+      s.k[i] = GB_EMPTY_KEY; s.c[i] = 0; s.m[i] = 0xFFFFFFFFu;
+    }
+  }
+  if (threadIdx.x == 0) *s.n_used = 0;
+}
+
+// warp-aggregated add of one key per lane (key == EMPTY -> lane does not contribute)
+__device__ __forceinline__ void warp_agg_add(const STable& s, const GTable& g, u64 key, u32 pos) {
+  unsigned grp = __match_any_sync(0xffffffffu, key);
+  if (key != GB_EMPTY_KEY) {
+    unsigned lane = threadIdx.x & 31;
+    if ((unsigned)(__ffs(grp) - 1) == lane) {  // lowest lane of the group holds the lowest position
+      u32 c = __popc(grp);
+      if (!stable_add(s, key, c, pos)) {
+        if (!gb_gtable_add(g.k, g.c, g.m, g.mask, key, c, pos)) atomicExch(g.overflow, 1);
+      }
+    }
+  }
+}
+
+// ---- key functors: load K1_VEC consecutive tokens per thread + the right neighbour of the last ----
+struct KeysM {
+  const u32* cls; const u32* glue;
+  __device__ __forceinline__ void keys(i64 j0, i64 T, u64 out[K1_VEC]) const {
+    u32 c[K1_VEC + 1], g[K1_VEC];
+    if (j0 + K1_VEC <= T) {
+      uint4 cv = *reinterpret_cast<const uint4*>(cls + j0);
+      uint4 gv = *reinterpret_cast<const uint4*>(glue + j0);
+      c[0] = cv.x; c[1] = cv.y; c[2] = cv.z; c[3] = cv.w;
+      g[0] = gv.x; g[1] = gv.y; g[2] = gv.z; g[3] = gv.w;
+    } else {
+#pragma unroll
+      for (int e = 0; e < K1_VEC; ++e) {
+        bool in = j0 + e < T;
+        c[e] = in ? cls[j0 + e] : 0u;
+        g[e] = in ? glue[j0 + e] : GB_LAST_FLAG;
+      }
+    }
+    // right neighbour of the 4th token: first token of the next lane, or one scalar load for lane 31
+    u32 nxt = __shfl_down_sync(0xffffffffu, c[0], 1);
+    if ((threadIdx.x & 31) == 31) nxt = (j0 + K1_VEC < T) ? cls[j0 + K1_VEC] : 0u;
+    c[K1_VEC] = nxt;
+#pragma unroll
+    for (int e = 0; e < K1_VEC; ++e) {
+      bool valid = (j0 + e + 1 < T) && !(g[e] & GB_LAST_FLAG);
+      out[e] = valid ? gb_key_m(c[e], g[e], c[e + 1]) : GB_EMPTY_KEY;
+    }
+  }
+};
+
+struct KeysH {
+  const u64* hsh; const u32* glue; const u32* len; const u64* powtab; u64 P;
+  __device__ __forceinline__ void keys(i64 j0, i64 T, u64 out[K1_VEC]) const {
+    u64 h[K1_VEC + 1]; u32 g[K1_VEC], l[K1_VEC + 1];
+    if (j0 + K1_VEC <= T) {
+      ulonglong2 h01 = *reinterpret_cast<const ulonglong2*>(hsh + j0);
+      ulonglong2 h23 = *reinterpret_cast<const ulonglong2*>(hsh + j0 + 2);
+      uint4 gv = *reinterpret_cast<const uint4*>(glue + j0);
+      uint4 lv = *reinterpret_cast<const uint4*>(len + j0);
+      h[0] = h01.x; h[1] = h01.y; h[2] = h23.x; h[3] = h23.y;
+      g[0] = gv.x; g[1] = gv.y; g[2] = gv.z; g[3] = gv.w;
+      l[0] = lv.x; l[1] = lv.y; l[2] = lv.z; l[3] = lv.w;
+    } else {
+#pragma unroll
+      for (int e = 0; e < K1_VEC; ++e) {
+        bool in = j0 + e < T;
+        h[e] = in ? hsh[j0 + e] : 0ull;
+        g[e] = in ? glue[j0 + e] : GB_LAST_FLAG;
+        l[e] = in ? len[j0 + e] : 1u;
+      }
+    }
+    u64 nh = __shfl_down_sync(0xffffffffu, h[0], 1);
+    u32 nl = __shfl_down_sync(0xffffffffu, l[0], 1);
+    if ((threadIdx.x & 31) == 31) {
+      bool in = j0 + K1_VEC < T;
+      nh = in ? hsh[j0 + K1_VEC] : 0ull;
+      nl = in ? len[j0 + K1_VEC] : 1u;
+    }
+    h[K1_VEC] = nh; l[K1_VEC] = nl;
+#pragma unroll
+    for (int e = 0; e < K1_VEC; ++e) {
+      bool valid = (j0 + e + 1 < T) && !(g[e] & GB_LAST_FLAG);
+      out[e] = valid ? gb_key_h(h[e], g[e], h[e + 1], P, __ldg(powtab + (2u * l[e + 1] - 1u))) : GB_EMPTY_KEY;
+    }
+  }
+};
+
+struct KeysArr {
+  const u64* k;
+  __device__ __forceinline__ void keys(i64 j0, i64 T, u64 out[K1_VEC]) const {
+#pragma unroll
+    for (int e = 0; e < K1_VEC; ++e) out[e] = (j0 + e < T) ? k[j0 + e] : GB_EMPTY_KEY;
+  }
+};
+
+template <class KF>
+__global__ void __launch_bounds__(K1_THREADS, 2) k_pair_count(KF kf, i64 T, GTable g) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  STable s;
+  s.k = reinterpret_cast<u64*>(smem_raw);
+  s.c = reinterpret_cast<u32*>(smem_raw + sizeof(u64) * K1_SLOTS);
+  s.m = s.c + K1_SLOTS;
+  s.n_used = s.m + K1_SLOTS;
+  stable_reset(s);
+  __syncthreads();
+  for (i64 base = (i64)blockIdx.x * K1_TILE; base < T; base += (i64)gridDim.x * K1_TILE) {
+    i64 j0 = base + (i64)threadIdx.x * K1_VEC;
+    u64 key[K1_VEC];
+    kf.keys(j0, T, key);
+#pragma unroll
+    for (int e = 0; e < K1_VEC; ++e) warp_agg_add(s, g, key[e], (u32)(j0 + e));
+    __syncthreads();
+    if (*s.n_used > K1_FLUSH_AT) {   // uniform across the block (read after the barrier)
+      __syncthreads();
+      stable_flush(s, g);
+    }
+    __syncthreads();
+  }
+  stable_flush(s, g);
+}
+
+static const size_t K1_SMEM = sizeof(u64) * K1_SLOTS + sizeof(u32) * K1_SLOTS * 2 + 16;
+
+template <class KF>
+static int launch_pair_count(KF kf, i64 T, i64 min_T, u64* tkeys, u32* tcnt, u32* tmin, i64 M, int32_t* overflow, cudaStream_t st) {
+  if (M <= 0 || (M & (M - 1))) { gb_set_error("pair_count: table size %lld is not a power of two", (long long)M); return -2; }
+  if (T < min_T) return 0;
+  static bool attr_set = false;
+  if (!attr_set) {
+    GB_CK(cudaFuncSetAttribute(k_pair_count<KF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K1_SMEM));
+    attr_set = true;
+  }
+  int sms = gb_sm_count();
+  if (sms <= 0) sms = 148;
+  int blocks = gb_blocks_for(T, K1_TILE, sms * 2);   // persistent: 2 CTAs per SM
+  GTable g{tkeys, tcnt, tmin, (u64)(M - 1), overflow};
+  k_pair_count<KF><<<blocks, K1_THREADS, K1_SMEM, st>>>(kf, T, g);
+  GB_LAUNCH_CK();
+  return 0;
+}
+
+extern "C" int gb_pair_count_m(const uint32_t* cls, const uint32_t* glue, int64_t T, uint64_t* tkeys,
+                               uint32_t* tcnt, uint32_t* tmin, int64_t M, int32_t* overflow, void* stream) {
+  KeysM kf{cls, glue};
+  return launch_pair_count(kf, (i64)T, 2, (u64*)tkeys, tcnt, tmin, (i64)M, overflow, (cudaStream_t)stream);
+}
+extern "C" int gb_pair_count_h(const uint64_t* hsh, const uint32_t* glue, const uint32_t* len, int64_t T,
+                               const uint64_t* powtab, uint64_t P, uint64_t* tkeys, uint32_t* tcnt,
+                               uint32_t* tmin, int64_t M, int32_t* overflow, void* stream) {
+  KeysH kf{(const u64*)hsh, glue, len, (const u64*)powtab, (u64)P};
+  return launch_pair_count(kf, (i64)T, 2, (u64*)tkeys, tcnt, tmin, (i64)M, overflow, (cudaStream_t)stream);
+}
+extern "C" int gb_key_count(const uint64_t* keys, int64_t n, uint64_t* tkeys, uint32_t* tcnt, uint32_t* tmin,
+                            int64_t M, int32_t* overflow, void* stream) {
+  KeysArr kf{(const u64*)keys};
+  return launch_pair_count(kf, (i64)n, 1, (u64*)tkeys, tcnt, tmin, (i64)M, overflow, (cudaStream_t)stream);
+}
+
+// ---- table maintenance ---------------------------------------------------------------------------
+__global__ void k_table_clear(u64* __restrict__ tk, u32* __restrict__ tc, u32* __restrict__ tm, i64 M) {
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (i64)gridDim.x * blockDim.x) {
+    tk[i] = GB_EMPTY_KEY; tc[i] = 0u; tm[i] = 0xFFFFFFFFu;
+  }
+}
+extern "C" int gb_table_clear(uint64_t* tkeys, uint32_t* tcnt, uint32_t* tmin, int64_t M, void* stream) {
+  if (M <= 0) return 0;
+  k_table_clear<<<gb_blocks_for(M, 256 * 4, 148 * 8), 256, 0, (cudaStream_t)stream>>>((u64*)tkeys, tcnt, tmin, M);
+  GB_LAUNCH_CK();
+  return 0;
+}
+
+// out4 = {max count, #ties, #distinct, 0}
+__global__ void __launch_bounds__(256) k_table_max(const u32* __restrict__ tc, i64 M, u32* __restrict__ out4) {
+  u32 mx = 0, nd = 0;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (i64)gridDim.x * blockDim.x) {
+    u32 c = tc[i];
+    mx = c > mx ? c : mx;
+    nd += c != 0;
+  }
+  for (int o = 16; o; o >>= 1) {
+    u32 a = __shfl_xor_sync(0xffffffffu, mx, o); mx = a > mx ? a : mx;
+    nd += __shfl_xor_sync(0xffffffffu, nd, o);
+  }
+  if ((threadIdx.x & 31) == 0) { atomicMax(&out4[0], mx); atomicAdd(&out4[2], nd); }
+}
+__global__ void __launch_bounds__(256) k_table_ties(const u64* __restrict__ tk, const u32* __restrict__ tc,
+                                                     const u32* __restrict__ tm, i64 M, u32* __restrict__ out4,
+                                                     u64* __restrict__ tie_keys, u32* __restrict__ tie_min, int cap) {
+  const u32 mx = out4[0];
+  if (mx == 0) return;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (i64)gridDim.x * blockDim.x) {
+    if (tc[i] == mx) {
+      u32 k = atomicAdd(&out4[1], 1u);
+      if (k < (u32)cap) { tie_keys[k] = tk[i]; tie_min[k] = tm[i]; }
+    }
+  }
+}
+extern "C" int gb_table_argmax(const uint64_t* tkeys, const uint32_t* tcnt, const uint32_t* tmin, int64_t M,
+                               uint32_t* out4, uint64_t* tie_keys, uint32_t* tie_minpos, int cap, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  GB_CK(cudaMemsetAsync(out4, 0, 4 * sizeof(u32), st));
+  if (M <= 0) return 0;
+  int blocks = gb_blocks_for(M, 256 * 4, 148 * 8);
+  k_table_max<<<blocks, 256, 0, st>>>(tcnt, M, out4);
+  GB_LAUNCH_CK();
+  k_table_ties<<<blocks, 256, 0, st>>>((const u64*)tkeys, tcnt, tmin, M, out4, (u64*)tie_keys, tie_minpos, cap);
+  GB_LAUNCH_CK();
+  return 0;
+}
+
+__global__ void k_table_lookup(const u64* __restrict__ tk, const u32* __restrict__ tc, const u32* __restrict__ tm,
+                               u64 mask, const u64* __restrict__ q, int Q, u32* __restrict__ oc, u32* __restrict__ om) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Q) return;
+  u64 key = q[i];
+  u64 s = gb_mix64(key) & mask;
+  u32 c = 0, m = 0xFFFFFFFFu;
+  for (u64 p = 0; p <= mask; ++p) {
+    u64 k = tk[s];
+    if (k == key) { c = tc[s]; m = tm[s]; break; }
+    if (k == GB_EMPTY_KEY) break;
+    s = (s + 1) & mask;
+  }
+  oc[i] = c; om[i] = m;
+}
+extern "C" int gb_table_lookup(const uint64_t* tkeys, const uint32_t* tcnt, const uint32_t* tmin, int64_t M,
+                               const uint64_t* qkeys, int Q, uint32_t* out_cnt, uint32_t* out_min, void* stream) {
+  if (Q <= 0) return 0;
+  k_table_lookup<<<(Q + 127) / 128, 128, 0, (cudaStream_t)stream>>>((const u64*)tkeys, tcnt, tmin, (u64)(M - 1),
+                                                                    (const u64*)qkeys, Q, out_cnt, out_min);
+  GB_LAUNCH_CK();
+  return 0;
+}
+
+__global__ void __launch_bounds__(256) k_table_dump(const u64* __restrict__ tk, const u32* __restrict__ tc,
+                                                     const u32* __restrict__ tm, i64 M, u64* __restrict__ ok,
+                                                     u32* __restrict__ oc, u32* __restrict__ om, u32* __restrict__ total) {
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (i64)gridDim.x * blockDim.x) {
+    u32 c = tc[i];
+    if (c) {
+      u32 k = atomicAdd(total, 1u);
+      ok[k] = tk[i]; oc[k] = c; om[k] = tm[i];
+    }
+  }
+}
+extern "C" int gb_table_dump(const uint64_t* tkeys, const uint32_t* tcnt, const uint32_t* tmin, int64_t M,
+                             uint64_t* out_keys, uint32_t* out_cnt, uint32_t* out_min, uint32_t* total, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  GB_CK(cudaMemsetAsync(total, 0, sizeof(u32), st));
+  if (M <= 0) return 0;
+  k_table_dump<<<gb_blocks_for(M, 256 * 4, 148 * 8), 256, 0, st>>>((const u64*)tkeys, tcnt, tmin, M, (u64*)out_keys,
+                                                                   out_cnt, out_min, total);
+  GB_LAUNCH_CK();
+  return 0;
+}
+
+// fold the exact local table into key-less direct-mapped counters for the NCCL allreduce
+__global__ void __launch_bounds__(256) k_table_to_slots(const u64* __restrict__ tk, const u32* __restrict__ tc, i64 M,
+                                                         u32* __restrict__ slots, u64 smask) {
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (i64)gridDim.x * blockDim.x) {
+    u32 c = tc[i];
+    if (c) atomicAdd(&slots[(gb_mix64(tk[i] ^ 0x9E3779B97F4A7C15ull)) & smask], c);
+  }
+}
+extern "C" int gb_table_to_slots(const uint64_t* tkeys, const uint32_t* tcnt, int64_t M, uint32_t* slots,
+                                 int64_t NS, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (NS <= 0 || (NS & (NS - 1))) { gb_set_error("gb_table_to_slots: NS must be a power of two"); return -2; }
+  GB_CK(cudaMemsetAsync(slots, 0, sizeof(u32) * (size_t)NS, st));
+  if (M <= 0) return 0;
+  k_table_to_slots<<<gb_blocks_for(M, 256 * 4, 148 * 8), 256, 0, st>>>((const u64*)tkeys, tcnt, M, slots, (u64)(NS - 1));
+  GB_LAUNCH_CK();
+  return 0;
+}
