@@ -1,0 +1,94 @@
+"""ctypes binding of libgeobpe_b200.so (C ABI in include/geobpe_b200.h).
+
+The product path has no CPU fallback: a missing library or a missing CUDA device raises."""
+import ctypes as C
+import os
+
+import torch
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG, "libgeobpe_b200.so")
+
+P, I64, I32, U32, U64, F64 = C.c_void_p, C.c_int64, C.c_int, C.c_uint32, C.c_uint64, C.c_double
+
+# name -> argtypes (all return int unless listed in _RESTYPES)
+SIGNATURES = {
+    "gb_residue_backbone": [P, I64, I64, P, P],
+    "gb_select_flagged": [P, I64, U32, P, P, P, P],
+    "gb_select_eq_u64": [P, I64, U64, P, P, P, P],
+    "gb_col_minmax": [P, I64, I64, P, P, P],
+    "gb_col_hist": [P, I64, I64, P, I32, P, P, P],
+    "gb_quantize_residues": [P, I64, I64, P, P, I64, P, I32, P, I32, F64, F64, F64, P, P, P, P, P],
+    "gb_table_clear": [P, P, P, I64, P],
+    "gb_pair_count_m": [P, P, I64, P, P, P, I64, P, P],
+    "gb_pair_count_h": [P, P, P, I64, P, U64, P, P, P, I64, P, P],
+    "gb_key_count": [P, I64, P, P, P, I64, P, P],
+    "gb_table_argmax": [P, P, P, I64, P, P, P, I32, P],
+    "gb_table_lookup": [P, P, P, I64, P, I32, P, P, P],
+    "gb_table_dump": [P, P, P, I64, P, P, P, P, P],
+    "gb_table_to_slots": [P, P, I64, P, I64, P],
+    "gb_flag_pairs_m": [P, P, I64, U64, P, P],
+    "gb_flag_pairs_h": [P, P, P, I64, P, U64, U64, P, P],
+    "gb_resolve_overlaps": [P, I64, P],
+    "gb_scatter_u32": [P, P, I64, P, P],
+    "gb_merge_compact": [P, I64] + [P] * 6 + [P] * 6 + [P, P, P, U64, U32, P, P, P],
+    "gb_write_events": [P, I64, P, P, P, P, P, P],
+    "gb_oplog_m": [P, I64, P, P, P, P, I64, P, P, P, P, P],
+    "gb_pair_keys_m": [P, P, P, I64, P, P, P],
+    "gb_verify_windows_h": [P, I64, P, P, P, I64, U32, U32, P, P],
+    "gb_window_coords": [P, I64, I64, P, P, P, I64, I32, I32, P, P, F64, F64, F64, P, P, I32, P, P],
+    "gb_kabsch_assign": [P, I64, I32, P, I32, P, P, P],
+    "gb_rmsd_matrix": [P, I32, I32, P, P],
+    "gb_last_error": [],
+    "gb_abi_version": [],
+    "gb_sm_count": [],
+    "gb_select_scratch_elems": [I64],
+}
+_RESTYPES = {"gb_last_error": C.c_char_p, "gb_select_scratch_elems": I64}
+
+_lib = None
+launches = 0  # number of C-ABI calls that launched kernels (bench.py reports it)
+
+
+def load():
+    """dlopen the in-tree library and declare every prototype; raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: build it with `python -m geobpe_b200.build` "
+                           "(there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    for name, args in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the header and the library disagree
+        fn.argtypes = args
+        fn.restype = _RESTYPES.get(name, C.c_int)
+    _lib = lib
+    return lib
+
+
+def ptr(t):
+    if t is None:
+        return None
+    assert t.is_cuda and t.is_contiguous(), "C ABI takes contiguous CUDA tensors"
+    return t.data_ptr()
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def call(name, *args):
+    """Invoke a status-returning entry point on torch's current stream; raise RuntimeError on failure."""
+    global launches
+    lib = load()
+    rc = getattr(lib, name)(*args, stream())
+    launches += 1
+    if rc != 0:
+        raise RuntimeError(f"{name} failed ({rc}): {lib.gb_last_error().decode()}")
+
+
+def require_cuda():
+    if not torch.cuda.is_available():
+        raise RuntimeError("geobpe_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    load()

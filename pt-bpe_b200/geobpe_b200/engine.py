@@ -1,0 +1,661 @@
+"""Device-side state of the GeoBPE hot path and the host logic that drives the sm_100a kernels.
+
+Everything numeric here runs through the C ABI (include/geobpe_b200.h); PyTorch only owns the device
+buffers and the stream.  Host Python keeps what the reference keeps in Python objects and what must
+follow Python semantics exactly: the vocabulary dicts, JSON key strings for the tie-break
+(bpe.py:1149,1469), the numpy RNG stream and the k-medoids iterations on the device-computed distance
+matrix (algo.py:184-211).
+"""
+import ctypes as C
+import json
+import math
+
+import numpy as np
+import torch
+
+from . import _lib
+
+BOND_TYPES = ["N:CA", "CA:C", "0C:1N"]                # tokenizer.py:19
+BOND_ANGLES = ["tau", "CA:C:1N", "C:1N:1CA"]          # tokenizer.py:21
+DIHEDRAL_ANGLES = ["psi", "omega", "phi"]             # tokenizer.py:22
+BOND_LENGTHS = [1.46, 1.54, 1.34]                     # nerf.py:17-19
+COLUMNS = ["0C:1N", "N:CA", "CA:C", "phi", "psi", "omega", "tau", "CA:C:1N", "C:1N:1CA"]
+COL = {c: i for i, c in enumerate(COLUMNS)}
+# residue-major slot order of rbins / edges (include/geobpe_b200.h)
+SLOTS = ["N:CA", "CA:C", "0C:1N", "tau", "CA:C:1N", "psi", "omega", "C:1N:1CA", "phi"]
+SLOT = {c: i for i, c in enumerate(SLOTS)}
+N_INIT = np.array([17.047, 14.099, 3.625])            # nerf.py:22-24
+CA_INIT = np.array([16.967, 12.784, 4.338])
+C_INIT = np.array([15.685, 12.755, 5.133])
+TWO_PI = 2 * np.pi
+NOBIN = 0x3FF
+LAST = 0x80000000
+EMPTY = 0xFFFFFFFFFFFFFFFF
+P61 = (1 << 61) - 1
+HASH_BASE = 0x1B873593A5C1F3D7 % P61                  # fixed base of the histogram-mode content hash
+
+
+def _angle_between(v1, v2):                           # angles_and_coords.py:746-752
+    u1 = v1 / np.linalg.norm(v1)
+    u2 = v2 / np.linalg.norm(v2)
+    return np.arccos(np.clip(np.dot(u1, u2), -1.0, 1.0))
+
+
+INIT_N_CA = float(np.linalg.norm(N_INIT - CA_INIT))   # tokenizer.py:74-77
+INIT_CA_C = float(np.linalg.norm(CA_INIT - C_INIT))
+INIT_TAU = float(_angle_between(N_INIT - CA_INIT, C_INIT - CA_INIT))
+
+
+def get_ind(v, values):
+    """bpe.py:1165-1189 on host (used for the handful of constants; arrays go through K3)."""
+    import bisect
+    left = [s for s, _ in values]
+    ind = bisect.bisect_right(left, v) - 1
+    if ind < 0:
+        raise ValueError(f"value {v} is below the first bin range")
+    s, e = values[ind]
+    if ind == len(values) - 1 and v == e:
+        return ind
+    if s <= v < e:
+        return ind
+    raise ValueError(f"value {v} does not fall into any bin")
+
+
+def _dev():
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _empty(n, dtype):
+    return torch.empty(max(int(n), 1), dtype=dtype, device=_dev())
+
+
+def _zeros(n, dtype):
+    return torch.zeros(max(int(n), 1), dtype=dtype, device=_dev())
+
+
+def next_pow2(x):
+    return 1 << max(int(x) - 1, 1).bit_length()
+
+
+class Backbones:
+    """Internal coordinates of a shard of backbones resident in HBM: vals f64 [9][R] (reference column
+    order), CSR offsets, residue->backbone map.  72 B per residue."""
+
+    def __init__(self, vals, offsets):
+        _lib.require_cuda()
+        vals = np.ascontiguousarray(vals, dtype=np.float64)
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        assert vals.ndim == 2 and vals.shape[0] == 9 and offsets[-1] == vals.shape[1]
+        self.R = int(vals.shape[1])
+        self.S = int(len(offsets) - 1)
+        self.offsets_host = offsets
+        self.lens_host = np.diff(offsets)
+        if self.R >= (1 << 32) - 2:
+            raise ValueError("a shard holds at most 2^32-2 residues (u32 positions)")
+        self.vals = torch.from_numpy(vals).pin_memory().to(_dev(), non_blocking=True)
+        self.offsets = torch.from_numpy(offsets).to(_dev())
+        self.bb = _empty(self.R, torch.int32)
+        _lib.call("gb_residue_backbone", _lib.ptr(self.offsets), self.S, self.R, _lib.ptr(self.bb))
+        self.h2d_bytes = vals.nbytes + offsets.nbytes
+
+    def backbone_of(self, r):
+        return int(np.searchsorted(self.offsets_host, r, side="right") - 1)
+
+
+class Thresholds:
+    """K3 driver: bpe.py:820-876 _init_thresholds + plotting.py:305-337 save_histogram."""
+
+    def __init__(self, bb, bins, bin_strategy, std_bonds):
+        self.keys = BOND_ANGLES + DIHEDRAL_ANGLES + ([] if std_bonds else BOND_TYPES)
+        self.std_bonds = std_bonds
+        self.thresholds = {}
+        self.bin_counts = {}
+        R, S = bb.R, bb.S
+        mm = _empty(18, torch.float64)
+        cnt = _empty(9, torch.int64)
+        _lib.call("gb_col_minmax", _lib.ptr(bb.vals), R, R, _lib.ptr(mm), _lib.ptr(cnt))
+        mm = mm.cpu().numpy().reshape(9, 2)
+        consts = {"tau": INIT_TAU, "N:CA": INIT_N_CA, "CA:C": INIT_CA_C}
+        host_cols = None
+        for size, B in bins.items():
+            B = int(B)
+            if B >= NOBIN - 1 or B > 512:
+                raise NotImplementedError("the packed glue field holds at most 512 bins per type")
+            edges_by_key = {}
+            for key in self.keys:
+                circ = key not in BOND_TYPES
+                lo, hi = mm[COL[key]]
+                if key in consts:
+                    c = (consts[key] + TWO_PI) % TWO_PI if circ else consts[key]
+                    lo, hi = min(lo, c), max(hi, c)
+                if bin_strategy.startswith("histogram"):
+                    rng_ = (0, TWO_PI) if ("cover" in bin_strategy and circ) else None
+                    # same code path as np.histogram(a, bins=B): only min and max of a matter for the edges
+                    edges = np.histogram_bin_edges(np.array([lo, hi]), bins=B, range=rng_)
+                elif bin_strategy == "uniform":
+                    if host_cols is None:
+                        host_cols = bb.vals.cpu().numpy()
+                    col = host_cols[COL[key]]
+                    a = col[(col == col) & (col != 0.0)]
+                    if key in consts:
+                        a = np.concatenate([a, np.full(S, consts[key])])
+                    if circ:
+                        a = (a + 2 * np.pi) % (2 * np.pi)
+                    edges = np.quantile(np.sort(a), np.linspace(0, 1, B + 1))   # plotting.py:276
+                else:
+                    raise NotImplementedError(bin_strategy)
+                edges_by_key[key] = np.asarray(edges, dtype=np.float64)
+            estride = B + 1
+            e_col = np.zeros((9, estride))
+            nb = (C.c_int * 9)(*([0] * 9))
+            for key in self.keys:
+                e_col[COL[key]] = edges_by_key[key]
+                nb[COL[key]] = B
+            e_dev = torch.from_numpy(e_col).to(_dev())
+            counts = _empty(9 * estride, torch.int64)
+            _lib.load().gb_col_hist  # (prototype check)
+            _lib.call("gb_col_hist", _lib.ptr(bb.vals), R, R, _lib.ptr(e_dev), estride, nb, _lib.ptr(counts))
+            counts = counts.cpu().numpy().reshape(9, estride)
+            th, bc = {}, {}
+            for key in self.keys:
+                e = edges_by_key[key]
+                th[key] = [(float(s), float(t)) for s, t in zip(e[:-1], e[1:])]
+                cts = counts[COL[key], :B].copy()
+                if key in consts:
+                    circ = key not in BOND_TYPES
+                    c = (consts[key] + TWO_PI) % TWO_PI if circ else consts[key]
+                    cts[get_ind(c, th[key])] += S
+                bc[key] = [int(x) for x in cts]
+            self.thresholds[size] = th
+            self.bin_counts[size] = bc
+
+    def residue_major_edges(self, size):
+        """edges f64 [9][B+1] in residue-major slot order + nb int[9] for gb_quantize_residues."""
+        th = self.thresholds[size]
+        B = max(len(v) for v in th.values())
+        e = np.zeros((9, B + 1))
+        nb = [0] * 9
+        for key, iv in th.items():
+            e[SLOT[key], :len(iv)] = [s for s, _ in iv]
+            e[SLOT[key], len(iv)] = iv[-1][1]
+            nb[SLOT[key]] = len(iv)
+        return e, nb, B + 1
+
+
+class PairTable:
+    """K1 driver: open-addressing (key, count, min position) table in HBM + argmax outputs."""
+    TIE_CAP = 1 << 16
+
+    def __init__(self):
+        self.M = 0
+        self.out4 = _zeros(4, torch.int32)
+        self.tie_keys = _empty(self.TIE_CAP, torch.int64)
+        self.tie_min = _empty(self.TIE_CAP, torch.int32)
+        self.overflow = _zeros(1, torch.int32)
+        self.distinct = 0
+
+    def ensure(self, M):
+        M = next_pow2(max(M, 1 << 12))
+        if M != self.M:
+            self.M = M
+            self.keys = _empty(M, torch.int64)
+            self.cnt = _empty(M, torch.int32)
+            self.min = _empty(M, torch.int32)
+
+    def ptrs(self):
+        return _lib.ptr(self.keys), _lib.ptr(self.cnt), _lib.ptr(self.min), self.M
+
+    def count(self, launch, n_pairs_bound):
+        """clear + count (+ retry on overflow with a larger table) + argmax.  `launch(table)` issues the
+        count kernel.  Returns (max_count, [(key, minpos)...] tied at the max)."""
+        want = 4 * max(self.distinct, 1024) + 4096
+        first = self.M == 0
+        self.ensure(2 * n_pairs_bound if first else max(want, 1 << 12))
+        while True:
+            _lib.call("gb_table_clear", *self.ptrs())
+            self.overflow.zero_()
+            launch(self)
+            _lib.call("gb_table_argmax", *self.ptrs(), _lib.ptr(self.out4), _lib.ptr(self.tie_keys),
+                      _lib.ptr(self.tie_min), self.TIE_CAP)
+            out4 = self.out4.cpu().numpy().astype(np.int64) & 0xFFFFFFFF
+            ovf = int(self.overflow.item())
+            distinct = int(out4[2])
+            if ovf or distinct * 2 > self.M:      # keep the load factor below 1/2
+                self.ensure(self.M * 4)
+                continue
+            break
+        self.distinct = distinct
+        mx, nt = int(out4[0]), int(out4[1])
+        if nt > self.TIE_CAP:
+            raise RuntimeError(f"{nt} keys tied at count {mx}: tie list capacity {self.TIE_CAP} exceeded")
+        tk = self.tie_keys[:nt].cpu().numpy().astype(np.uint64)
+        tm = self.tie_min[:nt].cpu().numpy().astype(np.int64) & 0xFFFFFFFF
+        return mx, list(zip(tk.tolist(), tm.tolist()))
+
+    def lookup(self, keys):
+        if not keys:
+            return [], []
+        q = torch.tensor(np.array(keys, dtype=np.uint64).view(np.int64), device=_dev())
+        oc = _empty(len(keys), torch.int32)
+        om = _empty(len(keys), torch.int32)
+        _lib.call("gb_table_lookup", *self.ptrs(), _lib.ptr(q), len(keys), _lib.ptr(oc), _lib.ptr(om))
+        return ((oc.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).tolist(),
+                (om.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).tolist())
+
+
+class TokenState:
+    """Live-token SoA in HBM (ping-pong buffers for the merge compaction)."""
+    FIELDS = ("cls", "hsh", "glue", "pos", "len", "tid")
+    DTYPES = {"cls": torch.int32, "hsh": torch.int64, "glue": torch.int32, "pos": torch.int32,
+              "len": torch.int32, "tid": torch.int32}
+
+    def __init__(self, R, mode):
+        self.mode = mode                     # "H" or "M"
+        self.cap = R + 8                     # + padding so 128-bit loads at the tail stay in bounds
+        self.T = 0
+        use = [f for f in self.FIELDS if not ((f == "cls" and mode == "H") or (f == "hsh" and mode == "M"))]
+        self.a = {f: _zeros(self.cap, self.DTYPES[f]) for f in use}
+        self.b = {f: _zeros(self.cap, self.DTYPES[f]) for f in use}
+        self.flags = _zeros(self.cap, torch.uint8)
+        self.aux = _zeros(self.cap, torch.int32)
+        self.scratch = _empty(_lib.load().gb_select_scratch_elems(self.cap), torch.int32)
+        self.idx = _empty(self.cap, torch.int32)      # occurrence list (all flagged)
+        self.kept = _empty(self.cap, torch.int32)     # kept occurrences
+        self.u32 = _zeros(4, torch.int32)
+
+    def p(self, f, out=False):
+        d = self.b if out else self.a
+        return _lib.ptr(d[f]) if f in d else None
+
+    def swap(self):
+        self.a, self.b = self.b, self.a
+
+    def select(self, mask, out):
+        _lib.call("gb_select_flagged", _lib.ptr(self.flags), self.T, mask, _lib.ptr(out), _lib.ptr(self.u32),
+                  _lib.ptr(self.scratch))
+        return int(self.u32[0].item())
+
+
+def _u32(t):
+    """int32 device tensor holding u32 values -> int64 numpy"""
+    return t.cpu().numpy().astype(np.int64) & 0xFFFFFFFF
+
+
+class Learner:
+    """GeoBPE learn state for one shard of backbones.
+
+    mode "H": rmsd_partition_min_size = inf  (histogram-quantised motifs; std_bonds only, as in the reference)
+    mode "M": rmsd_partition_min_size = 0    (every motif is a medoid token; rmsd_super_res, not rmsd_only)
+    """
+
+    def __init__(self, vals, offsets, bins, bin_strategy="histogram", std_bonds=True, mode="H",
+                 rmsd_super_res=True, num_partitions=3, max_num_strucs=500, rng=None, verify=True):
+        if len(bins) != 1:
+            raise NotImplementedError("size-bucketed --bins (more than one bucket) is not built yet: keys would "
+                                      "need re-quantisation per bucket (SURVEY 7.2 hard part 2)")
+        if mode == "H" and not std_bonds:
+            raise NotImplementedError("histogram mode with free bonds raises KeyError in the reference "
+                                      "(bpe.py:1516-1517); only std_bonds=True is defined")
+        if mode == "M" and not rmsd_super_res:
+            raise NotImplementedError("medoid mode is built for rmsd_super_res=True (README setting)")
+        self.mode = mode
+        self.std_bonds = std_bonds
+        self.bins = dict(bins)
+        self.size0 = next(iter(bins))
+        self.num_partitions = num_partitions
+        self.max_num_strucs = max_num_strucs
+        self.rng = rng
+        self.verify = verify
+        self.bb = Backbones(vals, offsets)
+        self.th = Thresholds(self.bb, self.bins, bin_strategy, std_bonds)
+        self.table = PairTable()
+        self.tokens = {}            # BPE._tokens
+        self.pop_log = []           # (count, key string) per popped key
+        self.step_events = []       # (token id / n, ev_start, ev_count, key)
+        self.n_steps = 0
+        self._quantize()
+        self.ts = TokenState(self.bb.R, mode)
+        R = self.bb.R
+        self.ev_left = _empty(R, torch.int32)
+        self.ev_right = _empty(R, torch.int32)
+        self.ev_p = _empty(R, torch.int32)
+        self.ev_n = 0
+        if mode == "H":
+            self._init_tokens_h()
+        else:
+            self._init_tokens_m()
+
+    # ---- K3 ------------------------------------------------------------------------------------
+    def _quantize(self, bond_mode=None):
+        bb = self.bb
+        R, S = bb.R, bb.S
+        e, nb, estride = self.th.residue_major_edges(self.size0)
+        self.edges_rm = e
+        self.nb_rm = nb
+        self.estride = estride
+        self.edges_dev = torch.from_numpy(e).to(_dev())
+        self.rbins = _empty(9 * R, torch.int16)
+        self.glue_res = _empty(R, torch.int32)
+        self.sym = _empty(R, torch.int64)
+        self.status = _zeros(S, torch.int32)
+        if bond_mode is None:
+            bond_mode = 0 if self.std_bonds else 1
+        _lib.call("gb_quantize_residues", _lib.ptr(bb.vals), R, R, _lib.ptr(bb.bb), _lib.ptr(bb.offsets), S,
+                  _lib.ptr(self.edges_dev), estride, (C.c_int * 9)(*nb), bond_mode, INIT_N_CA, INIT_CA_C, INIT_TAU,
+                  _lib.ptr(self.rbins), _lib.ptr(self.glue_res), _lib.ptr(self.sym), _lib.ptr(self.status))
+        st = self.status.cpu().numpy()
+        self.status_host = st
+        if bond_mode != 2 and st.any():
+            i = int(np.nonzero(st)[0][0])
+            raise ValueError(f"value {'is below the first bin range' if st[i] & 1 else 'does not fall into any bin'} "
+                             f"(backbone {i})")   # get_ind's ValueErrors, bpe.py:1179-1189
+
+    def centre(self, key, b):
+        s, e = self.th.thresholds[self.size0][key][b]
+        return (s + e) / 2                           # sum(relv[ind]) / 2, bpe.py:1503
+
+    def window_bins(self, r0, nres):
+        """rbins of residues [r0, r0+nres) -> int array [9][nres] (host)"""
+        rb = self.rbins.view(9, self.bb.R)[:, r0:r0 + nres].cpu().numpy().astype(np.int64) & 0xFFFF
+        return rb
+
+    # ---- histogram mode --------------------------------------------------------------------------
+    def _init_tokens_h(self):
+        """bpe.py:229-260,393: residue tokens labelled in first-seen order of their bin-centre key."""
+        R = self.bb.R
+        tab = self.table
+        tab.ensure(1 << 16)
+        while True:
+            _lib.call("gb_table_clear", *tab.ptrs())
+            tab.overflow.zero_()
+            _lib.call("gb_key_count", _lib.ptr(self.sym), R, *tab.ptrs(), _lib.ptr(tab.overflow))
+            ok = _empty(tab.M, torch.int64); oc = _empty(tab.M, torch.int32); om = _empty(tab.M, torch.int32)
+            tot = _zeros(1, torch.int32)
+            _lib.call("gb_table_dump", *tab.ptrs(), _lib.ptr(ok), _lib.ptr(oc), _lib.ptr(om), _lib.ptr(tot))
+            n = int(tot.item())
+            if int(tab.overflow.item()) or 2 * n > tab.M:
+                tab.ensure(tab.M * 4)
+                continue
+            break
+        tab.M = 0  # force re-sizing for the pair table
+        syms = ok[:n].cpu().numpy()
+        firsts = _u32(om[:n])
+        order = np.argsort(firsts, kind="stable")
+        syms, firsts = syms[order], firsts[order]
+        # ids in first-seen order; per-residue id by binary search over the sorted distinct symbols
+        sort2 = np.argsort(syms)
+        sorted_syms = torch.from_numpy(syms[sort2]).to(_dev())
+        ids_of_sorted = torch.from_numpy(sort2.astype(np.int32)).to(_dev())
+        idx = torch.searchsorted(sorted_syms, self.sym)
+        tid = ids_of_sorted[idx]
+        for k, (s, r) in enumerate(zip(syms.tolist(), firsts.tolist())):
+            v = s - 1
+            tb, cb, pb = v & 0x3FF, (v >> 10) & 0x3FF, (v >> 20) & 0x3FF
+            d = {"N:CA": [BOND_LENGTHS[0]], "CA:C": [BOND_LENGTHS[1]], "tau": [self.centre("tau", tb)]}
+            if cb != NOBIN:
+                d.update({"0C:1N": [BOND_LENGTHS[2]], "CA:C:1N": [self.centre("CA:C:1N", cb)],
+                          "psi": [self.centre("psi", pb)]})
+            self.tokens[k] = json.loads(json.dumps(d, sort_keys=True))
+        ts = self.ts
+        ts.T = R
+        ts.a["hsh"][:R] = self.sym
+        ts.a["glue"][:R] = self.glue_res
+        ts.a["pos"][:R] = torch.arange(R, device=_dev(), dtype=torch.int32)
+        ts.a["len"][:R] = 1
+        ts.a["tid"][:R] = tid
+        maxlen = int(self.bb.lens_host.max()) if self.bb.S else 1
+        pw = [1]
+        for _ in range(2 * maxlen + 2):
+            pw.append(pw[-1] * HASH_BASE % P61)
+        self.powtab = torch.tensor(pw, dtype=torch.int64, device=_dev())
+
+    def _h_key_dict(self, r0, nres):
+        """compute_geo_key's dict for a fully histogram-quantised window (bpe.py:1225-1298)"""
+        rb = self.window_bins(r0, nres)
+        ends = rb[SLOT["CA:C:1N"], nres - 1] == NOBIN
+        m = nres - 1 if ends else nres
+        d = {"N:CA": [0] * nres, "CA:C": [0] * nres, "0C:1N": [0] * m,
+             "tau": rb[SLOT["tau"]].tolist(), "CA:C:1N": rb[SLOT["CA:C:1N"], :m].tolist(),
+             "psi": rb[SLOT["psi"], :m].tolist()}
+        if nres > 1:
+            d["omega"] = rb[SLOT["omega"], :nres - 1].tolist()
+            d["C:1N:1CA"] = rb[SLOT["C:1N:1CA"], :nres - 1].tolist()
+            d["phi"] = rb[SLOT["phi"], :nres - 1].tolist()
+        return d
+
+    def _count_pairs(self):
+        ts = self.ts
+        if self.mode == "H":
+            def launch(tab):
+                _lib.call("gb_pair_count_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab),
+                          HASH_BASE, *tab.ptrs(), _lib.ptr(tab.overflow))
+        else:
+            def launch(tab):
+                _lib.call("gb_pair_count_m", ts.p("cls"), ts.p("glue"), ts.T, *tab.ptrs(), _lib.ptr(tab.overflow))
+        return self.table.count(launch, ts.T)
+
+    def step_h(self):
+        """one merge iteration, histogram mode (bpe.py:1792-2166 with rmsd_key None)"""
+        ts = self.ts
+        mx, ties = self._count_pairs()
+        if mx == 0:
+            raise IndexError("no adjacent pairs left (the reference's peekitem(0) raises here too)")
+        mins = torch.tensor([m for _, m in ties], device=_dev(), dtype=torch.int64)
+        p0 = _u32(ts.a["pos"][mins]); l0 = _u32(ts.a["len"][mins]); l1 = _u32(ts.a["len"][mins + 1])
+        cands = []
+        for (key, _), r0, a, b in zip(ties, p0.tolist(), l0.tolist(), l1.tolist()):
+            d = self._h_key_dict(r0, a + b)
+            cands.append((json.dumps(d, sort_keys=True), key, r0, a + b))
+        key_str, key, r0, nres = min(cands)            # SortedDict order: (-count, key string)
+        n = len(self.tokens)
+        self.tokens[n] = json.loads(key_str)
+        self.pop_log.append((mx, key_str))
+        _lib.call("gb_flag_pairs_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), HASH_BASE,
+                  key, _lib.ptr(ts.flags))
+        if self.verify:
+            nocc = ts.select(1, ts.idx)
+            if nocc != mx:
+                raise RuntimeError(f"flagged {nocc} occurrences, histogram counted {mx}")
+            _lib.call("gb_verify_windows_h", _lib.ptr(ts.idx), nocc, ts.p("pos"), ts.p("len"), _lib.ptr(self.rbins),
+                      self.bb.R, r0, nres, _lib.ptr(ts.u32))
+            if int(ts.u32[0].item()):
+                raise RuntimeError("61-bit content-hash collision detected (window bins differ); re-run with another HASH_BASE")
+        self._merge(key, n, None, None)
+        self.n_steps += 1
+
+    def _merge(self, key, new_tid, p2cls, p2tid):
+        """K2: overlap rule, event log, stream compaction"""
+        ts = self.ts
+        _lib.call("gb_resolve_overlaps", _lib.ptr(ts.flags), ts.T)
+        nk = ts.select(2, ts.kept)
+        aux = _lib.ptr(ts.aux) if p2cls is not None else None
+        if self.ev_n + nk > self.ev_left.numel():
+            raise RuntimeError("merge-event log overflow")
+        off = self.ev_n * 4
+        _lib.call("gb_write_events", _lib.ptr(ts.kept), nk, ts.p("pos"), aux, self.ev_left.data_ptr() + off,
+                  self.ev_right.data_ptr() + off, self.ev_p.data_ptr() + off)
+        if self.mode == "M":
+            self._oplog(nk, p2cls)
+        _lib.call("gb_merge_compact", _lib.ptr(ts.flags), ts.T,
+                  ts.p("cls"), ts.p("hsh"), ts.p("glue"), ts.p("pos"), ts.p("len"), ts.p("tid"),
+                  ts.p("cls", True), ts.p("hsh", True), ts.p("glue", True), ts.p("pos", True), ts.p("len", True),
+                  ts.p("tid", True), aux, _lib.ptr(p2cls) if p2cls is not None else None,
+                  _lib.ptr(p2tid) if p2tid is not None else None, key, new_tid & 0xFFFFFFFF,
+                  _lib.ptr(ts.u32), _lib.ptr(ts.scratch))
+        newT = int(ts.u32[0].item())
+        assert newT == ts.T - nk, (newT, ts.T, nk)
+        ts.swap()
+        ts.T = newT
+        self.step_events.append((new_tid, self.ev_n, nk, key))
+        self.ev_n += nk
+        return nk
+
+    # ---- medoid mode ---------------------------------------------------------------------------------
+    def num_p(self, length):
+        return self.num_partitions[length] if isinstance(self.num_partitions, dict) else self.num_partitions
+
+    def window_geo(self, r0, nbonds, f3=None):
+        """Tokenizer.token_geo(3*k, nbonds, orig=True) (tokenizer.py:169-202) for the window starting at global
+        residue r0; f3 = current (N:CA, CA:C, tau) of the backbone's first residue (Tokenizer._init_*)."""
+        V = self.vals_host
+        nres = (nbonds + 1) // 3
+        full = nbonds == 3 * nres
+        b = self.bb.backbone_of(r0)
+        first = r0 == int(self.bb.offsets_host[b])
+        g = {k: [] for k in ["N:CA", "CA:C", "0C:1N", "tau", "CA:C:1N", "C:1N:1CA", "psi", "omega", "phi"]}
+        for k in range(nres):
+            r = r0 + k
+            if k == 0 and first:
+                nca, cac, tau = f3
+            else:
+                nca, cac, tau = V[COL["N:CA"], r - 1], V[COL["CA:C"], r - 1], V[COL["tau"], r - 1]
+            g["N:CA"].append(float(nca)); g["CA:C"].append(float(cac)); g["tau"].append(float(tau))
+            if k < nres - 1 or full:
+                g["0C:1N"].append(float(V[COL["0C:1N"], r])); g["CA:C:1N"].append(float(V[COL["CA:C:1N"], r]))
+                g["psi"].append(float(V[COL["psi"], r]))
+            if k < nres - 1:
+                g["omega"].append(float(V[COL["omega"], r])); g["C:1N:1CA"].append(float(V[COL["C:1N:1CA"], r]))
+                g["phi"].append(float(V[COL["phi"], r + 1]))
+        return {k: v for k, v in g.items() if v}
+
+    def intern_class(self, geo):
+        s = json.dumps(geo)
+        c = self.class_of.get(s)
+        if c is None:
+            c = len(self.class_geo)
+            if c >= (1 << 18):
+                raise RuntimeError("more than 2^18 geometry classes: packed 64-bit pair key exhausted")
+            self.class_of[s] = c
+            self.class_geo.append(geo)
+            self.class_f3.append([geo["N:CA"][0], geo["CA:C"][0], geo["tau"][0]])
+            self._f3_dirty = True
+        return c
+
+    def f3tab(self):
+        if self._f3_dirty:
+            self._f3_dev = torch.tensor(self.class_f3, dtype=torch.float64, device=_dev()).contiguous()
+            self._f3_dirty = False
+        return self._f3_dev
+
+    def coords(self, r0_dev, Q, nres, A, f3cls_dev):
+        out = _empty(Q * A * 3, torch.float64)
+        bb = self.bb
+        _lib.call("gb_window_coords", _lib.ptr(bb.vals), bb.R, bb.R, _lib.ptr(bb.bb), _lib.ptr(bb.offsets),
+                  _lib.ptr(r0_dev), Q, nres, A, _lib.ptr(f3cls_dev) if f3cls_dev is not None else None,
+                  _lib.ptr(self.f3tab()) if f3cls_dev is not None else None, self.d_f3[0], self.d_f3[1], self.d_f3[2],
+                  None, None, 0, _lib.ptr(out))
+        return out.view(Q, A * 3)
+
+    def k_medoids(self, coords, k):
+        """algo.py:144-211 on the device-computed float32 distance matrix"""
+        N = coords.shape[0]
+        k = min(N, k)
+        if k == N:
+            return list(range(N))
+        A = coords.shape[1] // 3
+        D = _empty(N * N, torch.float32)
+        _lib.call("gb_rmsd_matrix", _lib.ptr(coords.contiguous()), N, A, _lib.ptr(D))
+        D = D.view(N, N).cpu().numpy()
+        rng = self.rng
+        medoid_indices = rng.choice(np.arange(N), size=k, replace=False)
+        for _ in range(10):
+            assignments = np.argmin(D[:, medoid_indices], axis=1)
+            total_shift = 0.0
+            new_medoid_indices = []
+            for j in range(k):
+                members = np.where(assignments == j)[0]
+                if members.size == 0:
+                    new_idx = rng.integers(N)
+                else:
+                    intra = D[np.ix_(members, members)].sum(axis=1)
+                    new_idx = members[np.argmin(intra)]
+                total_shift += D[medoid_indices[j], new_idx]
+                new_medoid_indices.append(new_idx)
+            medoid_indices = new_medoid_indices
+            if total_shift < 1e-4:
+                break
+        return [int(m) for m in medoid_indices]
+
+    def assign(self, coords, med_coords):
+        Q, K = coords.shape[0], med_coords.shape[0]
+        A = coords.shape[1] // 3
+        out = _empty(Q, torch.int32)
+        _lib.call("gb_kabsch_assign", _lib.ptr(coords.contiguous()), Q, A, _lib.ptr(med_coords.contiguous()), K,
+                  _lib.ptr(out), None)
+        return out
+
+    def _init_tokens_m(self):
+        """bpe.py:263-391: residue tokens = nearest of K medoids (size 3 = inner residues, size 2 = last)."""
+        bb = self.bb
+        R, S = bb.R, bb.S
+        self.class_of, self.class_geo, self.class_f3, self._f3_dirty = {}, [], [], True
+        self.sphere_dict = {}
+        self.sphere_packed = {}        # packed key -> key string, for keys popped in step()
+        self.token_keys = []           # list(_tokens)
+        th1 = self.th.thresholds[self.size0]
+        if self.std_bonds:
+            self.d_f3 = (BOND_LENGTHS[0], BOND_LENGTHS[1], INIT_TAU)
+        else:
+            self.d_f3 = (self.centre("N:CA", get_ind(INIT_N_CA, th1["N:CA"])),
+                         self.centre("CA:C", get_ind(INIT_CA_C, th1["CA:C"])), INIT_TAU)
+        if self.std_bonds:
+            raise NotImplementedError("medoid mode with std_bonds needs quantised-bond coordinates; free_bonds only")
+        is_last = torch.zeros(R, dtype=torch.bool, device=_dev())
+        is_last[(bb.offsets[1:] - 1)] = True
+        lists = {3: torch.nonzero(~is_last).flatten().to(torch.int32), 2: torch.nonzero(is_last).flatten().to(torch.int32)}
+        order = [3, 2] if bb.lens_host[0] > 1 else [2, 3]
+        cls_res = _zeros(R, torch.int32)
+        tid_res = _zeros(R, torch.int32)
+        for n, size in enumerate(order):
+            occ = lists[size].contiguous()
+            N = int(occ.numel())
+            if N == 0:
+                continue
+            A = size + 1
+            if N > self.max_num_strucs:
+                active = self.rng.choice(N, self.max_num_strucs, replace=False)
+            else:
+                active = np.arange(N)
+            allc = self.coords(occ, N, 1, A, None)
+            act_dev = torch.from_numpy(np.asarray(active, dtype=np.int64)).to(_dev())
+            actc = allc[act_dev].contiguous()
+            med = self.k_medoids(actc, self.num_p(size))
+            medc = actc[torch.tensor(med, device=_dev(), dtype=torch.int64)].contiguous()
+            asg = self.assign(allc, medc)
+            if size == 3:
+                k = '{"N:CA": [0], "CA:C": [0], "0C:1N": [0], "tau": [0], "CA:C:1N": [0], "psi": [0]}'
+            else:
+                k = '{"CA:C": [0], "0C:1N": [0], "CA:C:1N": [0]}'
+            self.sphere_dict[k] = []
+            occ_h = _u32(occ)
+            p2cls, p2tid = [], []
+            for p, m in enumerate(med):
+                r0 = int(occ_h[int(active[m])])
+                geo = self.window_geo(r0, size, self.d_f3)
+                self.sphere_dict[k].append(geo)
+                p2tid.append(len(self.token_keys))
+                self.tokens[(n, p)] = geo
+                self.token_keys.append((n, p))
+                p2cls.append(self.intern_class(geo))
+            p2cls_d = torch.tensor(p2cls, dtype=torch.int32, device=_dev())
+            p2tid_d = torch.tensor(p2tid, dtype=torch.int32, device=_dev())
+            occ_l = occ.to(torch.int64)
+            cls_res[occ_l] = p2cls_d[asg.to(torch.int64)]
+            tid_res[occ_l] = p2tid_d[asg.to(torch.int64)]
+        ts = self.ts
+        ts.T = R
+        ts.a["cls"][:R] = cls_res
+        ts.a["glue"][:R] = self.glue_res
+        ts.a["pos"][:R] = torch.arange(R, device=_dev(), dtype=torch.int32)
+        ts.a["len"][:R] = 1
+        ts.a["tid"][:R] = tid_res
+        # op log of the occurrence sets: initial segment = every adjacent pair in order (bpe.py:1441-1453)
+        self.log_cap = 5 * R + 16
+        self.log_key = _empty(self.log_cap, torch.int64)
+        self.log_pos = _empty(self.log_cap, torch.int32)
+        self.log_scratch = _empty(_lib.load().gb_select_scratch_elems(self.log_cap), torch.int32)
+        self.log_sel = _empty(self.log_cap, torch.int32)
+        _lib.call("gb_pair_keys_m", ts.p("cls"), ts.p("glue"), ts.p("pos"), R, _lib.ptr(self.log_key), _lib.ptr(self.log_pos))
+        self.log_n = R
+        self.log_bounds = [R]          # end offsets of: initial segment, step 1, step 2, ...
+        self.key_reset_at = {}         # packed key -> log offset after which its set is fresh
