@@ -307,6 +307,9 @@ class Learner:
         self.rng = rng
         self.verify = verify
         self.bb = Backbones(vals, offsets)
+        self.vals_host = np.ascontiguousarray(vals, dtype=np.float64)
+        self.sphere_n = {}
+        self._peek = None
         self.th = Thresholds(self.bb, self.bins, bin_strategy, std_bonds)
         self.table = PairTable()
         self.tokens = {}            # BPE._tokens
@@ -403,25 +406,32 @@ class Learner:
         ts.a["pos"][:R] = torch.arange(R, device=_dev(), dtype=torch.int32)
         ts.a["len"][:R] = 1
         ts.a["tid"][:R] = tid
+        self.init_tid = tid.clone()
         maxlen = int(self.bb.lens_host.max()) if self.bb.S else 1
         pw = [1]
         for _ in range(2 * maxlen + 2):
             pw.append(pw[-1] * HASH_BASE % P61)
         self.powtab = torch.tensor(pw, dtype=torch.int64, device=_dev())
 
-    def _h_key_dict(self, r0, nres):
-        """compute_geo_key's dict for a fully histogram-quantised window (bpe.py:1225-1298)"""
-        rb = self.window_bins(r0, nres)
-        ends = rb[SLOT["CA:C:1N"], nres - 1] == NOBIN
-        m = nres - 1 if ends else nres
-        d = {"N:CA": [0] * nres, "CA:C": [0] * nres, "0C:1N": [0] * m,
-             "tau": rb[SLOT["tau"]].tolist(), "CA:C:1N": rb[SLOT["CA:C:1N"], :m].tolist(),
-             "psi": rb[SLOT["psi"], :m].tolist()}
-        if nres > 1:
-            d["omega"] = rb[SLOT["omega"], :nres - 1].tolist()
-            d["C:1N:1CA"] = rb[SLOT["C:1N:1CA"], :nres - 1].tolist()
-            d["phi"] = rb[SLOT["phi"], :nres - 1].tolist()
-        return d
+    def _h_key_dicts(self, r0s, nress):
+        """compute_geo_key's dict for fully histogram-quantised windows (bpe.py:1225-1298); one batched gather"""
+        idx = np.concatenate([np.arange(r, r + n) for r, n in zip(r0s, nress)])
+        rb_all = self.rbins.view(9, self.bb.R)[:, torch.from_numpy(idx).to(_dev())].cpu().numpy().astype(np.int64) & 0xFFFF
+        out, o = [], 0
+        for nres in nress:
+            rb = rb_all[:, o:o + nres]
+            o += nres
+            ends = rb[SLOT["CA:C:1N"], nres - 1] == NOBIN
+            m = nres - 1 if ends else nres
+            d = {"N:CA": [0] * nres, "CA:C": [0] * nres, "0C:1N": [0] * m,
+                 "tau": rb[SLOT["tau"]].tolist(), "CA:C:1N": rb[SLOT["CA:C:1N"], :m].tolist(),
+                 "psi": rb[SLOT["psi"], :m].tolist()}
+            if nres > 1:
+                d["omega"] = rb[SLOT["omega"], :nres - 1].tolist()
+                d["C:1N:1CA"] = rb[SLOT["C:1N:1CA"], :nres - 1].tolist()
+                d["phi"] = rb[SLOT["phi"], :nres - 1].tolist()
+            out.append(d)
+        return out
 
     def _count_pairs(self):
         ts = self.ts
@@ -442,10 +452,10 @@ class Learner:
             raise IndexError("no adjacent pairs left (the reference's peekitem(0) raises here too)")
         mins = torch.tensor([m for _, m in ties], device=_dev(), dtype=torch.int64)
         p0 = _u32(ts.a["pos"][mins]); l0 = _u32(ts.a["len"][mins]); l1 = _u32(ts.a["len"][mins + 1])
-        cands = []
-        for (key, _), r0, a, b in zip(ties, p0.tolist(), l0.tolist(), l1.tolist()):
-            d = self._h_key_dict(r0, a + b)
-            cands.append((json.dumps(d, sort_keys=True), key, r0, a + b))
+        nress = (l0 + l1).tolist()
+        dicts = self._h_key_dicts(p0.tolist(), nress)
+        cands = [(json.dumps(d, sort_keys=True), key, r0, nr)
+                 for (key, _), d, r0, nr in zip(ties, dicts, p0.tolist(), nress)]
         key_str, key, r0, nres = min(cands)            # SortedDict order: (-count, key string)
         n = len(self.tokens)
         self.tokens[n] = json.loads(key_str)
@@ -649,6 +659,7 @@ class Learner:
         ts.a["pos"][:R] = torch.arange(R, device=_dev(), dtype=torch.int32)
         ts.a["len"][:R] = 1
         ts.a["tid"][:R] = tid_res
+        self.init_tid = tid_res.clone()
         # op log of the occurrence sets: initial segment = every adjacent pair in order (bpe.py:1441-1453)
         self.log_cap = 5 * R + 16
         self.log_key = _empty(self.log_cap, torch.int64)
@@ -659,3 +670,184 @@ class Learner:
         self.log_n = R
         self.log_bounds = [R]          # end offsets of: initial segment, step 1, step 2, ...
         self.key_reset_at = {}         # packed key -> log offset after which its set is fresh
+
+    def _oplog(self, nk, p2cls):
+        ts = self.ts
+        if self.log_n + 4 * nk > self.log_cap:
+            raise RuntimeError("occurrence-set op log overflow")
+        _lib.call("gb_oplog_m", _lib.ptr(ts.kept), nk, _lib.ptr(ts.flags), ts.p("cls"), ts.p("glue"), ts.p("pos"), ts.T,
+                  _lib.ptr(ts.aux), _lib.ptr(p2cls), self.log_key.data_ptr() + 8 * self.log_n,
+                  self.log_pos.data_ptr() + 4 * self.log_n)
+        self.log_n += 4 * nk
+        self.log_bounds.append(self.log_n)
+
+    def set_order(self, key):
+        """list(self._geo_dict[key]) (bpe.py:1744,1829,1888): replay this key's add/remove history through a real
+        CPython set, in the reference's operation order, and read its iteration order."""
+        _lib.call("gb_select_eq_u64", _lib.ptr(self.log_key), self.log_n, key, _lib.ptr(self.log_sel),
+                  _lib.ptr(self.ts.u32), _lib.ptr(self.log_scratch))
+        n = int(self.ts.u32[0].item())
+        sel = self.log_sel[:n]
+        idx = _u32(sel)
+        rpos = _u32(self.log_pos[sel.to(torch.int64)])
+        start = self.key_reset_at.get(key, 0)
+        keep = idx >= start
+        idx, rpos = idx[keep], rpos[keep]
+        offs = self.bb.offsets_host
+        bi = np.searchsorted(offs, rpos, side="right") - 1
+        index = 3 * (rpos - offs[bi])
+        bounds = np.asarray(self.log_bounds)
+        seg = np.searchsorted(bounds, idx, side="right")          # 0 = initial adds, s = step s
+        seg_start = np.concatenate([[0], bounds])[seg]
+        is_add = (seg == 0) | (((idx - seg_start) % 4) >= 2)
+        s = set()
+        cur = 0
+        for sg, add, i, ix in zip(seg.tolist(), is_add.tolist(), bi.tolist(), index.tolist()):
+            if sg != cur:
+                if not s:
+                    s = set()          # count hit 0 at the end of a step -> _geo_dict.pop(k) (bpe.py:2134-2135)
+                cur = sg
+            if add:
+                s.add((i, ix))
+            else:
+                s.remove((i, ix))
+        return list(s)
+
+    def m_key_string(self, key):
+        """json string of compute_geo_key for a medoid-medoid pair (bpe.py:1248-1256): raw medoid floats,
+        glue bins at the split"""
+        cL, cR, g = (key >> 45) & 0x3FFFF, (key >> 27) & 0x3FFFF, key & 0x7FFFFFF
+        gl, gr = self.class_geo[cL], self.class_geo[cR]
+        glue = {"omega": g & 0x1FF, "C:1N:1CA": (g >> 9) & 0x1FF, "phi": (g >> 18) & 0x1FF}
+        d = {}
+        for k in ["N:CA", "CA:C", "0C:1N", "tau", "CA:C:1N", "C:1N:1CA", "psi", "omega", "phi"]:
+            v = list(gl.get(k, []))
+            if k in glue:
+                v.append(int(glue[k]))
+            v += gr.get(k, [])
+            if v:
+                d[k] = v
+        return json.dumps(d, sort_keys=True), d
+
+    def peek_m(self):
+        """recount (K1) and look at the top of the priority order: (max count, ties, recurring choice or None).
+        Keys that already own medoids sort first whatever their count (bpe.py:2121-2127,2164-2166)."""
+        if self._peek is None:
+            mx, ties = self._count_pairs()
+            rec = None
+            if self.sphere_packed:
+                pk = list(self.sphere_packed)
+                cnts, _ = self.table.lookup(pk)
+                live = [(-c, self.sphere_packed[k], k) for k, c in zip(pk, cnts) if c > 0]
+                if live:
+                    negc, key_str, key = min(live)
+                    rec = (-negc, key_str, key)
+            self._peek = (mx, ties, rec)
+        return self._peek
+
+    def step_m(self):
+        """one merge iteration, medoid mode (bpe.py:1792-2166 with rmsd_key = key)"""
+        ts = self.ts
+        mx, ties, rec = self.peek_m()
+        self._peek = None
+        if mx == 0:
+            raise IndexError("no adjacent pairs left")
+        recurring = rec is not None
+        if recurring:
+            mx, key_str, key = rec
+        else:
+            key_str, key = min((self.m_key_string(k)[0], k) for k, _ in ties)
+        self.pop_log.append((mx, key_str))
+        cL, cR = (key >> 45) & 0x3FFFF, (key >> 27) & 0x3FFFF
+        gl, gr = self.class_geo[cL], self.class_geo[cR]
+        nb = lambda g: len(g["N:CA"]) + len(g["CA:C"]) + len(g.get("0C:1N", []))
+        length = nb(gl) + nb(gr)
+        nres = (length + 1) // 3
+        A = length + 1
+        _lib.call("gb_flag_pairs_m", ts.p("cls"), ts.p("glue"), ts.T, key, _lib.ptr(ts.flags))
+        N = ts.select(1, ts.idx)
+        if N != mx:
+            raise RuntimeError(f"flagged {N} occurrences, histogram counted {mx}")
+        occ = ts.idx[:N].to(torch.int64)
+        r0 = ts.a["pos"][occ].contiguous()
+        f3c = ts.a["cls"][occ].contiguous()
+        allc = self.coords(r0, N, nres, A, f3c)
+        if recurring:
+            geos = self.sphere_dict[key_str]
+            n = self.sphere_n[key_str]
+            medc = self.geo_coords(geos, A)
+        else:
+            all_pos = self.set_order(key)
+            if len(all_pos) != N:
+                raise RuntimeError(f"occurrence-set replay gave {len(all_pos)} entries, expected {N}")
+            rpos = _u32(ts.a["pos"][occ + 1])                     # global residue of the right token, ascending
+            offs = self.bb.offsets_host
+            gp = np.array([offs[i] + ix // 3 for i, ix in all_pos], dtype=np.int64)
+            rank = np.searchsorted(rpos, gp)                      # occurrence rank of every set entry
+            if N > self.max_num_strucs:
+                active = self.rng.choice(N, self.max_num_strucs, replace=False)
+            else:
+                active = np.arange(N)
+            act_rank = rank[active]
+            actc = allc[torch.from_numpy(act_rank).to(_dev())].contiguous()
+            med = self.k_medoids(actc, self.num_p(length))
+            medc = actc[torch.tensor(med, device=_dev(), dtype=torch.int64)].contiguous()
+            r0_h, f3c_h = _u32(r0), _u32(f3c)
+            geos = []
+            for m in med:
+                q = int(act_rank[m])
+                geos.append(self.window_geo(int(r0_h[q]), length, self.class_f3[int(f3c_h[q])]))
+            self.sphere_dict[key_str] = geos
+            self.sphere_packed[key] = key_str
+            n = len(self.tokens)
+            self.sphere_n[key_str] = n
+            for p, geo in enumerate(geos):
+                self.tokens[(n, p)] = geo
+                self.token_keys.append((n, p))
+        p2cls = torch.tensor([self.intern_class(g) for g in geos], dtype=torch.int32, device=_dev())
+        tid0 = self.token_keys.index((n, 0))
+        p2tid = torch.arange(tid0, tid0 + len(geos), dtype=torch.int32, device=_dev())
+        asg = self.assign(allc, medc)
+        _lib.call("gb_scatter_u32", _lib.ptr(ts.idx), _lib.ptr(asg), N, _lib.ptr(ts.aux))
+        self._merge(key, n, p2cls, p2tid)
+        self.key_reset_at[key] = self.log_n
+        if not recurring:
+            self.n_steps += 1
+        return recurring
+
+    def geo_coords(self, geos, A):
+        """Tokenizer.key_coords (tokenizer.py:204-230) for medoid geometries: each one placed in its own blank
+        backbone and run through K4."""
+        nres = A // 3 if A % 3 == 0 else (A - 1) // 3
+        K = len(geos)
+        vals = np.full((9, K * (nres + 1)), np.nan)
+        vals[:3] = 0.0
+        f3 = []
+        for k, g in enumerate(geos):
+            b = k * (nres + 1)
+            f3.append([g["N:CA"][0], g["CA:C"][0], g["tau"][0]])
+            for r in range(nres):
+                if r > 0:
+                    vals[COL["N:CA"], b + r - 1] = g["N:CA"][r]; vals[COL["CA:C"], b + r - 1] = g["CA:C"][r]
+                    vals[COL["tau"], b + r - 1] = g["tau"][r]
+                if r < len(g.get("0C:1N", [])):
+                    vals[COL["0C:1N"], b + r] = g["0C:1N"][r]; vals[COL["CA:C:1N"], b + r] = g["CA:C:1N"][r]
+                    vals[COL["psi"], b + r] = g["psi"][r]
+                if r < len(g.get("omega", [])):
+                    vals[COL["omega"], b + r] = g["omega"][r]; vals[COL["C:1N:1CA"], b + r] = g["C:1N:1CA"][r]
+                    vals[COL["phi"], b + r + 1] = g["phi"][r]
+        offsets = np.arange(K + 1, dtype=np.int64) * (nres + 1)
+        mini = Backbones(vals, offsets)
+        f3t = torch.tensor(f3, dtype=torch.float64, device=_dev())
+        r0 = torch.from_numpy(offsets[:-1].astype(np.int32)).to(_dev())
+        f3c = torch.arange(K, dtype=torch.int32, device=_dev())
+        out = _empty(K * A * 3, torch.float64)
+        _lib.call("gb_window_coords", _lib.ptr(mini.vals), mini.R, mini.R, _lib.ptr(mini.bb), _lib.ptr(mini.offsets),
+                  _lib.ptr(r0), K, nres, A, _lib.ptr(f3c), _lib.ptr(f3t), 0.0, 0.0, 0.0, None, None, 0, _lib.ptr(out))
+        return out.view(K, A * 3)
+
+    def step(self):
+        if self.mode == "H":
+            self.step_h()
+            return False
+        return self.step_m()
