@@ -129,7 +129,9 @@ __global__ void __launch_bounds__(128) k_rmsd_matrix(const double* __restrict__ 
   if (t >= (i64)N * N) return;
   int i = (int)(t / N), j = (int)(t % N);
   if (j < i) return;
-  double d = gb_kabsch_rmsd(P + (i64)i * A * 3, P + (i64)j * A * 3, A);   // compute_rmsd(strucs[i], strucs[j])
+  // compute_rmsd(strucs[i], strucs[j]); the diagonal is ~1e-16 in the reference (exact 0 after float32 sums),
+  // here E0 - 2*sum(sigma) cancels to ~1e-8, so it is pinned to 0
+  double d = (i == j) ? 0.0 : gb_kabsch_rmsd(P + (i64)i * A * 3, P + (i64)j * A * 3, A);
   float f = (float)d;
   D[(i64)i * N + j] = f;
   D[(i64)j * N + i] = f;
