@@ -1,0 +1,300 @@
+#!/usr/bin/env python
+"""bench.py -- GeoBPE learn hot path on B200 (BASELINE.json metric: BPE merge iterations / s).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--mode H|M] [--impl reference]
+
+A "step" is one merge iteration (K1 pair count + argmax, tie-break, K2 merge [+K4/K5/K6 in medoid mode]) over
+the resident shard of synthetic backbones.  N=1 workload = BASELINE.json configs[1]: 10k backbones x 256
+residues, histogram quantisation, 2,000 merges.  N>1: every rank holds its own 10k x 256 shard (weak scaling),
+pair counts combined by an NCCL allreduce.  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "pt-bpe_b200"))
+
+import numpy as np
+
+INF = float("inf")
+NUM_P = {2: 2, 3: 5, 5: 1, 6: 2, 8: 1}          # README cmd 1 --num-p (encode.sh:35)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--mode", default="H", choices=["H", "M"])
+    ap.add_argument("--backbones", type=int, default=10000)
+    ap.add_argument("--residues", type=int, default=256)
+    ap.add_argument("--bins", type=int, default=None)
+    ap.add_argument("--cpu-backbones", type=int, default=320)
+    ap.add_argument("--cpu-steps", type=int, default=2000)
+    ap.add_argument("--no-scale-probe", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def hparams(mode, bins):
+    if mode == "H":
+        return dict(bins={1: bins or 8}, bin_strategy="histogram", std_bonds=True, mode="H")
+    return dict(bins={1: bins or 50}, bin_strategy="histogram", std_bonds=False, mode="M", rmsd_super_res=True,
+                num_partitions=NUM_P, max_num_strucs=500)
+
+
+def oracle_hparams(mode, bins):
+    if mode == "H":
+        return dict(bins={1: bins or 8}, bin_strategy="histogram", std_bonds=True, rmsd_partition_min_size=INF)
+    return dict(bins={1: bins or 50}, bin_strategy="histogram", std_bonds=False, rmsd_partition_min_size=0,
+                rmsd_super_res=True, num_partitions=NUM_P, max_num_strucs=500)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.stop = [], False
+        self.index = index
+        self.t = threading.Thread(target=self.run, daemon=True)
+
+    def run(self):
+        while not self.stop:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.t.join(timeout=6)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(r[3 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def reference_arm(args):
+    """--impl reference / cpu_baseline: the CPU oracle (port of the reference's algorithm; the reference itself is
+    Python and cannot travel to the GPU box) on a BOUNDED sample of the same workload, host cores."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import geobpe_oracle as O
+    from geobpe_b200 import synthetic
+    S, n = args.cpu_backbones, args.residues
+    vals, offs = synthetic.generate(S, n, seed=0)
+    strucs = synthetic.to_structures(vals, offs)
+    t0 = time.perf_counter()
+    bpe = O.BPE(strucs, res_init=True, seed=0, **oracle_hparams(args.mode, args.bins))
+    bpe.initialize()
+    t1 = time.perf_counter()
+    bpe.bin()
+    t2 = time.perf_counter()
+    k = 0
+    nsteps = min(args.steps + args.warmup, args.cpu_steps)
+    while k < nsteps:
+        bpe.step()
+        k += 1
+    t3 = time.perf_counter()
+    return {"value": k / (t3 - t0), "steps_only_value": k / (t3 - t2), "unit": "merge_iters/s", "cores": 1, "kind": "port",
+            "sample": f"{S} backbones x {n} residues ({S * n} residues), mode {args.mode}, value = steps/(initialize+bin+steps): initialize {t1 - t0:.2f}s, "
+                      f"bin {t2 - t1:.2f}s, {k} steps {t3 - t2:.3f}s (incremental; cost grows with occurrences/merge; "
+                      f"bin() alone extrapolates linearly to {(t2 - t1) * args.backbones / S:.0f}s at {args.backbones} backbones)",
+            "init_s": t1 - t0, "bin_s": t2 - t1, "steps_s": t3 - t2}
+
+
+def k1_scale_probe(learner, mode, reps=20, target_tokens=48_000_000):
+    """K1 alone at the per-GPU shard size of BASELINE config 5 (48 M live tokens): the token arrays of this
+    workload tiled on the device (same key distribution), larger than L2 (126 MB)."""
+    import torch
+    from geobpe_b200 import _lib, engine as E
+    ts = learner.ts
+    T0 = ts.T
+    rep = max(1, target_tokens // T0)
+    T = T0 * rep
+    tab = E.PairTable()
+    tab.ensure(4 * max(learner.table.distinct, 1024) + 4096)
+    if mode == "H":
+        h = ts.a["hsh"][:T0].repeat(rep).contiguous(); g = ts.a["glue"][:T0].repeat(rep).contiguous()
+        l = ts.a["len"][:T0].repeat(rep).contiguous()
+        pad = lambda t: torch.cat([t, torch.zeros(8, dtype=t.dtype, device=t.device)])
+        h, g, l = pad(h), pad(g), pad(l)
+        l[T:] = 1
+        launch = lambda: _lib.call("gb_pair_count_h", _lib.ptr(h), _lib.ptr(g), _lib.ptr(l), T, _lib.ptr(learner.powtab),
+                                   E.HASH_BASE, *tab.ptrs(), _lib.ptr(tab.overflow))
+        bpt = 16
+    else:
+        c = ts.a["cls"][:T0].repeat(rep).contiguous(); g = ts.a["glue"][:T0].repeat(rep).contiguous()
+        pad = lambda t: torch.cat([t, torch.zeros(8, dtype=t.dtype, device=t.device)])
+        c, g = pad(c), pad(g)
+        launch = lambda: _lib.call("gb_pair_count_m", _lib.ptr(c), _lib.ptr(g), T, *tab.ptrs(), _lib.ptr(tab.overflow))
+        bpt = 8
+    ms = []
+    for i in range(reps + 3):
+        _lib.call("gb_table_clear", *tab.ptrs())
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); launch(); e1.record()
+        torch.cuda.synchronize()
+        if i >= 3:
+            ms.append(e0.elapsed_time(e1))
+    assert int(tab.overflow.item()) == 0
+    return T, bpt, float(np.mean(ms)), float(np.min(ms))
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        r = reference_arm(args)
+        line = {"impl": "reference", "metric": "bpe_merge_iters_per_s", "value": r["value"], "unit": "merge_iters/s",
+                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": 1e3 / r["value"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "u64" if args.mode == "H" else "f64", "data": "synthetic",
+                "config": {"workload": f"BASELINE configs[1] bounded sample on host cores: {r['sample']}"},
+                "cpu_baseline": r, "e2e": {"value": r["value"], "unit": "merge_iters/s", "h2d_bytes_per_step": 0,
+                                           "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from geobpe_b200 import _lib, engine as E, synthetic
+    from geobpe_b200 import build as B
+    B.build()
+    hp = hparams(args.mode, args.bins)
+    vals, offs = synthetic.generate(args.backbones, args.residues, seed=rank)
+    R = int(offs[-1])
+    mk = lambda: E.Learner(vals, offs, rng=np.random.default_rng(0), verify=True, **hp)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- device-resident arm: inputs already in HBM, W warm-up + K timed merge iterations ----------------
+    L = mk()
+    for _ in range(args.warmup):
+        L.step()
+    L.k1_events = []
+    T_start = L.ts.T
+    barrier()
+    launches0 = _lib.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk:
+        e0.record()
+        done = 0
+        while done < args.steps:
+            L.step()
+            done += 1
+        e1.record()
+        barrier()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    launches = _lib.launches - launches0
+    k1_ms = [a.elapsed_time(b) for a, b, _ in L.k1_events]
+    k1_T = [t for _, _, t in L.k1_events]
+    bpt = 16 if args.mode == "H" else 8
+    k1_avg_ms = float(np.mean(k1_ms))
+    k1_bytes = bpt * float(np.mean(k1_T))
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s"
+    achieved = k1_bytes / (k1_avg_ms * 1e-3) / 1e9
+    distinct, pairs, top = L.table.distinct, L.ts.T - L.bb.S, L.pop_log[-1][0]
+    T_end = L.ts.T
+    k1_share = sum(k1_ms) / ms
+    L.k1_events = None
+    scale = None
+    if not args.no_scale_probe and rank == 0:
+        Ts, b2, avg, best = k1_scale_probe(L, args.mode)
+        a2 = b2 * Ts / (avg * 1e-3) / 1e9
+        scale = {"bound": "hbm", "tokens": Ts, "bytes_per_token": b2, "ms": avg, "ms_min": best, "achieved": a2,
+                 "peak": peak, "unit": "GB/s", "frac": a2 / peak,
+                 "note": "K1 alone on this workload's token arrays tiled to the per-GPU shard of BASELINE config 5 (48 M tokens > L2)"}
+    del L
+    torch.cuda.empty_cache()
+
+    # ---- e2e arm: host buffers -> H2D -> initialize (K3, residue tokens) -> K merges -> D2H token arrays ----
+    e2e = None
+    if not args.no_e2e:
+        barrier()
+        t0 = time.perf_counter()
+        L2 = mk()
+        for _ in range(args.steps):
+            L2.step()
+        ts = L2.ts
+        out = [ts.a[f][:ts.T].cpu() for f in ("pos", "len", "tid")]
+        n_ev = L2.ev_n
+        out += [L2.ev_left[:n_ev].cpu(), L2.ev_right[:n_ev].cpu()]
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        d2h = sum(o.numel() * o.element_size() for o in out)
+        e2e = {"value": args.steps / dt, "unit": "merge_iters/s", "h2d_bytes_per_step": L2.bb.h2d_bytes / args.steps,
+               "d2h_bytes_per_step": d2h / args.steps, "seconds": dt,
+               "note": "Learner(host arrays): H2D of 72 B/residue, K3 thresholds+binning, residue tokens, K merges, D2H of segmentation + merge events"}
+        del L2
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu = reference_arm(args)
+    if rank != 0:
+        return
+    line = {
+        "metric": "bpe_merge_iters_per_s", "value": args.steps / (ms * 1e-3), "unit": "merge_iters/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u64" if args.mode == "H" else "f64", "data": "synthetic",
+        "config": {"workload": f"BASELINE configs[1]: {args.backbones} backbones x {args.residues} residues per GPU "
+                               f"({R} residues), {'histogram' if args.mode == 'H' else 'medoid'} quantisation, bins {hp['bins'][1]}, "
+                               f"{args.steps} merges after {args.warmup} warm-up merges",
+                   "mode": args.mode, "l2": "inputs (token arrays 41 MB + table) smaller than L2 at this config; "
+                                            "the at-scale probe uses 48 M tokens (768 MB) > L2",
+                   "live_tokens_start": T_start, "live_tokens_end": T_end, "distinct_keys": distinct,
+                   "pairs": pairs, "distinct_over_pairs": distinct / max(pairs, 1), "last_top_count": top,
+                   "residues_total": R * world},
+        "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
+        "roofline": {"bound": "hbm", "kernel": "k_pair_count<KeysH>" if args.mode == "H" else "k_pair_count<KeysM>",
+                     "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "avg_ms": k1_avg_ms, "algorithmic_bytes_per_launch": k1_bytes,
+                     "bytes_per_token": bpt, "share_of_step": k1_share},
+        "roofline_at_scale": scale, "cpu_baseline": cpu,
+    }
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

@@ -47,7 +47,10 @@ SIGNATURES = {
 _RESTYPES = {"gb_last_error": C.c_char_p, "gb_select_scratch_elems": I64}
 
 _lib = None
-launches = 0  # number of C-ABI calls that launched kernels (bench.py reports it)
+launches = 0  # kernels launched through the C ABI (bench.py reports it)
+# kernels per entry point (default 1)
+KERNELS = {"gb_select_flagged": 3, "gb_select_eq_u64": 3, "gb_merge_compact": 3, "gb_table_argmax": 2,
+           "gb_col_minmax": 3}
 
 
 def load():
@@ -83,7 +86,7 @@ def call(name, *args):
     global launches
     lib = load()
     rc = getattr(lib, name)(*args, stream())
-    launches += 1
+    launches += KERNELS.get(name, 1)
     if rc != 0:
         raise RuntimeError(f"{name} failed ({rc}): {lib.gb_last_error().decode()}")
 

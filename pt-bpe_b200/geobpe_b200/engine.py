@@ -309,6 +309,7 @@ class Learner:
         self.bb = Backbones(vals, offsets)
         self.vals_host = np.ascontiguousarray(vals, dtype=np.float64)
         self.sphere_n = {}
+        self.k1_events = None
         self._peek = None
         self.th = Thresholds(self.bb, self.bins, bin_strategy, std_bonds)
         self.table = PairTable()
@@ -442,6 +443,15 @@ class Learner:
         else:
             def launch(tab):
                 _lib.call("gb_pair_count_m", ts.p("cls"), ts.p("glue"), ts.T, *tab.ptrs(), _lib.ptr(tab.overflow))
+        if self.k1_events is not None:          # bench.py: CUDA events around the K1 launch on its own stream
+            inner = launch
+
+            def launch(tab):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                inner(tab)
+                e1.record()
+                self.k1_events.append((e0, e1, ts.T))
         return self.table.count(launch, ts.T)
 
     def step_h(self):
