@@ -86,7 +86,17 @@ int gb_pair_count_m(const uint32_t* cls, const uint32_t* glue, int64_t T, uint64
 int gb_pair_count_h(const uint64_t* hsh, const uint32_t* glue, const uint32_t* len, int64_t T,
                     const uint64_t* powtab, uint64_t P, uint64_t* tkeys, uint32_t* tcnt,
                     uint32_t* tmin, int64_t M, int32_t* overflow, void* stream);
-/* generic: histogram of an explicit key array (residue-token interning, bpe.py:243-247) */
+/* pair_count_* only fill keys and counts (one RED per distinct key per CTA).  The first position of every key tied
+ * at the max is found afterwards by gb_first_positions_* (reads max / tie list from the device buffers written by
+ * gb_table_argmax, so no host round trip lies between): tie_minpos[i] = lowest j whose pair (j,j+1) has key tie_keys[i] */
+int gb_first_positions_m(const uint32_t* cls, const uint32_t* glue, int64_t T, const uint64_t* tkeys,
+                         const uint32_t* tcnt, uint32_t* tmin, int64_t M, const uint32_t* out4,
+                         const uint64_t* tie_keys, uint32_t* tie_minpos, int cap, void* stream);
+int gb_first_positions_h(const uint64_t* hsh, const uint32_t* glue, const uint32_t* len, int64_t T,
+                         const uint64_t* powtab, uint64_t P, const uint64_t* tkeys, const uint32_t* tcnt,
+                         uint32_t* tmin, int64_t M, const uint32_t* out4, const uint64_t* tie_keys,
+                         uint32_t* tie_minpos, int cap, void* stream);
+/* generic: histogram of an explicit key array with first positions (residue-token interning, bpe.py:243-247) */
 int gb_key_count(const uint64_t* keys, int64_t n, uint64_t* tkeys, uint32_t* tcnt, uint32_t* tmin,
                  int64_t M, int32_t* overflow, void* stream);
 /* out u32 [4]: {max count, number of keys tied at max, distinct keys, 0}; ties (first `cap`) in

@@ -22,6 +22,8 @@ SIGNATURES = {
     "gb_table_clear": [P, P, P, I64, P],
     "gb_pair_count_m": [P, P, I64, P, P, P, I64, P, P],
     "gb_pair_count_h": [P, P, P, I64, P, U64, P, P, P, I64, P, P],
+    "gb_first_positions_m": [P, P, I64, P, P, P, I64, P, P, P, I32, P],
+    "gb_first_positions_h": [P, P, P, I64, P, U64, P, P, P, I64, P, P, P, I32, P],
     "gb_key_count": [P, I64, P, P, P, I64, P, P],
     "gb_table_argmax": [P, P, P, I64, P, P, P, I32, P],
     "gb_table_lookup": [P, P, P, I64, P, I32, P, P, P],
@@ -50,7 +52,7 @@ _lib = None
 launches = 0  # kernels launched through the C ABI (bench.py reports it)
 # kernels per entry point (default 1)
 KERNELS = {"gb_select_flagged": 3, "gb_select_eq_u64": 3, "gb_merge_compact": 3, "gb_table_argmax": 2,
-           "gb_col_minmax": 3}
+           "gb_col_minmax": 3, "gb_first_positions_m": 2, "gb_first_positions_h": 2}
 
 
 def load():

@@ -10,62 +10,44 @@
 #define K1_THREADS 512
 #define K1_VEC 4
 #define K1_TILE (K1_THREADS * K1_VEC)
-#define K1_SLOTS 4096           // shared-memory table slots per CTA (64 KB)
-#define K1_SPROBES 12
-#define K1_FLUSH_AT ((K1_SLOTS * 5) / 8)
+#define K1_SLOTS 8192           // direct-mapped shared-memory cache per CTA: u64 key + u32 count = 96 KB
 
-struct STable {
-  u64* k; u32* c; u32* m; u32* n_used;
-};
+struct GTable { u64* k; u32* c; u64 mask; int32_t* overflow; };
 
-__device__ __forceinline__ void stable_reset(const STable& s) {
-  for (int i = threadIdx.x; i < K1_SLOTS; i += blockDim.x) { s.k[i] = GB_EMPTY_KEY; s.c[i] = 0; s.m[i] = 0xFFFFFFFFu; }
-  if (threadIdx.x == 0) *s.n_used = 0;
-}
-
-__device__ __forceinline__ bool stable_add(const STable& s, u64 key, u32 c, u32 mn) {
-  u32 slot = (u32)(gb_mix64(key) >> 20) & (K1_SLOTS - 1);
+// count-only insertion into the global (L2-resident) table: plain load first, CAS only on an empty slot,
+// then one RED on the count
+__device__ __forceinline__ void gtable_count(const GTable& g, u64 key, u32 c) {
+  u64 s = gb_mix64(key) & g.mask;
 #pragma unroll 1
-  for (int p = 0; p < K1_SPROBES; ++p) {
-    u64 prev = s.k[slot];
-    if (prev == GB_EMPTY_KEY) {
-      prev = atomicCAS(&s.k[slot], (u64)GB_EMPTY_KEY, key);
-      if (prev == GB_EMPTY_KEY) atomicAdd(s.n_used, 1u);
-    }
-    if (prev == GB_EMPTY_KEY || prev == key) {
-      atomicAdd(&s.c[slot], c);
-      atomicMin(&s.m[slot], mn);
-      return true;
-    }
-    slot = (slot + 1) & (K1_SLOTS - 1);
+  for (int probe = 0; probe < GB_MAX_PROBES; ++probe) {
+    u64 prev = __ldcg(g.k + s);
+    if (prev == GB_EMPTY_KEY) prev = atomicCAS(g.k + s, (u64)GB_EMPTY_KEY, key);
+    if (prev == GB_EMPTY_KEY || prev == key) { atomicAdd(g.c + s, c); return; }
+    s = (s + 1) & g.mask;
   }
-  return false;
+  atomicExch(g.overflow, 1);
 }
 
-struct GTable { u64* k; u32* c; u32* m; u64 mask; int32_t* overflow; };
+struct SCache { u64* k; u32* c; };
 
-__device__ __forceinline__ void stable_flush(const STable& s, const GTable& g) {
-  for (int i = threadIdx.x; i < K1_SLOTS; i += blockDim.x) {
-    u64 key = s.k[i];
-    if (key != GB_EMPTY_KEY) {
-      if (!gb_gtable_add(g.k, g.c, g.m, g.mask, key, s.c[i], s.m[i])) atomicExch(g.overflow, 1);
-      s.k[i] = GB_EMPTY_KEY; s.c[i] = 0; s.m[i] = 0xFFFFFFFFu;
-    }
-  }
-  if (threadIdx.x == 0) *s.n_used = 0;
+// direct-mapped, first-come: a key that finds its slot taken by another key goes straight to the global table
+// (no probing -> no divergent probe loops; hot keys claim their slots early and absorb their repeats)
+__device__ __forceinline__ void scache_count(const SCache& s, const GTable& g, u64 key, u32 c) {
+  u32 slot = (u32)(gb_mix64(key) >> 24) & (K1_SLOTS - 1);
+  u64 prev = s.k[slot];
+  if (prev == GB_EMPTY_KEY) prev = atomicCAS(&s.k[slot], (u64)GB_EMPTY_KEY, key);
+  if (prev == GB_EMPTY_KEY || prev == key) atomicAdd(&s.c[slot], c);
+  else gtable_count(g, key, c);
 }
 
-// warp-aggregated add of one key per lane (key == EMPTY -> lane does not contribute)
-__device__ __forceinline__ void warp_agg_add(const STable& s, const GTable& g, u64 key, u32 pos) {
+// warp-aggregated count of one key per lane (key == EMPTY -> lane does not contribute)
+template <bool USE_SMEM>
+__device__ __forceinline__ void warp_agg_count(const SCache& s, const GTable& g, u64 key) {
   unsigned grp = __match_any_sync(0xffffffffu, key);
-  if (key != GB_EMPTY_KEY) {
-    unsigned lane = threadIdx.x & 31;
-    if ((unsigned)(__ffs(grp) - 1) == lane) {  // lowest lane of the group holds the lowest position
-      u32 c = __popc(grp);
-      if (!stable_add(s, key, c, pos)) {
-        if (!gb_gtable_add(g.k, g.c, g.m, g.mask, key, c, pos)) atomicExch(g.overflow, 1);
-      }
-    }
+  if (key != GB_EMPTY_KEY && (unsigned)(__ffs(grp) - 1) == (threadIdx.x & 31)) {
+    u32 c = __popc(grp);
+    if (USE_SMEM) scache_count(s, g, key, c);
+    else gtable_count(g, key, c);
   }
 }
 
@@ -144,48 +126,50 @@ struct KeysArr {
   }
 };
 
-template <class KF>
+template <class KF, bool USE_SMEM>
 __global__ void __launch_bounds__(K1_THREADS, 2) k_pair_count(KF kf, i64 T, GTable g) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  STable s;
+  SCache s;
   s.k = reinterpret_cast<u64*>(smem_raw);
   s.c = reinterpret_cast<u32*>(smem_raw + sizeof(u64) * K1_SLOTS);
-  s.m = s.c + K1_SLOTS;
-  s.n_used = s.m + K1_SLOTS;
-  stable_reset(s);
-  __syncthreads();
+  if (USE_SMEM) {
+    for (int i = threadIdx.x; i < K1_SLOTS; i += blockDim.x) { s.k[i] = GB_EMPTY_KEY; s.c[i] = 0; }
+    __syncthreads();
+  }
   for (i64 base = (i64)blockIdx.x * K1_TILE; base < T; base += (i64)gridDim.x * K1_TILE) {
     i64 j0 = base + (i64)threadIdx.x * K1_VEC;
     u64 key[K1_VEC];
     kf.keys(j0, T, key);
 #pragma unroll
-    for (int e = 0; e < K1_VEC; ++e) warp_agg_add(s, g, key[e], (u32)(j0 + e));
-    __syncthreads();
-    if (*s.n_used > K1_FLUSH_AT) {   // uniform across the block (read after the barrier)
-      __syncthreads();
-      stable_flush(s, g);
-    }
-    __syncthreads();
+    for (int e = 0; e < K1_VEC; ++e) warp_agg_count<USE_SMEM>(s, g, key[e]);
   }
-  stable_flush(s, g);
+  if (USE_SMEM) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < K1_SLOTS; i += blockDim.x) {
+      u64 key = s.k[i];
+      if (key != GB_EMPTY_KEY) gtable_count(g, key, s.c[i]);
+    }
+  }
 }
 
-static const size_t K1_SMEM = sizeof(u64) * K1_SLOTS + sizeof(u32) * K1_SLOTS * 2 + 16;
+static const size_t K1_SMEM = (sizeof(u64) + sizeof(u32)) * K1_SLOTS;
+#define K1_SMEM_MIN_PER_CTA 32768   // pairs per CTA below which the shared cache only adds a flush
 
 template <class KF>
-static int launch_pair_count(KF kf, i64 T, i64 min_T, u64* tkeys, u32* tcnt, u32* tmin, i64 M, int32_t* overflow, cudaStream_t st) {
+static int launch_pair_count(KF kf, i64 T, i64 min_T, u64* tkeys, u32* tcnt, i64 M, int32_t* overflow, cudaStream_t st) {
   if (M <= 0 || (M & (M - 1))) { gb_set_error("pair_count: table size %lld is not a power of two", (long long)M); return -2; }
   if (T < min_T) return 0;
   static bool attr_set = false;
   if (!attr_set) {
-    GB_CK(cudaFuncSetAttribute(k_pair_count<KF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K1_SMEM));
+    GB_CK(cudaFuncSetAttribute(k_pair_count<KF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K1_SMEM));
     attr_set = true;
   }
   int sms = gb_sm_count();
   if (sms <= 0) sms = 148;
   int blocks = gb_blocks_for(T, K1_TILE, sms * 2);   // persistent: 2 CTAs per SM
-  GTable g{tkeys, tcnt, tmin, (u64)(M - 1), overflow};
-  k_pair_count<KF><<<blocks, K1_THREADS, K1_SMEM, st>>>(kf, T, g);
+  GTable g{tkeys, tcnt, (u64)(M - 1), overflow};
+  if (T / blocks >= K1_SMEM_MIN_PER_CTA) k_pair_count<KF, true><<<blocks, K1_THREADS, K1_SMEM, st>>>(kf, T, g);
+  else k_pair_count<KF, false><<<blocks, K1_THREADS, 0, st>>>(kf, T, g);
   GB_LAUNCH_CK();
   return 0;
 }
@@ -193,18 +177,106 @@ static int launch_pair_count(KF kf, i64 T, i64 min_T, u64* tkeys, u32* tcnt, u32
 extern "C" int gb_pair_count_m(const uint32_t* cls, const uint32_t* glue, int64_t T, uint64_t* tkeys,
                                uint32_t* tcnt, uint32_t* tmin, int64_t M, int32_t* overflow, void* stream) {
   KeysM kf{cls, glue};
-  return launch_pair_count(kf, (i64)T, 2, (u64*)tkeys, tcnt, tmin, (i64)M, overflow, (cudaStream_t)stream);
+  return launch_pair_count(kf, (i64)T, 2, (u64*)tkeys, tcnt, (i64)M, overflow, (cudaStream_t)stream);
 }
 extern "C" int gb_pair_count_h(const uint64_t* hsh, const uint32_t* glue, const uint32_t* len, int64_t T,
                                const uint64_t* powtab, uint64_t P, uint64_t* tkeys, uint32_t* tcnt,
                                uint32_t* tmin, int64_t M, int32_t* overflow, void* stream) {
   KeysH kf{(const u64*)hsh, glue, len, (const u64*)powtab, (u64)P};
-  return launch_pair_count(kf, (i64)T, 2, (u64*)tkeys, tcnt, tmin, (i64)M, overflow, (cudaStream_t)stream);
+  return launch_pair_count(kf, (i64)T, 2, (u64*)tkeys, tcnt, (i64)M, overflow, (cudaStream_t)stream);
+}
+__global__ void __launch_bounds__(256) k_key_count_min(const u64* __restrict__ keys, i64 n, u64* tk, u32* tc, u32* tm,
+                                                        u64 mask, int32_t* overflow) {
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x)
+    if (!gb_gtable_add(tk, tc, tm, mask, keys[i], 1u, (u32)i)) atomicExch(overflow, 1);
 }
 extern "C" int gb_key_count(const uint64_t* keys, int64_t n, uint64_t* tkeys, uint32_t* tcnt, uint32_t* tmin,
                             int64_t M, int32_t* overflow, void* stream) {
-  KeysArr kf{(const u64*)keys};
-  return launch_pair_count(kf, (i64)n, 1, (u64*)tkeys, tcnt, tmin, (i64)M, overflow, (cudaStream_t)stream);
+  if (M <= 0 || (M & (M - 1))) { gb_set_error("gb_key_count: table size is not a power of two"); return -2; }
+  if (n <= 0) return 0;
+  k_key_count_min<<<gb_blocks_for(n, 256 * 4, 148 * 8), 256, 0, (cudaStream_t)stream>>>((const u64*)keys, n, (u64*)tkeys,
+                                                                                      tcnt, tmin, (u64)(M - 1), overflow);
+  GB_LAUNCH_CK();
+  return 0;
+}
+
+// ---- first position of every key tied at the max (example occurrence for the host's json tie-break) ----
+#define FP_LIST 64
+template <class KF>
+__global__ void __launch_bounds__(K1_THREADS) k_first_pos(KF kf, i64 T, const u64* __restrict__ tk, const u32* __restrict__ tc,
+                                                          u32* __restrict__ tm, u64 mask, const u32* __restrict__ out4,
+                                                          const u64* __restrict__ tie_keys, u32* __restrict__ tie_min) {
+  __shared__ u64 lk[FP_LIST];
+  const u32 mx = out4[0], nt = out4[1];
+  if (mx == 0 || nt == 0) return;
+  const bool small = nt <= FP_LIST;
+  if (small && threadIdx.x < nt) lk[threadIdx.x] = tie_keys[threadIdx.x];
+  __syncthreads();
+  for (i64 base = (i64)blockIdx.x * K1_TILE; base < T; base += (i64)gridDim.x * K1_TILE) {
+    i64 j0 = base + (i64)threadIdx.x * K1_VEC;
+    u64 key[K1_VEC];
+    kf.keys(j0, T, key);
+#pragma unroll
+    for (int e = 0; e < K1_VEC; ++e) {
+      if (key[e] == GB_EMPTY_KEY) continue;
+      if (small) {
+        for (u32 i = 0; i < nt; ++i)
+          if (key[e] == lk[i]) { atomicMin(&tie_min[i], (u32)(j0 + e)); break; }
+      } else {
+        u64 s = gb_mix64(key[e]) & mask;
+        for (int p = 0; p < GB_MAX_PROBES; ++p) {
+          u64 k = tk[s];
+          if (k == key[e]) { if (tc[s] == mx) atomicMin(&tm[s], (u32)(j0 + e)); break; }
+          if (k == GB_EMPTY_KEY) break;
+          s = (s + 1) & mask;
+        }
+      }
+    }
+  }
+}
+__global__ void k_ties_fill(const u64* __restrict__ tk, const u32* __restrict__ tm, u64 mask, const u32* __restrict__ out4,
+                            const u64* __restrict__ tie_keys, u32* __restrict__ tie_min, int cap) {
+  const u32 nt = out4[1];
+  if (nt <= FP_LIST) return;
+  u32 n = nt < (u32)cap ? nt : (u32)cap;
+  for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    u64 key = tie_keys[i];
+    u64 s = gb_mix64(key) & mask;
+    for (int p = 0; p < GB_MAX_PROBES; ++p) {
+      u64 k = tk[s];
+      if (k == key) { tie_min[i] = tm[s]; break; }
+      if (k == GB_EMPTY_KEY) break;
+      s = (s + 1) & mask;
+    }
+  }
+}
+template <class KF>
+static int launch_first_pos(KF kf, i64 T, const u64* tk, const u32* tc, u32* tm, i64 M, const u32* out4, const u64* tie_keys,
+                            u32* tie_min, int cap, cudaStream_t st) {
+  if (T < 2) return 0;
+  int sms = gb_sm_count();
+  if (sms <= 0) sms = 148;
+  int blocks = gb_blocks_for(T, K1_TILE, sms * 2);
+  k_first_pos<KF><<<blocks, K1_THREADS, 0, st>>>(kf, T, tk, tc, tm, (u64)(M - 1), out4, tie_keys, tie_min);
+  GB_LAUNCH_CK();
+  k_ties_fill<<<64, 256, 0, st>>>(tk, tm, (u64)(M - 1), out4, tie_keys, tie_min, cap);
+  GB_LAUNCH_CK();
+  return 0;
+}
+extern "C" int gb_first_positions_m(const uint32_t* cls, const uint32_t* glue, int64_t T, const uint64_t* tkeys,
+                                    const uint32_t* tcnt, uint32_t* tmin, int64_t M, const uint32_t* out4,
+                                    const uint64_t* tie_keys, uint32_t* tie_minpos, int cap, void* stream) {
+  KeysM kf{cls, glue};
+  return launch_first_pos(kf, (i64)T, (const u64*)tkeys, tcnt, tmin, (i64)M, out4, (const u64*)tie_keys, tie_minpos, cap,
+                          (cudaStream_t)stream);
+}
+extern "C" int gb_first_positions_h(const uint64_t* hsh, const uint32_t* glue, const uint32_t* len, int64_t T,
+                                    const uint64_t* powtab, uint64_t P, const uint64_t* tkeys, const uint32_t* tcnt,
+                                    uint32_t* tmin, int64_t M, const uint32_t* out4, const uint64_t* tie_keys,
+                                    uint32_t* tie_minpos, int cap, void* stream) {
+  KeysH kf{(const u64*)hsh, glue, len, (const u64*)powtab, (u64)P};
+  return launch_first_pos(kf, (i64)T, (const u64*)tkeys, tcnt, tmin, (i64)M, out4, (const u64*)tie_keys, tie_minpos, cap,
+                          (cudaStream_t)stream);
 }
 
 // ---- table maintenance ---------------------------------------------------------------------------
@@ -242,7 +314,7 @@ __global__ void __launch_bounds__(256) k_table_ties(const u64* __restrict__ tk, 
   for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (i64)gridDim.x * blockDim.x) {
     if (tc[i] == mx) {
       u32 k = atomicAdd(&out4[1], 1u);
-      if (k < (u32)cap) { tie_keys[k] = tk[i]; tie_min[k] = tm[i]; }
+      if (k < (u32)cap) { tie_keys[k] = tk[i]; tie_min[k] = 0xFFFFFFFFu; }
     }
   }
 }

@@ -205,7 +205,7 @@ class PairTable:
     def ptrs(self):
         return _lib.ptr(self.keys), _lib.ptr(self.cnt), _lib.ptr(self.min), self.M
 
-    def count(self, launch, n_pairs_bound):
+    def count(self, launch, n_pairs_bound, first_pos=None):
         """clear + count (+ retry on overflow with a larger table) + argmax.  `launch(table)` issues the
         count kernel.  Returns (max_count, [(key, minpos)...] tied at the max)."""
         want = 4 * max(self.distinct, 1024) + 4096
@@ -217,6 +217,8 @@ class PairTable:
             launch(self)
             _lib.call("gb_table_argmax", *self.ptrs(), _lib.ptr(self.out4), _lib.ptr(self.tie_keys),
                       _lib.ptr(self.tie_min), self.TIE_CAP)
+            if first_pos is not None:
+                first_pos(self)
             out4 = self.out4.cpu().numpy().astype(np.int64) & 0xFFFFFFFF
             ovf = int(self.overflow.item())
             distinct = int(out4[2])
@@ -443,6 +445,13 @@ class Learner:
         else:
             def launch(tab):
                 _lib.call("gb_pair_count_m", ts.p("cls"), ts.p("glue"), ts.T, *tab.ptrs(), _lib.ptr(tab.overflow))
+        if self.mode == "H":
+            def first_pos(tab):
+                _lib.call("gb_first_positions_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab),
+                          HASH_BASE, *tab.ptrs(), _lib.ptr(tab.out4), _lib.ptr(tab.tie_keys), _lib.ptr(tab.tie_min),
+                          tab.TIE_CAP)
+        else:
+            first_pos = None                    # medoid keys decode to (class, glue, class): no example window needed
         if self.k1_events is not None:          # bench.py: CUDA events around the K1 launch on its own stream
             inner = launch
 
@@ -452,7 +461,7 @@ class Learner:
                 inner(tab)
                 e1.record()
                 self.k1_events.append((e0, e1, ts.T))
-        return self.table.count(launch, ts.T)
+        return self.table.count(launch, ts.T, first_pos)
 
     def step_h(self):
         """one merge iteration, histogram mode (bpe.py:1792-2166 with rmsd_key None)"""
