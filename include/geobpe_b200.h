@@ -67,7 +67,8 @@ int gb_col_hist(const double* vals, int64_t R, int64_t ld, const double* edges, 
  * bond_mode 0: std_bonds (bond bins = 0), 1: free bonds strict, 2: free bonds clamped (strict=False,
  * bpe.py:726-729).  Outputs: rbins u16 [9][R] (GB_NOBIN = absent), glue u32 [R], sym u64 [R]
  * (1 + tau | CA:C:1N<<10 | psi<<20: the histogram-mode residue symbol), status i32 [S]
- * (bit0: value below first bin, bit1: value in no bin -- get_ind's two ValueErrors). */
+ * (glue angles and bonds: bit0 value below first bin, bit1 value in no bin -- get_ind's two ValueErrors;
+ * motif-internal angles tau / CA:C:1N / psi: the same two in bits 2-3). */
 int gb_quantize_residues(const double* vals, int64_t R, int64_t ld, const uint32_t* bb,
                          const int64_t* offsets, int64_t S, const double* edges, int estride,
                          const int* nb_host, int bond_mode, double init_nca, double init_cac,

@@ -103,92 +103,11 @@ class Tokenizer:
     visualize_bonds = visualize
 
 
-class BPE:
-    def __init__(self, structures, bins, bin_strategy="histogram", save_dir=None, compute_sec_structs=False,
-                 plot_iou_with_sec_structs=False, res_init=False, std_bonds=True, rmsd_partition_min_size=4,
-                 rmsd_super_res=False, rmsd_only=False, num_partitions=3, max_num_strucs=500, glue_opt=False,
-                 glue_opt_prior=0.0, glue_opt_every=10, glue_opt_method="all", seed=None):
-        if not res_init:
-            raise NotImplementedError("bond-level tokens (res_init=False) are the legacy path (SURVEY 2 #15)")
-        if glue_opt:
-            raise NotImplementedError("glue optimisation is the 'next' row f-1 of SURVEY 8(f)")
-        if compute_sec_structs:
-            raise NotImplementedError("secondary-structure priority is disabled by encode.sh:28")
-        if rmsd_only:
-            raise NotImplementedError("rmsd_only=True keeps raw geometry (near-unique keys); not built")
-        if rmsd_partition_min_size == INF:
-            self._mode = "H"
-        elif rmsd_partition_min_size <= 2:
-            self._mode = "M"
-        else:
-            raise NotImplementedError("mixed histogram/medoid vocabularies (2 < p_min_size < inf) are not built")
-        self._vals, self._offsets = from_structures(structures)
-        self.tokenizers = [Tokenizer(s, self, i) for i, s in enumerate(structures)]
-        self.compute_sec_structs = compute_sec_structs
-        self.plot_iou_with_sec_structs = plot_iou_with_sec_structs
-        self.rmsd_partition_min_size = rmsd_partition_min_size
-        self.rmsd_super_res = rmsd_super_res
-        self.rmsd_only = rmsd_only
-        self.glue_opt, self.glue_opt_every = glue_opt, glue_opt_every
-        self.glue_opt_prior, self.glue_opt_method = glue_opt_prior, glue_opt_method
-        self.num_partitions = ThresholdDict(num_partitions) if isinstance(num_partitions, dict) else num_partitions
-        self.max_num_strucs = max_num_strucs
-        self.res_init = res_init
-        self.std_bonds = std_bonds
-        self.bins = bins
-        self.bin_strategy = bin_strategy
-        self.n = len(self.tokenizers)
-        self.seed = seed
-        self.rng = np.random.default_rng(seed)         # bpe.py:84
-        self.save_dir = save_dir
-        self._step = 0
-        self._times = []
-        self._ious = []
-        self._learner = None
-        self._export = None
-
-    # ---- bpe.py:91-103 -------------------------------------------------------------------------------
-    def initialize(self, path=None):
-        self._learner = E.Learner(self._vals, self._offsets, self.bins, self.bin_strategy, self.std_bonds,
-                                  mode=self._mode, rmsd_super_res=self.rmsd_super_res,
-                                  num_partitions=self.num_partitions, max_num_strucs=self.max_num_strucs,
-                                  rng=self.rng)
-        L = self._learner
-        self._thresholds = ThresholdDict(L.th.thresholds)
-        self._bin_counts = ThresholdDict(L.th.bin_counts)
-        if self.std_bonds:
-            for i in range(3):
-                self._thresholds[E.BOND_TYPES[i]] = [(E.BOND_LENGTHS[i], E.BOND_LENGTHS[i])]
-        self._tokens = L.tokens
-        if self._mode == "M":
-            self._sphere_dict = L.sphere_dict
-
-    def bin(self):
-        """bpe.py:1431-1474.  Pair counts are recomputed on the device at every step (K1), so there is no
-        persistent _geo_dict to build."""
-        return None
-
-    def step(self):
-        t0 = time.perf_counter()
-        L = self._learner
-        L.step()
-        if self._mode == "M":                          # bpe.py:2164-2166: recurse while the top key is recurring
-            while L.ts.T > L.bb.S and L.peek_m()[2] is not None:
-                L.step()
-        self._step = self._learner.n_steps
-        self._times.append(time.perf_counter() - t0)
-
-    @property
-    def pop_log(self):
-        return self._learner.pop_log
-
-    def glue_opt_all(self):
-        return None
-
-    def visualize(self, *a, **k):
-        return None
-
-    plot_times = plot_iou = visualize
+class _View:
+    """materialises reference-style Python objects from a device-resident engine state (Learner or Inducer)"""
+    _learner = None
+    _export = None
+    _ev_cache = None
 
     # ---- export ---------------------------------------------------------------------------------------
     def _token_arrays(self):
@@ -280,6 +199,8 @@ class BPE:
                 th[i1] = (i1, tok, left[2] + right[2])
         if dict(th) != seg:
             raise RuntimeError(f"merge-event replay and device token arrays disagree for backbone {i}")
+        if getattr(L, "failed", None) is not None and L.failed[i]:
+            raise ValueError("a glue angle of this backbone falls outside the vocabulary's bins (bpe.py:1105-1108)")
         return {"bond_to_token": th, "cur": cur, "init": init}
 
     def _event_arrays(self):
@@ -308,6 +229,94 @@ class BPE:
                     E._lib.ptr(r0), 1, n, 3 * n, None, None, float(f3[0]), float(f3[1]), float(f3[2]), None, None, 0,
                     E._lib.ptr(out))
         return out.view(3 * n, 3).cpu().numpy()
+
+
+class BPE(_View):
+    def __init__(self, structures, bins, bin_strategy="histogram", save_dir=None, compute_sec_structs=False,
+                 plot_iou_with_sec_structs=False, res_init=False, std_bonds=True, rmsd_partition_min_size=4,
+                 rmsd_super_res=False, rmsd_only=False, num_partitions=3, max_num_strucs=500, glue_opt=False,
+                 glue_opt_prior=0.0, glue_opt_every=10, glue_opt_method="all", seed=None):
+        if not res_init:
+            raise NotImplementedError("bond-level tokens (res_init=False) are the legacy path (SURVEY 2 #15)")
+        if glue_opt:
+            raise NotImplementedError("glue optimisation is the 'next' row f-1 of SURVEY 8(f)")
+        if compute_sec_structs:
+            raise NotImplementedError("secondary-structure priority is disabled by encode.sh:28")
+        if rmsd_only:
+            raise NotImplementedError("rmsd_only=True keeps raw geometry (near-unique keys); not built")
+        if rmsd_partition_min_size == INF:
+            self._mode = "H"
+        elif rmsd_partition_min_size <= 2:
+            self._mode = "M"
+        else:
+            raise NotImplementedError("mixed histogram/medoid vocabularies (2 < p_min_size < inf) are not built")
+        self._vals, self._offsets = from_structures(structures)
+        self.tokenizers = [Tokenizer(s, self, i) for i, s in enumerate(structures)]
+        self.compute_sec_structs = compute_sec_structs
+        self.plot_iou_with_sec_structs = plot_iou_with_sec_structs
+        self.rmsd_partition_min_size = rmsd_partition_min_size
+        self.rmsd_super_res = rmsd_super_res
+        self.rmsd_only = rmsd_only
+        self.glue_opt, self.glue_opt_every = glue_opt, glue_opt_every
+        self.glue_opt_prior, self.glue_opt_method = glue_opt_prior, glue_opt_method
+        self.num_partitions = ThresholdDict(num_partitions) if isinstance(num_partitions, dict) else num_partitions
+        self.max_num_strucs = max_num_strucs
+        self.res_init = res_init
+        self.std_bonds = std_bonds
+        self.bins = bins
+        self.bin_strategy = bin_strategy
+        self.n = len(self.tokenizers)
+        self.seed = seed
+        self.rng = np.random.default_rng(seed)         # bpe.py:84
+        self.save_dir = save_dir
+        self._step = 0
+        self._times = []
+        self._ious = []
+        self._learner = None
+        self._export = None
+
+    # ---- bpe.py:91-103 -------------------------------------------------------------------------------
+    def initialize(self, path=None):
+        self._learner = E.Learner(self._vals, self._offsets, self.bins, self.bin_strategy, self.std_bonds,
+                                  mode=self._mode, rmsd_super_res=self.rmsd_super_res,
+                                  num_partitions=self.num_partitions, max_num_strucs=self.max_num_strucs,
+                                  rng=self.rng)
+        L = self._learner
+        self._thresholds = ThresholdDict(L.th.thresholds)
+        self._bin_counts = ThresholdDict(L.th.bin_counts)
+        if self.std_bonds:
+            for i in range(3):
+                self._thresholds[E.BOND_TYPES[i]] = [(E.BOND_LENGTHS[i], E.BOND_LENGTHS[i])]
+        self._tokens = L.tokens
+        if self._mode == "M":
+            self._sphere_dict = L.sphere_dict
+
+    def bin(self):
+        """bpe.py:1431-1474.  Pair counts are recomputed on the device at every step (K1), so there is no
+        persistent _geo_dict to build."""
+        return None
+
+    def step(self):
+        t0 = time.perf_counter()
+        L = self._learner
+        L.step()
+        if self._mode == "M":                          # bpe.py:2164-2166: recurse while the top key is recurring
+            while L.ts.T > L.bb.S and L.peek_m()[2] is not None:
+                L.step()
+        self._step = self._learner.n_steps
+        self._times.append(time.perf_counter() - t0)
+
+    @property
+    def pop_log(self):
+        return self._learner.pop_log
+
+    def glue_opt_all(self):
+        return None
+
+    def visualize(self, *a, **k):
+        return None
+
+    plot_times = plot_iou = visualize
 
     # ---- bpe.py:879-956 -------------------------------------------------------------------------------
     def cum_bin_count(self, key=None):
@@ -340,3 +349,30 @@ class BPE:
                 out.append(len(self._tokens) + self.cum_bin_count(token[1]) +
                            E.get_ind((token[2] + 2 * np.pi) % (2 * np.pi), relv))
         return out
+
+    # ---- induce (bpe.py:1053-1140) -------------------------------------------------------------------
+    def induce(self, structures):
+        """Batched BPE.tokenize: encode held-out structures against this (frozen) vocabulary on the device.
+        Returns (tokenizers, ok) -- tokenizers[i] raises ValueError on access when ok[i] is False, mirroring the
+        reference's get_ind ValueError for out-of-range glue angles."""
+        if not self.res_init or self._mode != "M":
+            raise NotImplementedError("tokenize needs res_init and a medoid-mode vocabulary (bpe.py:1054-1055,1077)")
+        vals, offs = from_structures(structures)
+        ind = E.Inducer(vals, offs, self._tokens, self._sphere_dict, self._thresholds, self.std_bonds,
+                        self.rmsd_super_res)
+        view = _View()
+        view._learner, view._vals, view._mode = ind, vals, "M"
+        view.tokenizers = [Tokenizer(s, view, i) for i, s in enumerate(structures)]
+        return view.tokenizers, ~ind.failed
+
+    def tokenize(self, t):
+        """bpe.py:1053: one structure (Tokenizer built from a structure dict) -> (Tokenizer, metrics)"""
+        toks, ok = self.induce([t._structure])
+        if not ok[0]:
+            raise ValueError("value does not fall into any bin")
+        tk = toks[0]
+        ind = tk._bpe._learner
+        L = [tk.n]
+        for (e0, cnt) in ind.replay:                     # one backbone -> every event of a step belongs to it
+            L.append(L[-1] - cnt)
+        return tk, {"L": L}

@@ -211,12 +211,13 @@ __global__ void __launch_bounds__(256) k_quantize_residues(QArgs a) {
       bins[1] = quant_one(se + 1 * a.estride, a.nb.nb[1], cac, false, clamp, st);
       bins[2] = last ? GB_NOBIN : quant_one(se + 2 * a.estride, a.nb.nb[2], V[0 * ld + r], false, clamp, st);
     }
-    bins[3] = quant_one(se + 3 * a.estride, a.nb.nb[3], tau, true, 0, st);
+    int st2 = 0;   // motif-internal angles (tau, CA:C:1N, psi): reported in bits 2-3 (induce never bins them)
+    bins[3] = quant_one(se + 3 * a.estride, a.nb.nb[3], tau, true, 0, st2);
     if (last) {
       bins[4] = bins[5] = bins[6] = bins[7] = bins[8] = GB_NOBIN;
     } else {
-      bins[4] = quant_one(se + 4 * a.estride, a.nb.nb[4], V[7 * ld + r], true, 0, st);
-      bins[5] = quant_one(se + 5 * a.estride, a.nb.nb[5], V[4 * ld + r], true, 0, st);
+      bins[4] = quant_one(se + 4 * a.estride, a.nb.nb[4], V[7 * ld + r], true, 0, st2);
+      bins[5] = quant_one(se + 5 * a.estride, a.nb.nb[5], V[4 * ld + r], true, 0, st2);
       bins[6] = quant_one(se + 6 * a.estride, a.nb.nb[6], V[5 * ld + r], true, 0, st);
       bins[7] = quant_one(se + 7 * a.estride, a.nb.nb[7], V[8 * ld + r], true, 0, st);
       bins[8] = quant_one(se + 8 * a.estride, a.nb.nb[8], V[3 * ld + r + 1], true, 0, st);
@@ -225,6 +226,7 @@ __global__ void __launch_bounds__(256) k_quantize_residues(QArgs a) {
     for (int k = 0; k < 9; ++k) a.rbins[(i64)k * R + r] = (u16)bins[k];
     a.glue[r] = last ? GB_LAST_FLAG : (bins[6] | (bins[7] << 10) | (bins[8] << 20));
     a.sym[r] = 1ull + (u64)(bins[3] | (bins[4] << 10) | (bins[5] << 20));
+    st |= st2 << 2;
     if (st) atomicOr(&a.status[s], st);
   }
 }

@@ -353,7 +353,7 @@ class Learner:
         self.status_host = st
         if bond_mode != 2 and st.any():
             i = int(np.nonzero(st)[0][0])
-            raise ValueError(f"value {'is below the first bin range' if st[i] & 1 else 'does not fall into any bin'} "
+            raise ValueError(f"value {'is below the first bin range' if st[i] & 5 else 'does not fall into any bin'} "
                              f"(backbone {i})")   # get_ind's ValueErrors, bpe.py:1179-1189
 
     def centre(self, key, b):
@@ -566,9 +566,14 @@ class Learner:
             self._f3_dirty = False
         return self._f3_dev
 
-    def coords(self, r0_dev, Q, nres, A, f3cls_dev):
+    def coords(self, r0_dev, Q, nres, A, f3cls_dev, bond_centres=None):
         out = _empty(Q * A * 3, torch.float64)
         bb = self.bb
+        if bond_centres is not None:       # induce: bond lengths taken quantised (bpe.py:1061,1085)
+            _lib.call("gb_window_coords", _lib.ptr(bb.vals), bb.R, bb.R, _lib.ptr(bb.bb), _lib.ptr(bb.offsets),
+                      _lib.ptr(r0_dev), Q, nres, A, None, None, self.d_f3[0], self.d_f3[1], self.d_f3[2],
+                      _lib.ptr(self.rbins), _lib.ptr(bond_centres), bond_centres.shape[1], _lib.ptr(out))
+            return out.view(Q, A * 3)
         _lib.call("gb_window_coords", _lib.ptr(bb.vals), bb.R, bb.R, _lib.ptr(bb.bb), _lib.ptr(bb.offsets),
                   _lib.ptr(r0_dev), Q, nres, A, _lib.ptr(f3cls_dev) if f3cls_dev is not None else None,
                   _lib.ptr(self.f3tab()) if f3cls_dev is not None else None, self.d_f3[0], self.d_f3[1], self.d_f3[2],
@@ -870,3 +875,144 @@ class Learner:
             self.step_h()
             return False
         return self.step_m()
+
+
+def parse_m_key(key_str):
+    """split a medoid-mode key string (bpe.py:1248-1256) into (left geometry, glue bins, right geometry)"""
+    d = json.loads(key_str)
+    ints = {k: [i for i, v in enumerate(d[k]) if isinstance(v, int)] for k in ("omega", "C:1N:1CA", "phi")}
+    if any(len(v) != 1 for v in ints.values()):
+        raise ValueError("not a medoid-medoid pair key")
+    nl = ints["omega"][0] + 1                     # residues in the left token
+    gl, gr = {}, {}
+    for k, v in d.items():
+        if k in ints:
+            i = ints[k][0]
+            l, r = v[:i], v[i + 1:]
+        else:
+            l, r = v[:nl], v[nl:]
+        if l:
+            gl[k] = l
+        if r:
+            gr[k] = r
+    order = ["N:CA", "CA:C", "0C:1N", "tau", "CA:C:1N", "C:1N:1CA", "psi", "omega", "phi"]
+    gl = {k: gl[k] for k in order if k in gl}
+    gr = {k: gr[k] for k in order if k in gr}
+    glue = (d["omega"][ints["omega"][0]], d["C:1N:1CA"][ints["C:1N:1CA"][0]], d["phi"][ints["phi"][0]])
+    return gl, glue, gr
+
+
+def pack_m_key(cL, glue, cR):
+    om, cn, ph = glue
+    return (cL << 45) | (cR << 27) | (om & 0x1FF) | ((cn & 0x1FF) << 9) | ((ph & 0x1FF) << 18)
+
+
+class Inducer(Learner):
+    """K7: frozen-vocabulary encode of a batch of held-out backbones (BPE.tokenize, bpe.py:1053-1140, with
+    bin_helper 1301-1314 and step_helper 1316-1425), all backbones advanced together merge by merge."""
+
+    def __init__(self, vals, offsets, tokens, sphere_dict, thresholds, std_bonds, rmsd_super_res=True):
+        if std_bonds:
+            raise NotImplementedError("induce is built for free_bonds vocabularies (README setting)")
+        if not rmsd_super_res:
+            raise NotImplementedError("induce is built for rmsd_super_res=True vocabularies")
+        if not all(isinstance(k, tuple) for k in tokens):
+            raise NotImplementedError("BPE.tokenize needs a medoid-mode vocabulary (bpe.py:1077,1117)")
+        self.mode = "M"
+        self.std_bonds = std_bonds
+        self.size0 = 1
+        self.tokens = tokens
+        self.token_keys = list(tokens)
+        self.sphere_dict = sphere_dict
+        self.bb = Backbones(vals, offsets)
+        self.vals_host = np.ascontiguousarray(vals, dtype=np.float64)
+        self.th = Thresholds.__new__(Thresholds)
+        self.th.thresholds = {1: thresholds[1]}
+        self.k1_events = None
+        self.pop_log, self.step_events, self.n_steps = [], [], 0
+        self.class_of, self.class_geo, self.class_f3, self._f3_dirty = {}, [], [], True
+        self.d_f3 = (0.0, 0.0, INIT_TAU)
+        self._quantize(bond_mode=2)
+        R, S = self.bb.R, self.bb.S
+        self.failed = (self.status_host & 3) != 0          # glue angle outside the training range -> ValueError
+        self.ts = TokenState(R, "M")
+        self.ev_left = _empty(R, torch.int32); self.ev_right = _empty(R, torch.int32); self.ev_p = _empty(R, torch.int32)
+        self.ev_n = 0
+        th1 = thresholds[1]
+        B = max(len(th1[k]) for k in BOND_TYPES)
+        bc = np.zeros((3, B))
+        for i, k in enumerate(BOND_TYPES):               # residue-major slots 0,1,2 = N:CA, CA:C, 0C:1N
+            bc[i, :len(th1[k])] = [(a + b) / 2 for a, b in th1[k]]
+        self.bond_centres = torch.from_numpy(bc).to(_dev())
+        tid_of = {k: i for i, k in enumerate(self.token_keys)}
+        ns = sorted(set(k[0] for k in tokens))
+        geo_keys = list(sphere_dict)
+        assert len(ns) == len(geo_keys)
+        # ---- residue tokens (bpe.py:1072-1099): nearest medoid of (0,p) for inner residues, (1,p) for the last one
+        is_last = torch.zeros(R, dtype=torch.bool, device=_dev())
+        is_last[(self.bb.offsets[1:] - 1)] = True
+        lists = {3: torch.nonzero(~is_last).flatten().to(torch.int32), 2: torch.nonzero(is_last).flatten().to(torch.int32)}
+        order = [3, 2] if self.bb.lens_host[0] > 1 else [2, 3]
+        cls_res = _zeros(R, torch.int32); tid_res = _zeros(R, torch.int32)
+        for n, size in enumerate(order):
+            occ = lists[size].contiguous()
+            N = int(occ.numel())
+            if N == 0:
+                continue
+            geos = []
+            p = 0
+            while (n, p) in tokens:
+                geos.append(tokens[(n, p)]); p += 1
+            A = size + 1
+            medc = self.geo_coords(geos, A)
+            allc = self.coords(occ, N, 1, A, None, self.bond_centres)
+            asg = self.assign(allc, medc).to(torch.int64)
+            p2cls = torch.tensor([self.intern_class(g) for g in geos], dtype=torch.int32, device=_dev())
+            p2tid = torch.tensor([tid_of[(n, q)] for q in range(len(geos))], dtype=torch.int32, device=_dev())
+            cls_res[occ.to(torch.int64)] = p2cls[asg]
+            tid_res[occ.to(torch.int64)] = p2tid[asg]
+        ts = self.ts
+        ts.T = R
+        ts.a["cls"][:R] = cls_res
+        ts.a["glue"][:R] = self.glue_res
+        ts.a["pos"][:R] = torch.arange(R, device=_dev(), dtype=torch.int32)
+        ts.a["len"][:R] = 1
+        ts.a["tid"][:R] = tid_res
+        self.init_tid = tid_res.clone()
+        # failed backbones must not take part: cut every one of their pairs (the reference aborts them, bpe.py:1105-1108)
+        if self.failed.any():
+            bad = torch.from_numpy(self.failed).to(_dev())[self.bb.bb.to(torch.int64)]
+            ts.a["glue"][:R] = torch.where(bad, torch.full_like(self.glue_res, -(1 << 31)), self.glue_res)
+        # ---- merge replay in learned order (bpe.py:1116-1139)
+        self.replay = []                     # per vocabulary merge: (event start, event count) -- (0, 0) if it never fired
+        for n, key_str in list(zip(ns, geo_keys))[2:]:
+            self.replay.append((self.ev_n, 0))
+            gl, glue, gr = parse_m_key(key_str)
+            cL, cR = self.class_of.get(json.dumps(gl)), self.class_of.get(json.dumps(gr))
+            geos = sphere_dict[key_str]
+            p2cls = torch.tensor([self.intern_class(g) for g in geos], dtype=torch.int32, device=_dev())
+            if cL is None or cR is None:
+                continue                                   # a constituent motif never occurred -> key not in geo_dict
+            key = pack_m_key(cL, glue, cR)
+            _lib.call("gb_flag_pairs_m", ts.p("cls"), ts.p("glue"), ts.T, key, _lib.ptr(ts.flags))
+            N = ts.select(1, ts.idx)
+            if N == 0:
+                continue
+            nb = lambda g: len(g["N:CA"]) + len(g["CA:C"]) + len(g.get("0C:1N", []))
+            length = nb(gl) + nb(gr)
+            nres, A = (length + 1) // 3, length + 1
+            occ = ts.idx[:N].to(torch.int64)
+            r0 = ts.a["pos"][occ].contiguous(); f3c = ts.a["cls"][occ].contiguous()
+            allc = self.coords(r0, N, nres, A, f3c)
+            medc = self.geo_coords(geos, A)
+            asg = self.assign(allc, medc)
+            _lib.call("gb_scatter_u32", _lib.ptr(ts.idx), _lib.ptr(asg), N, _lib.ptr(ts.aux))
+            tid0 = tid_of[(n, 0)]
+            p2tid = torch.arange(tid0, tid0 + len(geos), dtype=torch.int32, device=_dev())
+            e0 = self.ev_n
+            self._merge(key, n, p2cls, p2tid)
+            self.replay[-1] = (e0, self.ev_n - e0)
+            self.n_steps += 1
+
+    def _oplog(self, nk, p2cls):          # induce needs no occurrence-set order
+        return None

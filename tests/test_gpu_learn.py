@@ -78,3 +78,33 @@ def test_m_mode_vs_oracle_fresh():
         ora.step(); bpe.step()
     assert [list(p) for p in bpe.pop_log] == [list(p) for p in ora.pop_log]
     assert norm(O.dump_state(bpe, max_angles=30)) == norm(O.dump_state(ora, max_angles=30))
+
+
+@pytest.mark.parametrize("name", ["m20", "m6_sub"])
+def test_induce_vs_reference_golden(name):
+    """BPE.tokenize on training and held-out backbones: segmentation, L trace, ids and the set of backbones the
+    reference rejects (glue angle outside the learned bins) must match the reference run."""
+    g = load_golden(name)
+    bpe, strucs = run_learn(g)
+    S2, n2, seed2 = g["induce_gen"]
+    v2, o2 = synthetic.generate(S2, n2, seed=seed2)
+    s2 = synthetic.to_structures(v2, o2)
+    srcs = [strucs[0], strucs[1]] + s2
+    from geobpe_b200.bpe import Tokenizer
+    for src, want in zip(srcs, g["induce"]):
+        try:
+            tk, metrics = bpe.tokenize(Tokenizer(src))
+        except ValueError:
+            assert not want["ok"]
+            continue
+        assert want["ok"]
+        assert norm(list(tk.bond_to_token.values())) == want["segmentation"]
+        assert metrics["L"] == want["L"]
+        assert bpe.quantize(tk) == want["ids"]
+    # batched call: same answers, failures flagged per backbone
+    toks, ok = bpe.induce(srcs)
+    assert [bool(x) for x in ok] == [w["ok"] for w in g["induce"]]
+    for tk, want in zip(toks, g["induce"]):
+        if want["ok"]:
+            assert norm(list(tk.bond_to_token.values())) == want["segmentation"]
+            assert bpe.quantize(tk) == want["ids"]
