@@ -26,9 +26,20 @@ class Tokenizer:
             self.aa = structure.get("aa")
         self._cache_step = None
 
+    # -- pickling: materialise, drop the device-backed owner (ref_tokenizers={t}.pkl, {idx}.pkl, bpe_iter={t}.pkl) ---
+    def __getstate__(self):
+        d = dict(self.__dict__)
+        if d.get("_bpe") is not None and getattr(d["_bpe"], "_learner", None) is not None:
+            d["_mat"] = self._state()
+        d["_bpe"] = None
+        d["_cache_step"] = None
+        return d
+
     # -- materialisation ------------------------------------------------------------------------------
     def _state(self):
         b = self._bpe
+        if b is None and getattr(self, "_mat", None) is not None:
+            return self._mat                           # unpickled: frozen snapshot
         if b is None or b._learner is None:
             raise RuntimeError("Tokenizer is not attached to an initialised BPE")
         key = (id(b._learner), b._learner.n_steps, len(b._learner.pop_log))
@@ -275,6 +286,20 @@ class BPE(_View):
         self._learner = None
         self._export = None
 
+    def __getstate__(self):
+        """pickle layout of encode.py:403-427: vocabulary + hyper-parameters + materialised tokenizers; the device
+        state (HBM buffers) is not part of the pickle"""
+        d = dict(self.__dict__)
+        for k in ("_learner", "_export", "_ev_cache"):
+            d[k] = None
+        return d
+
+    def __setstate__(self, d):
+        self.__dict__.update(d)
+        for t in self.tokenizers:
+            if getattr(t, "_mat", None) is None:
+                t._bpe = self
+
     # ---- bpe.py:91-103 -------------------------------------------------------------------------------
     def initialize(self, path=None):
         self._learner = E.Learner(self._vals, self._offsets, self.bins, self.bin_strategy, self.std_bonds,
@@ -299,6 +324,9 @@ class BPE(_View):
     def step(self):
         t0 = time.perf_counter()
         L = self._learner
+        if L is None:
+            raise RuntimeError("this BPE was unpickled: the device state is gone; resume by re-running initialize() "
+                               "(learning is seconds on the GPU) -- induce/tokenize/quantize work on the pickle as is")
         L.step()
         if self._mode == "M":                          # bpe.py:2164-2166: recurse while the top key is recurring
             while L.ts.T > L.bb.S and L.peek_m()[2] is not None:
@@ -376,3 +404,8 @@ class BPE(_View):
         for (e0, cnt) in ind.replay:                     # one backbone -> every event of a step belongs to it
             L.append(L[-1] - cnt)
         return tk, {"L": L}
+
+
+# pickle class paths of the reference: foldingdiff.bpe.BPE, foldingdiff.tokenizer.Tokenizer
+BPE.__module__ = "foldingdiff.bpe"
+Tokenizer.__module__ = "foldingdiff.tokenizer"

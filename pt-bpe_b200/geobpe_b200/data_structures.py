@@ -112,3 +112,8 @@ class ThresholdDict(dict):
             if i >= 0:
                 return super().__getitem__(self._int_keys[i])
         raise KeyError(key)
+
+
+for _c in (Node, BinaryTreeBuilder, TokenHierarchy, ThresholdDict):
+    _c.__module__ = "foldingdiff.data_structures"
+_rebuild_hierarchy.__module__ = "foldingdiff.data_structures"

@@ -108,3 +108,29 @@ def test_induce_vs_reference_golden(name):
         if want["ok"]:
             assert norm(list(tk.bond_to_token.values())) == want["segmentation"]
             assert bpe.quantize(tk) == want["ids"]
+
+
+def test_pickle_layout_and_induce_from_pickle(tmp_path):
+    """bpe_iter={t}.pkl round trip: class paths resolve under foldingdiff.*, tokenizers keep their segmentation and
+    merge trees, and a loaded vocabulary encodes held-out backbones exactly like the live one."""
+    import pickle
+    import pickletools
+    g = load_golden("m6_sub")
+    bpe, strucs = run_learn(g)
+    path = tmp_path / "bpe_iter=19.pkl"
+    with open(path, "wb") as f:
+        pickle.dump(bpe, f)
+    names = {a for op, a, _ in pickletools.genops(open(path, "rb").read()) if op.name in ("GLOBAL", "STACK_GLOBAL", "SHORT_BINUNICODE") and isinstance(a, str)}
+    assert "foldingdiff.bpe" in names and "foldingdiff.tokenizer" in names and "foldingdiff.data_structures" in names
+    with open(path, "rb") as f:
+        b2 = pickle.load(f)
+    assert norm(list(b2._tokens.items())) == norm(list(bpe._tokens.items()))
+    assert [list(t.bond_to_token.values()) for t in b2.tokenizers] == [list(t.bond_to_token.values()) for t in bpe.tokenizers]
+    assert b2.quantize(b2.tokenizers[0]) == g["final_ids"][0]
+    S2, n2, seed2 = g["induce_gen"]
+    v2, o2 = synthetic.generate(S2, n2, seed=seed2)
+    toks, ok = b2.induce(synthetic.to_structures(v2, o2))
+    for tk, good, want in zip(toks, ok, g["induce"][2:]):
+        assert bool(good) == want["ok"]
+        if good:
+            assert norm(list(tk.bond_to_token.values())) == want["segmentation"]
