@@ -115,6 +115,10 @@ int gb_table_dump(const uint64_t* tkeys, const uint32_t* tcnt, const uint32_t* t
 int gb_table_to_slots(const uint64_t* tkeys, const uint32_t* tcnt, int64_t M, uint32_t* slots,
                       int64_t NS, void* stream);
 
+/* entries of this rank's table whose slot (same hash as gb_table_to_slots) is marked in slotmark u8 [NS] */
+int gb_table_dump_marked(const uint64_t* tkeys, const uint32_t* tcnt, int64_t M, const uint8_t* slotmark,
+                         int64_t NS, uint64_t* out_keys, uint32_t* out_cnt, uint32_t* total, int cap, void* stream);
+
 /* ---- K2: merge (bpe.py:1895-2017) --------------------------------------------------------------- */
 /* flags[j] bit0 = pair (j,j+1) has key `key` */
 int gb_flag_pairs_m(const uint32_t* cls, const uint32_t* glue, int64_t T, uint64_t key, uint8_t* flags,

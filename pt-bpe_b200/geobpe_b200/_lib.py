@@ -29,6 +29,7 @@ SIGNATURES = {
     "gb_table_lookup": [P, P, P, I64, P, I32, P, P, P],
     "gb_table_dump": [P, P, P, I64, P, P, P, P, P],
     "gb_table_to_slots": [P, P, I64, P, I64, P],
+    "gb_table_dump_marked": [P, P, I64, P, I64, P, P, P, I32, P],
     "gb_flag_pairs_m": [P, P, I64, U64, P, P],
     "gb_flag_pairs_h": [P, P, P, I64, P, U64, U64, P, P],
     "gb_resolve_overlaps": [P, I64, P],

@@ -395,3 +395,31 @@ extern "C" int gb_table_to_slots(const uint64_t* tkeys, const uint32_t* tcnt, in
   GB_LAUNCH_CK();
   return 0;
 }
+
+// multi-GPU: this rank's (key, count) entries whose direct-mapped slot is marked (top slots after the allreduce)
+__global__ void __launch_bounds__(256) k_table_dump_marked(const u64* __restrict__ tk, const u32* __restrict__ tc, i64 M,
+                                                            const u8* __restrict__ mark, u64 smask, u64* __restrict__ ok,
+                                                            u32* __restrict__ oc, u32* __restrict__ total, u32 cap) {
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (i64)gridDim.x * blockDim.x) {
+    u32 c = tc[i];
+    if (c) {
+      u64 key = tk[i];
+      if (mark[gb_mix64(key ^ 0x9E3779B97F4A7C15ull) & smask]) {
+        u32 k = atomicAdd(total, 1u);
+        if (k < cap) { ok[k] = key; oc[k] = c; }
+      }
+    }
+  }
+}
+extern "C" int gb_table_dump_marked(const uint64_t* tkeys, const uint32_t* tcnt, int64_t M, const uint8_t* slotmark,
+                                    int64_t NS, uint64_t* out_keys, uint32_t* out_cnt, uint32_t* total, int cap,
+                                    void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (NS <= 0 || (NS & (NS - 1))) { gb_set_error("gb_table_dump_marked: NS must be a power of two"); return -2; }
+  GB_CK(cudaMemsetAsync(total, 0, sizeof(u32), st));
+  if (M <= 0) return 0;
+  k_table_dump_marked<<<gb_blocks_for(M, 256 * 4, 148 * 8), 256, 0, st>>>((const u64*)tkeys, tcnt, M, slotmark, (u64)(NS - 1),
+                                                                          (u64*)out_keys, out_cnt, total, (u32)cap);
+  GB_LAUNCH_CK();
+  return 0;
+}

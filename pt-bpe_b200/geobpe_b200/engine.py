@@ -105,7 +105,7 @@ class Backbones:
 class Thresholds:
     """K3 driver: bpe.py:820-876 _init_thresholds + plotting.py:305-337 save_histogram."""
 
-    def __init__(self, bb, bins, bin_strategy, std_bonds):
+    def __init__(self, bb, bins, bin_strategy, std_bonds, comm=None):
         self.keys = BOND_ANGLES + DIHEDRAL_ANGLES + ([] if std_bonds else BOND_TYPES)
         self.std_bonds = std_bonds
         self.thresholds = {}
@@ -114,6 +114,16 @@ class Thresholds:
         mm = _empty(18, torch.float64)
         cnt = _empty(9, torch.int64)
         _lib.call("gb_col_minmax", _lib.ptr(bb.vals), R, R, _lib.ptr(mm), _lib.ptr(cnt))
+        S_total = S
+        if comm is not None and comm.world > 1:      # global min / max / backbone count
+            if bin_strategy == "uniform":
+                raise NotImplementedError("quantile edges need all values on one rank; use bin_strategy=histogram")
+            mm2 = mm.view(9, 2)
+            lo, hi = mm2[:, 0].contiguous(), mm2[:, 1].contiguous()
+            comm.all_reduce(lo, "min"); comm.all_reduce(hi, "max")
+            mm = torch.stack([lo, hi], dim=1).contiguous()
+            st = torch.tensor([S], dtype=torch.int64, device=_dev())
+            S_total = int(comm.all_reduce(st, "sum").item())
         mm = mm.cpu().numpy().reshape(9, 2)
         consts = {"tau": INIT_TAU, "N:CA": INIT_N_CA, "CA:C": INIT_CA_C}
         host_cols = None
@@ -155,6 +165,8 @@ class Thresholds:
             counts = _empty(9 * estride, torch.int64)
             _lib.load().gb_col_hist  # (prototype check)
             _lib.call("gb_col_hist", _lib.ptr(bb.vals), R, R, _lib.ptr(e_dev), estride, nb, _lib.ptr(counts))
+            if comm is not None and comm.world > 1:
+                comm.all_reduce(counts, "sum")
             counts = counts.cpu().numpy().reshape(9, estride)
             th, bc = {}, {}
             for key in self.keys:
@@ -164,7 +176,7 @@ class Thresholds:
                 if key in consts:
                     circ = key not in BOND_TYPES
                     c = (consts[key] + TWO_PI) % TWO_PI if circ else consts[key]
-                    cts[get_ind(c, th[key])] += S
+                    cts[get_ind(c, th[key])] += S_total
                 bc[key] = [int(x) for x in cts]
             self.thresholds[size] = th
             self.bin_counts[size] = bc
@@ -291,7 +303,11 @@ class Learner:
     """
 
     def __init__(self, vals, offsets, bins, bin_strategy="histogram", std_bonds=True, mode="H",
-                 rmsd_super_res=True, num_partitions=3, max_num_strucs=500, rng=None, verify=True):
+                 rmsd_super_res=True, num_partitions=3, max_num_strucs=500, rng=None, verify=True, comm=None):
+        self.comm = comm if (comm is not None and comm.world > 1) else None
+        if self.comm is not None and mode != "H":
+            raise NotImplementedError("multi-GPU medoid mode needs the sampled windows gathered in set order "
+                                      "(SURVEY 8e row 3); histogram mode is distributed this round")
         if len(bins) != 1:
             raise NotImplementedError("size-bucketed --bins (more than one bucket) is not built yet: keys would "
                                       "need re-quantisation per bucket (SURVEY 7.2 hard part 2)")
@@ -313,7 +329,7 @@ class Learner:
         self.sphere_n = {}
         self.k1_events = None
         self._peek = None
-        self.th = Thresholds(self.bb, self.bins, bin_strategy, std_bonds)
+        self.th = Thresholds(self.bb, self.bins, bin_strategy, std_bonds, self.comm)
         self.table = PairTable()
         self.tokens = {}            # BPE._tokens
         self.pop_log = []           # (count, key string) per popped key
@@ -388,6 +404,14 @@ class Learner:
         firsts = _u32(om[:n])
         order = np.argsort(firsts, kind="stable")
         syms, firsts = syms[order], firsts[order]
+        if self.comm is not None:        # global first-seen order = (rank, local first position) (bpe.py:243-247)
+            seen, gs = set(), []
+            for part in self.comm.all_gather_object(syms.tolist()):
+                for x in part:
+                    if x not in seen:
+                        seen.add(x); gs.append(x)
+            syms = np.array(gs, dtype=np.int64)
+            firsts = np.zeros(len(gs), dtype=np.int64)
         # ids in first-seen order; per-residue id by binary search over the sorted distinct symbols
         sort2 = np.argsort(syms)
         sorted_syms = torch.from_numpy(syms[sort2]).to(_dev())
@@ -411,6 +435,8 @@ class Learner:
         ts.a["tid"][:R] = tid
         self.init_tid = tid.clone()
         maxlen = int(self.bb.lens_host.max()) if self.bb.S else 1
+        if self.comm is not None:
+            maxlen = int(self.comm.all_reduce(torch.tensor([maxlen], device=_dev()), "max").item())
         pw = [1]
         for _ in range(2 * maxlen + 2):
             pw.append(pw[-1] * HASH_BASE % P61)
@@ -461,11 +487,26 @@ class Learner:
                 inner(tab)
                 e1.record()
                 self.k1_events.append((e0, e1, ts.T))
+        self._k1_launch_fn = launch
         return self.table.count(launch, ts.T, first_pos)
+
+    def _k1_launch(self, tab):
+        ts = self.ts
+        e = self.k1_events
+        if e is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        _lib.call("gb_pair_count_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab),
+                  HASH_BASE, *tab.ptrs(), _lib.ptr(tab.overflow))
+        if e is not None:
+            e1.record()
+            e.append((e0, e1, ts.T))
 
     def step_h(self):
         """one merge iteration, histogram mode (bpe.py:1792-2166 with rmsd_key None)"""
         ts = self.ts
+        if self.comm is not None:
+            return self._step_h_dist()
         mx, ties = self._count_pairs()
         if mx == 0:
             raise IndexError("no adjacent pairs left (the reference's peekitem(0) raises here too)")
@@ -489,6 +530,81 @@ class Learner:
                       self.bb.R, r0, nres, _lib.ptr(ts.u32))
             if int(ts.u32[0].item()):
                 raise RuntimeError("61-bit content-hash collision detected (window bins differ); re-run with another HASH_BASE")
+        self._merge(key, n, None, None)
+        self.n_steps += 1
+
+    NS = 1 << 20      # direct-mapped slot counters exchanged per iteration (4 MB allreduce)
+
+    def _step_h_dist(self):
+        """histogram-mode merge iteration on a shard: local K1 -> slot allreduce -> exact top keys -> local K2"""
+        from .distributed import global_top
+        ts, tab, comm = self.ts, self.table, self.comm
+        want = 4 * max(tab.distinct, 1024) + 4096
+        tab.ensure(2 * ts.T if tab.M == 0 else max(want, 1 << 12))
+        while True:
+            _lib.call("gb_table_clear", *tab.ptrs())
+            tab.overflow.zero_()
+            self._k1_launch(tab)
+            _lib.call("gb_table_argmax", *tab.ptrs(), _lib.ptr(tab.out4), _lib.ptr(tab.tie_keys), _lib.ptr(tab.tie_min),
+                      tab.TIE_CAP)
+            out4 = _u32(tab.out4)
+            if int(tab.overflow.item()) or int(out4[2]) * 2 > tab.M:
+                tab.ensure(tab.M * 4)
+                continue
+            tab.distinct = int(out4[2])
+            break
+        if not hasattr(self, "_slots"):
+            self._slots = _zeros(self.NS, torch.int32)
+            self._mark = _zeros(self.NS, torch.uint8)
+            self._ck = _empty(1 << 14, torch.int64); self._cc = _empty(1 << 14, torch.int32)
+        _lib.call("gb_table_to_slots", _lib.ptr(tab.keys), _lib.ptr(tab.cnt), tab.M, _lib.ptr(self._slots), self.NS)
+
+        def cand(sel):
+            self._mark.zero_()
+            self._mark[torch.from_numpy(sel).to(_dev())] = 1
+            _lib.call("gb_table_dump_marked", _lib.ptr(tab.keys), _lib.ptr(tab.cnt), tab.M, _lib.ptr(self._mark), self.NS,
+                      _lib.ptr(self._ck), _lib.ptr(self._cc), _lib.ptr(ts.u32), 1 << 14)
+            n = int(ts.u32[0].item())
+            if n > (1 << 14):
+                raise RuntimeError("too many local keys in the top slots")
+            return self._ck[:n].cpu().numpy(), _u32(self._cc[:n])
+        mx, tied = global_top(comm, self._slots, cand, _dev())
+        if mx == 0:
+            raise IndexError("no adjacent pairs left")
+        keys = sorted(tied)
+        # example window of every tied key this rank holds (chunks of 64 = the list path of k_first_pos)
+        local = {}
+        for c0 in range(0, len(keys), 64):
+            ch = keys[c0:c0 + 64]
+            tab.tie_keys[:len(ch)] = torch.tensor(ch, dtype=torch.int64, device=_dev())
+            tab.tie_min[:len(ch)] = -1
+            tab.out4.copy_(torch.tensor([mx, len(ch), 0, 0], dtype=torch.int32))
+            _lib.call("gb_first_positions_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab),
+                      HASH_BASE, *tab.ptrs(), _lib.ptr(tab.out4), _lib.ptr(tab.tie_keys), _lib.ptr(tab.tie_min), tab.TIE_CAP)
+            mp = _u32(tab.tie_min[:len(ch)])
+            have = [(k, int(m)) for k, m in zip(ch, mp.tolist()) if m != 0xFFFFFFFF]
+            if have:
+                mins = torch.tensor([m for _, m in have], device=_dev(), dtype=torch.int64)
+                p0 = _u32(ts.a["pos"][mins]); nr = (_u32(ts.a["len"][mins]) + _u32(ts.a["len"][mins + 1])).tolist()
+                for (k, _), d, r0, n_ in zip(have, self._h_key_dicts(p0.tolist(), nr), p0.tolist(), nr):
+                    local[k] = (json.dumps(d, sort_keys=True), r0, n_)
+        strings = {}
+        for part in comm.all_gather_object({k: v[0] for k, v in local.items()}):
+            for k, v in part.items():
+                if strings.setdefault(k, v) != v:
+                    raise RuntimeError("61-bit content-hash collision across ranks (window bins differ)")
+        key_str, key = min((strings[k], k) for k in keys)
+        n = len(self.tokens)
+        self.tokens[n] = json.loads(key_str)
+        self.pop_log.append((mx, key_str))
+        _lib.call("gb_flag_pairs_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), HASH_BASE,
+                  key, _lib.ptr(ts.flags))
+        if self.verify and key in local:
+            nocc = ts.select(1, ts.idx)
+            _lib.call("gb_verify_windows_h", _lib.ptr(ts.idx), nocc, ts.p("pos"), ts.p("len"), _lib.ptr(self.rbins),
+                      self.bb.R, local[key][1], local[key][2], _lib.ptr(ts.u32))
+            if int(ts.u32[0].item()):
+                raise RuntimeError("61-bit content-hash collision detected (window bins differ)")
         self._merge(key, n, None, None)
         self.n_steps += 1
 

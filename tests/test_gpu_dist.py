@@ -1,0 +1,68 @@
+"""2-GPU NCCL test of sharded histogram-mode learning: backbones split across ranks, pair counts combined by the
+slot allreduce + exact top resolution; pop order, vocabulary and per-backbone segmentation must equal the oracle run
+on the whole set.  Needs 2 GPUs (skipped otherwise); run with `gpurun --gpus 2`."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pytestmark = pytest.mark.gpu
+HP = dict(bins={1: 5}, bin_strategy="histogram", std_bonds=True)
+GEN = (40, 48, 31)
+STEPS = 40
+
+
+def worker(rank, world, port, q):
+    for p in (os.path.join(ROOT, "pt-bpe_b200"),):
+        sys.path.insert(0, p)
+    import torch.distributed as dist
+    from geobpe_b200 import engine as E, synthetic
+    from geobpe_b200.distributed import Comm, shard_ranges
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    vals, offs = synthetic.generate(GEN[0], GEN[1], seed=GEN[2], ragged=True)
+    a, b = shard_ranges(np.diff(offs), world)[rank]
+    v = vals[:, offs[a]:offs[b]]
+    o = offs[a:b + 1] - offs[a]
+    L = E.Learner(v, o, mode="H", comm=Comm(), **HP)
+    for _ in range(STEPS):
+        L.step()
+    ts = L.ts
+    pos, ln, tid, glue = (E._u32(ts.a[f][:ts.T]) for f in ("pos", "len", "tid", "glue"))
+    segs = []
+    for i in range(b - a):
+        lo, hi = np.searchsorted(pos, o[i]), np.searchsorted(pos, o[i + 1])
+        segs.append([[int(3 * (pos[j] - o[i])), int(tid[j]), int(3 * ln[j] - (1 if glue[j] & E.LAST else 0))]
+                     for j in range(lo, hi)])
+    q.put((rank, a, [list(p) for p in L.pop_log], [[k, v] for k, v in L.tokens.items()], segs))
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_two_gpu_h_mode_matches_oracle():
+    import torch.multiprocessing as mp
+    import geobpe_oracle as O
+    from geobpe_b200 import synthetic
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 1000
+    ps = [ctx.Process(target=worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in ps]
+    res = sorted(q.get(timeout=300) for _ in ps)
+    [p.join(60) for p in ps]
+    vals, offs = synthetic.generate(GEN[0], GEN[1], seed=GEN[2], ragged=True)
+    ora = O.BPE(synthetic.to_structures(vals, offs), res_init=True, seed=0, rmsd_partition_min_size=float("inf"), **HP)
+    ora.initialize(); ora.bin()
+    for _ in range(STEPS):
+        ora.step()
+    want_pops = [list(p) for p in ora.pop_log]
+    want_tokens = [[k, v] for k, v in ora._tokens.items()]
+    for rank, a, pops, tokens, segs in res:
+        assert pops == want_pops
+        assert tokens == want_tokens
+        for i, seg in enumerate(segs):
+            assert seg == [list(x) for x in ora.tokenizers[a + i].bond_to_token.values()]
