@@ -184,6 +184,7 @@ def main():
     import torch.distributed as dist
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line (NCCL prints its version at VERSION)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from geobpe_b200 import _lib, engine as E, synthetic
     from geobpe_b200 import build as B
@@ -191,7 +192,9 @@ def main():
     hp = hparams(args.mode, args.bins)
     vals, offs = synthetic.generate(args.backbones, args.residues, seed=rank)
     R = int(offs[-1])
-    mk = lambda: E.Learner(vals, offs, rng=np.random.default_rng(0), verify=True, **hp)
+    from geobpe_b200.distributed import Comm
+    comm = Comm() if world > 1 else None
+    mk = lambda: E.Learner(vals, offs, rng=np.random.default_rng(0), verify=True, comm=comm, **hp)
 
     def barrier():
         torch.cuda.synchronize()
@@ -293,7 +296,9 @@ def main():
                      "bytes_per_token": bpt, "share_of_step": k1_share},
         "roofline_at_scale": scale, "cpu_baseline": cpu,
     }
-    print(json.dumps(line))
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
