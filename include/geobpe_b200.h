@@ -143,7 +143,8 @@ int gb_merge_compact(const uint8_t* flags, int64_t T,
                      uint64_t key, uint32_t new_tid, uint32_t* newT, uint32_t* scratch, void* stream);
 /* merge-event log for the merge tree (data_structures.py:217-226): for kept occurrence q (token
  * kept[q]): ev_left[q]=pos[j], ev_right[q]=pos[j+1], ev_p[q]=aux? aux[j] : 0 */
-int gb_write_events(const uint32_t* kept, int64_t Q, const uint32_t* pos, const uint32_t* aux,
+int gb_write_events(const uint32_t* kept, int64_t Q, const uint32_t* count_dev /*nullable: device-side bound*/,
+                    const uint32_t* pos, const uint32_t* aux,
                     uint32_t* ev_left, uint32_t* ev_right, uint32_t* ev_p, void* stream);
 /* medoid mode: occurrence-set op log (SURVEY 7.2 hard part 1).  For kept occurrence q writes 4
  * records at log_key/log_pos[4q..4q+3]: remove left key, remove right key, add new left key, add
@@ -159,6 +160,15 @@ int gb_pair_keys_m(const uint32_t* cls, const uint32_t* glue, const uint32_t* po
 int gb_verify_windows_h(const uint32_t* occ, int64_t Q, const uint32_t* pos, const uint32_t* len,
                         const uint16_t* rbins, int64_t R, uint32_t ref_r0, uint32_t nres,
                         uint32_t* mismatches, void* stream);
+
+/* same check straight from the flags array; out2 u32 [2] = {mismatching windows, flagged pairs} */
+int gb_verify_flagged_h(const uint8_t* flags, int64_t T, const uint32_t* pos, const uint32_t* len,
+                        const uint16_t* rbins, int64_t R, uint32_t ref_r0, uint32_t nres, uint32_t* out2, void* stream);
+/* packs {argmax out4, overflow, first nfirst ties: key, min position, pos, window residues} into res i64 [5+4*nfirst]
+ * so the host reads one buffer per iteration; pos/len nullable (medoid mode needs no window) */
+int gb_pack_result(const uint32_t* out4, const int32_t* overflow, const uint64_t* tie_keys,
+                   const uint32_t* tie_minpos, const uint32_t* pos, const uint32_t* len, int nfirst,
+                   int64_t* res, void* stream);
 
 /* ---- K4/K5/K6: NeRF windows, Kabsch RMSD, medoid assignment (tokenizer.py:347-363, nerf.py:84-210,
  *      angles_and_coords.py:238-317, algo.py:8-65,170-181, bpe.py:646-657) -------------------------- */

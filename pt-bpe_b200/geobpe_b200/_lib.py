@@ -35,7 +35,9 @@ SIGNATURES = {
     "gb_resolve_overlaps": [P, I64, P],
     "gb_scatter_u32": [P, P, I64, P, P],
     "gb_merge_compact": [P, I64] + [P] * 6 + [P] * 6 + [P, P, P, U64, U32, P, P, P],
-    "gb_write_events": [P, I64, P, P, P, P, P, P],
+    "gb_write_events": [P, I64, P, P, P, P, P, P, P],
+    "gb_verify_flagged_h": [P, I64, P, P, P, I64, U32, U32, P, P],
+    "gb_pack_result": [P, P, P, P, P, P, I32, P, P],
     "gb_oplog_m": [P, I64, P, P, P, P, I64, P, P, P, P, P],
     "gb_pair_keys_m": [P, P, P, I64, P, P, P],
     "gb_verify_windows_h": [P, I64, P, P, P, I64, U32, U32, P, P],

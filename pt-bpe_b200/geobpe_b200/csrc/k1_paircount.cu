@@ -423,3 +423,31 @@ extern "C" int gb_table_dump_marked(const uint64_t* tkeys, const uint32_t* tcnt,
   GB_LAUNCH_CK();
   return 0;
 }
+
+// one small result record per iteration so the host needs a single D2H: res i64 [5 + 4*nfirst] =
+// {max, #ties, #distinct, 0, overflow, then for the first nfirst ties: key, min position j, pos[j], len[j]+len[j+1]}
+__global__ void k_pack_result(const u32* __restrict__ out4, const int32_t* __restrict__ overflow,
+                              const u64* __restrict__ tie_keys, const u32* __restrict__ tie_min,
+                              const u32* __restrict__ pos, const u32* __restrict__ len, int nfirst, long long* __restrict__ res) {
+  int i = threadIdx.x;
+  if (i < 4) res[i] = out4[i];
+  if (i == 4) res[4] = *overflow;
+  if (i < nfirst) {
+    long long* r = res + 5 + 4 * i;
+    if ((u32)i < out4[1]) {
+      u32 m = tie_min[i];
+      r[0] = (long long)tie_keys[i]; r[1] = m;
+      bool ok = pos != nullptr && m != 0xFFFFFFFFu;
+      r[2] = ok ? pos[m] : 0; r[3] = ok ? (long long)len[m] + len[m + 1] : 0;
+    } else { r[0] = r[1] = r[2] = r[3] = 0; }
+  }
+}
+extern "C" int gb_pack_result(const uint32_t* out4, const int32_t* overflow, const uint64_t* tie_keys,
+                              const uint32_t* tie_minpos, const uint32_t* pos, const uint32_t* len, int nfirst,
+                              int64_t* res, void* stream) {
+  if (nfirst < 0 || nfirst > 64) { gb_set_error("gb_pack_result: nfirst must be in [0, 64]"); return -2; }
+  k_pack_result<<<1, 64, 0, (cudaStream_t)stream>>>(out4, overflow, (const u64*)tie_keys, tie_minpos, pos, len, nfirst,
+                                                   (long long*)res);
+  GB_LAUNCH_CK();
+  return 0;
+}

@@ -79,10 +79,11 @@ extern "C" int gb_scatter_u32(const uint32_t* occ, const uint32_t* val, int64_t 
   return 0;
 }
 
-__global__ void k_write_events(const u32* __restrict__ kept, i64 Q, const u32* __restrict__ pos,
-                               const u32* __restrict__ aux, u32* __restrict__ el, u32* __restrict__ er,
-                               u32* __restrict__ ep) {
+__global__ void k_write_events(const u32* __restrict__ kept, i64 Q, const u32* __restrict__ count_dev,
+                               const u32* __restrict__ pos, const u32* __restrict__ aux, u32* __restrict__ el,
+                               u32* __restrict__ er, u32* __restrict__ ep) {
   i64 q = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (count_dev && q >= (i64)*count_dev) return;
   if (q < Q) {
     u32 j = kept[q];
     el[q] = pos[j];
@@ -90,10 +91,10 @@ __global__ void k_write_events(const u32* __restrict__ kept, i64 Q, const u32* _
     ep[q] = aux ? aux[j] : 0u;
   }
 }
-extern "C" int gb_write_events(const uint32_t* kept, int64_t Q, const uint32_t* pos, const uint32_t* aux,
-                               uint32_t* ev_left, uint32_t* ev_right, uint32_t* ev_p, void* stream) {
+extern "C" int gb_write_events(const uint32_t* kept, int64_t Q, const uint32_t* count_dev, const uint32_t* pos,
+                               const uint32_t* aux, uint32_t* ev_left, uint32_t* ev_right, uint32_t* ev_p, void* stream) {
   if (Q <= 0) return 0;
-  k_write_events<<<(unsigned)((Q + 255) / 256), 256, 0, (cudaStream_t)stream>>>(kept, Q, pos, aux, ev_left, ev_right, ev_p);
+  k_write_events<<<(unsigned)((Q + 255) / 256), 256, 0, (cudaStream_t)stream>>>(kept, Q, count_dev, pos, aux, ev_left, ev_right, ev_p);
   GB_LAUNCH_CK();
   return 0;
 }
@@ -194,6 +195,34 @@ extern "C" int gb_verify_windows_h(const uint32_t* occ, int64_t Q, const uint32_
   if (Q <= 0) return 0;
   i64 threads = Q * 32;
   k_verify_windows_h<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(occ, Q, pos, len, rbins, R, ref_r0, nres, mismatches);
+  GB_LAUNCH_CK();
+  return 0;
+}
+
+// same check driven by the flags array (no occurrence list, no host round trip): out2 = {mismatches, flagged}
+__global__ void __launch_bounds__(256) k_verify_flagged_h(const u8* __restrict__ flags, i64 T, const u32* __restrict__ pos,
+                                                           const u32* __restrict__ len, const u16* __restrict__ rbins, i64 R,
+                                                           u32 ref_r0, u32 nres, u32* __restrict__ out2) {
+  for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < T; j += (i64)gridDim.x * blockDim.x) {
+    if (!(flags[j] & 1)) continue;
+    atomicAdd(&out2[1], 1u);
+    u32 r0 = pos[j];
+    bool bad = (len[j] + len[j + 1]) != nres;
+    for (u32 slot = 3; slot < 9 && !bad; ++slot) {
+      u32 n = (slot >= 6) ? nres - 1 : nres;   // glue of the last residue lies outside the window
+      for (u32 k = 0; k < n; ++k)
+        if (rbins[(i64)slot * R + r0 + k] != rbins[(i64)slot * R + ref_r0 + k]) { bad = true; break; }
+    }
+    if (bad) atomicAdd(&out2[0], 1u);
+  }
+}
+extern "C" int gb_verify_flagged_h(const uint8_t* flags, int64_t T, const uint32_t* pos, const uint32_t* len,
+                                   const uint16_t* rbins, int64_t R, uint32_t ref_r0, uint32_t nres, uint32_t* out2,
+                                   void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  GB_CK(cudaMemsetAsync(out2, 0, 2 * sizeof(u32), st));
+  if (T <= 0) return 0;
+  k_verify_flagged_h<<<gb_blocks_for(T, 256 * 4, 148 * 8), 256, 0, st>>>(flags, T, pos, len, rbins, R, ref_r0, nres, out2);
   GB_LAUNCH_CK();
   return 0;
 }

@@ -217,12 +217,17 @@ class PairTable:
     def ptrs(self):
         return _lib.ptr(self.keys), _lib.ptr(self.cnt), _lib.ptr(self.min), self.M
 
-    def count(self, launch, n_pairs_bound, first_pos=None):
-        """clear + count (+ retry on overflow with a larger table) + argmax.  `launch(table)` issues the
-        count kernel.  Returns (max_count, [(key, minpos)...] tied at the max)."""
+    NFIRST = 16
+
+    def count(self, launch, n_pairs_bound, first_pos=None, pos_ptr=None, len_ptr=None):
+        """clear + count (+ retry on overflow with a larger table) + argmax (+ first positions), ONE D2H.
+        `launch(table)` issues the count kernel.  Returns (max_count, ties) with ties = [(key, minpos, pos, nres)]
+        (pos / nres = start residue and residue count of the example window; 0 when pos_ptr is None)."""
         want = 4 * max(self.distinct, 1024) + 4096
         first = self.M == 0
         self.ensure(2 * n_pairs_bound if first else max(want, 1 << 12))
+        if not hasattr(self, "res"):
+            self.res = _zeros(5 + 4 * self.NFIRST, torch.int64)
         while True:
             _lib.call("gb_table_clear", *self.ptrs())
             self.overflow.zero_()
@@ -231,20 +236,24 @@ class PairTable:
                       _lib.ptr(self.tie_min), self.TIE_CAP)
             if first_pos is not None:
                 first_pos(self)
-            out4 = self.out4.cpu().numpy().astype(np.int64) & 0xFFFFFFFF
-            ovf = int(self.overflow.item())
-            distinct = int(out4[2])
+            _lib.call("gb_pack_result", _lib.ptr(self.out4), _lib.ptr(self.overflow), _lib.ptr(self.tie_keys),
+                      _lib.ptr(self.tie_min), pos_ptr, len_ptr, self.NFIRST, _lib.ptr(self.res))
+            res = self.res.cpu().numpy()
+            mx, nt, distinct, ovf = int(res[0]), int(res[1]), int(res[2]), int(res[4])
             if ovf or distinct * 2 > self.M:      # keep the load factor below 1/2
                 self.ensure(self.M * 4)
                 continue
             break
         self.distinct = distinct
-        mx, nt = int(out4[0]), int(out4[1])
         if nt > self.TIE_CAP:
             raise RuntimeError(f"{nt} keys tied at count {mx}: tie list capacity {self.TIE_CAP} exceeded")
-        tk = self.tie_keys[:nt].cpu().numpy().astype(np.uint64)
-        tm = self.tie_min[:nt].cpu().numpy().astype(np.int64) & 0xFFFFFFFF
-        return mx, list(zip(tk.tolist(), tm.tolist()))
+        if nt <= self.NFIRST:
+            r = res[5:5 + 4 * nt].reshape(nt, 4)
+            ties = [(int(np.uint64(k)), int(m), int(p), int(n)) for k, m, p, n in r.tolist()]
+            return mx, ties
+        tk = self.tie_keys[:nt].cpu().numpy().astype(np.uint64).tolist()
+        tm = (self.tie_min[:nt].cpu().numpy().astype(np.int64) & 0xFFFFFFFF).tolist()
+        return mx, [(k, m, None, None) for k, m in zip(tk, tm)]
 
     def lookup(self, keys):
         if not keys:
@@ -275,7 +284,7 @@ class TokenState:
         self.scratch = _empty(_lib.load().gb_select_scratch_elems(self.cap), torch.int32)
         self.idx = _empty(self.cap, torch.int32)      # occurrence list (all flagged)
         self.kept = _empty(self.cap, torch.int32)     # kept occurrences
-        self.u32 = _zeros(4, torch.int32)
+        self.u32 = _zeros(8, torch.int32)
 
     def p(self, f, out=False):
         d = self.b if out else self.a
@@ -487,7 +496,8 @@ class Learner:
                 inner(tab)
                 e1.record()
                 self.k1_events.append((e0, e1, ts.T))
-        self._k1_launch_fn = launch
+        if self.mode == "H":
+            return self.table.count(launch, ts.T, first_pos, ts.p("pos"), ts.p("len"))
         return self.table.count(launch, ts.T, first_pos)
 
     def _k1_launch(self, tab):
@@ -510,27 +520,29 @@ class Learner:
         mx, ties = self._count_pairs()
         if mx == 0:
             raise IndexError("no adjacent pairs left (the reference's peekitem(0) raises here too)")
-        mins = torch.tensor([m for _, m in ties], device=_dev(), dtype=torch.int64)
-        p0 = _u32(ts.a["pos"][mins]); l0 = _u32(ts.a["len"][mins]); l1 = _u32(ts.a["len"][mins + 1])
-        nress = (l0 + l1).tolist()
-        dicts = self._h_key_dicts(p0.tolist(), nress)
-        cands = [(json.dumps(d, sort_keys=True), key, r0, nr)
-                 for (key, _), d, r0, nr in zip(ties, dicts, p0.tolist(), nress)]
+        if ties[0][2] is None:                      # long tie list: gather the example windows' extents
+            mins = torch.tensor([t[1] for t in ties], device=_dev(), dtype=torch.int64)
+            p0 = _u32(ts.a["pos"][mins]).tolist()
+            nress = (_u32(ts.a["len"][mins]) + _u32(ts.a["len"][mins + 1])).tolist()
+        else:
+            p0, nress = [t[2] for t in ties], [t[3] for t in ties]
+        dicts = self._h_key_dicts(p0, nress)
+        cands = [(json.dumps(d, sort_keys=True), t[0], r0, nr) for t, d, r0, nr in zip(ties, dicts, p0, nress)]
         key_str, key, r0, nres = min(cands)            # SortedDict order: (-count, key string)
         n = len(self.tokens)
         self.tokens[n] = json.loads(key_str)
         self.pop_log.append((mx, key_str))
         _lib.call("gb_flag_pairs_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), HASH_BASE,
                   key, _lib.ptr(ts.flags))
+        if self.verify:                                # checked after the merge's single read-back (u32[3], u32[4])
+            _lib.call("gb_verify_flagged_h", _lib.ptr(ts.flags), ts.T, ts.p("pos"), ts.p("len"), _lib.ptr(self.rbins),
+                      self.bb.R, r0, nres, ts.u32.data_ptr() + 12)
+        r = self._merge(key, n, None, None, bound=mx)
         if self.verify:
-            nocc = ts.select(1, ts.idx)
-            if nocc != mx:
-                raise RuntimeError(f"flagged {nocc} occurrences, histogram counted {mx}")
-            _lib.call("gb_verify_windows_h", _lib.ptr(ts.idx), nocc, ts.p("pos"), ts.p("len"), _lib.ptr(self.rbins),
-                      self.bb.R, r0, nres, _lib.ptr(ts.u32))
-            if int(ts.u32[0].item()):
+            if int(r[3]):
                 raise RuntimeError("61-bit content-hash collision detected (window bins differ); re-run with another HASH_BASE")
-        self._merge(key, n, None, None)
+            if int(r[4]) != mx:
+                raise RuntimeError(f"flagged {int(r[4])} occurrences, histogram counted {mx}")
         self.n_steps += 1
 
     NS = 1 << 20      # direct-mapped slot counters exchanged per iteration (4 MB allreduce)
@@ -608,16 +620,23 @@ class Learner:
         self._merge(key, n, None, None)
         self.n_steps += 1
 
-    def _merge(self, key, new_tid, p2cls, p2tid):
-        """K2: overlap rule, event log, stream compaction"""
+    def _merge(self, key, new_tid, p2cls, p2tid, bound=None):
+        """K2: overlap rule, event log, stream compaction.  With `bound` (an upper bound of the kept occurrences,
+        histogram mode) nothing is read back until the end: one D2H of ts.u32 = {-, kept, newT, verify...}."""
         ts = self.ts
         _lib.call("gb_resolve_overlaps", _lib.ptr(ts.flags), ts.T)
-        nk = ts.select(2, ts.kept)
         aux = _lib.ptr(ts.aux) if p2cls is not None else None
-        if self.ev_n + nk > self.ev_left.numel():
-            raise RuntimeError("merge-event log overflow")
         off = self.ev_n * 4
-        _lib.call("gb_write_events", _lib.ptr(ts.kept), nk, ts.p("pos"), aux, self.ev_left.data_ptr() + off,
+        u = ts.u32.data_ptr()
+        _lib.call("gb_select_flagged", _lib.ptr(ts.flags), ts.T, 2, _lib.ptr(ts.kept), u + 4, _lib.ptr(ts.scratch))
+        if bound is None:
+            nk = int(ts.u32[1].item())
+            q, cnt_dev = nk, None
+        else:
+            q, cnt_dev = min(bound, ts.T), u + 4
+        if self.ev_n + q > self.ev_left.numel():
+            raise RuntimeError("merge-event log overflow")
+        _lib.call("gb_write_events", _lib.ptr(ts.kept), q, cnt_dev, ts.p("pos"), aux, self.ev_left.data_ptr() + off,
                   self.ev_right.data_ptr() + off, self.ev_p.data_ptr() + off)
         if self.mode == "M":
             self._oplog(nk, p2cls)
@@ -626,14 +645,15 @@ class Learner:
                   ts.p("cls", True), ts.p("hsh", True), ts.p("glue", True), ts.p("pos", True), ts.p("len", True),
                   ts.p("tid", True), aux, _lib.ptr(p2cls) if p2cls is not None else None,
                   _lib.ptr(p2tid) if p2tid is not None else None, key, new_tid & 0xFFFFFFFF,
-                  _lib.ptr(ts.u32), _lib.ptr(ts.scratch))
-        newT = int(ts.u32[0].item())
+                  u + 8, _lib.ptr(ts.scratch))
+        r = _u32(ts.u32)
+        nk, newT = int(r[1]), int(r[2])
         assert newT == ts.T - nk, (newT, ts.T, nk)
         ts.swap()
         ts.T = newT
         self.step_events.append((new_tid, self.ev_n, nk, key))
         self.ev_n += nk
-        return nk
+        return r
 
     # ---- medoid mode ---------------------------------------------------------------------------------
     def num_p(self, length):
@@ -896,7 +916,7 @@ class Learner:
         if recurring:
             mx, key_str, key = rec
         else:
-            key_str, key = min((self.m_key_string(k)[0], k) for k, _ in ties)
+            key_str, key = min((self.m_key_string(t[0])[0], t[0]) for t in ties)
         self.pop_log.append((mx, key_str))
         cL, cR = (key >> 45) & 0x3FFFF, (key >> 27) & 0x3FFFF
         gl, gr = self.class_geo[cL], self.class_geo[cR]

@@ -17,7 +17,7 @@ for step in range(g["final"]["step"]):
     (ex, negc, key), _ = ora._priority_dict.peekitem(0)
     want = list(ora._geo_dict[key])
     mx, ties, rec = L.peek_m()
-    ks, k = min((L.m_key_string(kk)[0], kk) for kk, _ in ties)
+    ks, k = min((L.m_key_string(kk)[0], kk) for kk, *_ in ties)
     got = L.set_order(k)
     same_key = ks == key
     print("step", step, "count", -negc, "samekey", same_key, "setorder_equal", got == want, "sorted_equal", sorted(got) == sorted(want))
