@@ -126,40 +126,50 @@ def reference_arm(args):
 
 def k1_scale_probe(learner, mode, reps=20, target_tokens=48_000_000):
     """K1 alone at the per-GPU shard size of BASELINE config 5 (48 M live tokens): the token arrays of this
-    workload tiled on the device (same key distribution), larger than L2 (126 MB)."""
+    workload tiled on the device (same key distribution), larger than L2 (126 MB).  Times pass 1 (k_slot_count, the
+    pair-count kernel) and pass 2 (k_cand_count, exact resolution of the top slots) separately."""
     import torch
     from geobpe_b200 import _lib, engine as E
     ts = learner.ts
     T0 = ts.T
     rep = max(1, target_tokens // T0)
     T = T0 * rep
-    tab = E.PairTable()
-    tab.ensure(4 * max(learner.table.distinct, 1024) + 4096)
+    pad = lambda t: torch.cat([t, torch.zeros(8, dtype=t.dtype, device=t.device)])
+    sk = E.SlotSketch(T0)          # same slot count as the learner's own sketch: the tiled data has the same distinct keys
     if mode == "H":
-        h = ts.a["hsh"][:T0].repeat(rep).contiguous(); g = ts.a["glue"][:T0].repeat(rep).contiguous()
-        l = ts.a["len"][:T0].repeat(rep).contiguous()
-        pad = lambda t: torch.cat([t, torch.zeros(8, dtype=t.dtype, device=t.device)])
-        h, g, l = pad(h), pad(g), pad(l)
+        h = pad(ts.a["hsh"][:T0].repeat(rep)); g = pad(ts.a["glue"][:T0].repeat(rep)); l = pad(ts.a["len"][:T0].repeat(rep))
         l[T:] = 1
-        launch = lambda: _lib.call("gb_pair_count_h", _lib.ptr(h), _lib.ptr(g), _lib.ptr(l), T, _lib.ptr(learner.powtab),
-                                   E.HASH_BASE, *tab.ptrs(), _lib.ptr(tab.overflow))
+        p1 = lambda: _lib.call("gb_slot_count_h", _lib.ptr(h), _lib.ptr(g), _lib.ptr(l), T, _lib.ptr(learner.powtab), E.HASH_BASE,
+                               _lib.ptr(sk.slots), sk.log2ns, None, sk.variant | 8, sk.ctas)
+        p2 = lambda: _lib.call("gb_cand_count_h", _lib.ptr(h), _lib.ptr(g), _lib.ptr(l), T, _lib.ptr(learner.powtab), E.HASH_BASE,
+                               sk.log2ns, _lib.ptr(sk.cand), sk.sout.data_ptr() + 4, sk.CAP, *sk.small.ptrs(),
+                               _lib.ptr(sk.small.overflow), 1)
         bpt = 16
     else:
-        c = ts.a["cls"][:T0].repeat(rep).contiguous(); g = ts.a["glue"][:T0].repeat(rep).contiguous()
-        pad = lambda t: torch.cat([t, torch.zeros(8, dtype=t.dtype, device=t.device)])
-        c, g = pad(c), pad(g)
-        launch = lambda: _lib.call("gb_pair_count_m", _lib.ptr(c), _lib.ptr(g), T, *tab.ptrs(), _lib.ptr(tab.overflow))
+        c = pad(ts.a["cls"][:T0].repeat(rep)); g = pad(ts.a["glue"][:T0].repeat(rep))
+        p1 = lambda: _lib.call("gb_slot_count_m", _lib.ptr(c), _lib.ptr(g), T, _lib.ptr(sk.slots), sk.log2ns, None,
+                               sk.variant | 8, sk.ctas)
+        p2 = lambda: _lib.call("gb_cand_count_m", _lib.ptr(c), _lib.ptr(g), T, sk.log2ns, _lib.ptr(sk.cand),
+                               sk.sout.data_ptr() + 4, sk.CAP, *sk.small.ptrs(), _lib.ptr(sk.small.overflow), 1)
         bpt = 8
-    ms = []
-    for i in range(reps + 3):
-        _lib.call("gb_table_clear", *tab.ptrs())
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(); launch(); e1.record()
-        torch.cuda.synchronize()
-        if i >= 3:
-            ms.append(e0.elapsed_time(e1))
-    assert int(tab.overflow.item()) == 0
-    return T, bpt, float(np.mean(ms)), float(np.min(ms))
+
+    def timed(fn, pre):
+        ms = []
+        for i in range(reps + 3):
+            pre()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record()
+            torch.cuda.synchronize()
+            if i >= 3:
+                ms.append(e0.elapsed_time(e1))
+        return float(np.mean(ms)), float(np.min(ms))
+    avg, best = timed(p1, lambda: sk.slots.zero_())
+    _lib.call("gb_slots_top", _lib.ptr(sk.slots), sk.log2ns, 0, _lib.ptr(sk.sout), _lib.ptr(sk.cand), sk.CAP, _lib.ptr(sk.bmax))
+    avg2, best2 = timed(p2, lambda: _lib.call("gb_table_clear", *sk.small.ptrs()))
+    so = sk.sout.cpu().numpy()
+    assert int(sk.small.overflow.item()) == 0
+    return {"tokens": T, "bytes_per_token": bpt, "ms": avg, "ms_min": best, "pass2_ms": avg2, "pass2_ms_min": best2,
+            "slots": 1 << sk.log2ns, "nonzero_slots": int(so[2]), "top_slot_count": int(so[0])}
 
 
 def main():
@@ -234,17 +244,22 @@ def main():
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s"
     achieved = k1_bytes / (k1_avg_ms * 1e-3) / 1e9
-    distinct, pairs, top = L.table.distinct, L.ts.T - L.bb.S, L.pop_log[-1][0]
+    sk = getattr(L, "sketch", None)
+    distinct = int(sk.sout.cpu()[2]) if sk is not None else L.table.distinct   # sketch: non-zero slots (lower bound)
+    k1_name = ("k_slot_count" if sk is not None else "k_pair_count") + ("<KeysH>" if args.mode == "H" else "<KeysM>")
+    sk_rounds = list(sk.rounds) if sk is not None else None
+    pairs, top = L.ts.T - L.bb.S, L.pop_log[-1][0]
     T_end = L.ts.T
     k1_share = sum(k1_ms) / ms
     L.k1_events = None
     scale = None
     if not args.no_scale_probe and rank == 0:
-        Ts, b2, avg, best = k1_scale_probe(L, args.mode)
-        a2 = b2 * Ts / (avg * 1e-3) / 1e9
-        scale = {"bound": "hbm", "tokens": Ts, "bytes_per_token": b2, "ms": avg, "ms_min": best, "achieved": a2,
-                 "peak": peak, "unit": "GB/s", "frac": a2 / peak,
-                 "note": "K1 alone on this workload's token arrays tiled to the per-GPU shard of BASELINE config 5 (48 M tokens > L2)"}
+        pr = k1_scale_probe(L, args.mode)
+        a2 = pr["bytes_per_token"] * pr["tokens"] / (pr["ms"] * 1e-3) / 1e9
+        scale = dict(pr, bound="hbm", achieved=a2, peak=peak, unit="GB/s", frac=a2 / peak,
+                     pass2_achieved=pr["bytes_per_token"] * pr["tokens"] / (pr["pass2_ms"] * 1e-3) / 1e9,
+                     note="K1 pass 1 (k_slot_count) alone on this workload's token arrays tiled to the per-GPU shard of "
+                          "BASELINE config 5 (48 M tokens > L2); pass2_* = k_cand_count (exact resolution) on the same arrays")
     del L
     torch.cuda.empty_cache()
 
@@ -290,7 +305,7 @@ def main():
                    "pairs": pairs, "distinct_over_pairs": distinct / max(pairs, 1), "last_top_count": top,
                    "residues_total": R * world},
         "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
-        "roofline": {"bound": "hbm", "kernel": "k_pair_count<KeysH>" if args.mode == "H" else "k_pair_count<KeysM>",
+        "roofline": {"bound": "hbm", "kernel": k1_name, "resolve_rounds_1_2_fallback": sk_rounds,
                      "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "avg_ms": k1_avg_ms, "algorithmic_bytes_per_launch": k1_bytes,
                      "bytes_per_token": bpt, "share_of_step": k1_share},

@@ -119,6 +119,31 @@ int gb_table_to_slots(const uint64_t* tkeys, const uint32_t* tcnt, int64_t M, ui
 int gb_table_dump_marked(const uint64_t* tkeys, const uint32_t* tcnt, int64_t M, const uint8_t* slotmark,
                          int64_t NS, uint64_t* out_keys, uint32_t* out_cnt, uint32_t* total, int cap, void* stream);
 
+/* ---- K1s: slot-sketch pair counting (same reference rows as K1: bpe.py:1431-1474 bin, 1796 peekitem,
+ *      2077-2138 recount).  slots u32 [1 << log2ns], slot = (key * 0x9E3779B97F4A7C15) >> (64 - log2ns).
+ *      variant bits: 1 = match.any warp aggregation, 2 = dynamic shared-memory hot stage, 4 = static hot list
+ *      (hot_tags u32 [8192], 0xFFFFFFFF = unused), 8 = cache-streaming token loads, 16 = dry run (no REDs; timing
+ *      probe only).  The caller zeroes `slots`. */
+int gb_slot_count_m(const uint32_t* cls, const uint32_t* glue, int64_t T, uint32_t* slots, int log2ns,
+                    const uint32_t* hot_tags, int variant, int ctas_per_sm, void* stream);
+int gb_slot_count_h(const uint64_t* hsh, const uint32_t* glue, const uint32_t* len, int64_t T,
+                    const uint64_t* powtab, uint64_t P, uint32_t* slots, int log2ns,
+                    const uint32_t* hot_tags, int variant, int ctas_per_sm, void* stream);
+/* sout u32 [4] = {max slot count, #candidates, #non-zero slots, 0}.  thr_host == 0: find the max and list the slots
+ * holding it; thr_host > 0: list the slots with count >= thr_host (sout[0], sout[2], bmax of the thr_host == 0 call
+ * are reused).  cand u32 [cap]; log2ns >= 12 */
+int gb_slots_top(const uint32_t* slots, int log2ns, uint32_t thr_host, uint32_t* sout, uint32_t* cand, int cap,
+                 uint32_t* bmax /* scratch u32 [(1 << log2ns) / 4096]: per-chunk maxima */, void* stream);
+/* exact (key, count, first position) of every pair whose slot is in cand[0 .. *n_cand_dev) into the open-addressing
+ * table (cleared by the caller).  overflow: 1 = table full, 2 = *n_cand_dev > cap (nothing counted); cap <= 4096 */
+int gb_cand_count_m(const uint32_t* cls, const uint32_t* glue, int64_t T, int log2ns, const uint32_t* cand,
+                    const uint32_t* n_cand_dev, int cap, uint64_t* tkeys, uint32_t* tcnt, uint32_t* tmin,
+                    int64_t M, int32_t* overflow, int streaming, void* stream);
+int gb_cand_count_h(const uint64_t* hsh, const uint32_t* glue, const uint32_t* len, int64_t T,
+                    const uint64_t* powtab, uint64_t P, int log2ns, const uint32_t* cand,
+                    const uint32_t* n_cand_dev, int cap, uint64_t* tkeys, uint32_t* tcnt, uint32_t* tmin,
+                    int64_t M, int32_t* overflow, int streaming, void* stream);
+
 /* ---- K2: merge (bpe.py:1895-2017) --------------------------------------------------------------- */
 /* flags[j] bit0 = pair (j,j+1) has key `key` */
 int gb_flag_pairs_m(const uint32_t* cls, const uint32_t* glue, int64_t T, uint64_t key, uint8_t* flags,
@@ -168,6 +193,7 @@ int gb_verify_flagged_h(const uint8_t* flags, int64_t T, const uint32_t* pos, co
  * so the host reads one buffer per iteration; pos/len nullable (medoid mode needs no window) */
 int gb_pack_result(const uint32_t* out4, const int32_t* overflow, const uint64_t* tie_keys,
                    const uint32_t* tie_minpos, const uint32_t* pos, const uint32_t* len, int nfirst,
+                   const uint32_t* sout /* nullable: gb_slots_top's sout -> res[3] = sout[0] | sout[1] << 32 */,
                    int64_t* res, void* stream);
 
 /* ---- K4/K5/K6: NeRF windows, Kabsch RMSD, medoid assignment (tokenizer.py:347-363, nerf.py:84-210,

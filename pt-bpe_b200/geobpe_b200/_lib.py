@@ -30,6 +30,11 @@ SIGNATURES = {
     "gb_table_dump": [P, P, P, I64, P, P, P, P, P],
     "gb_table_to_slots": [P, P, I64, P, I64, P],
     "gb_table_dump_marked": [P, P, I64, P, I64, P, P, P, I32, P],
+    "gb_slot_count_m": [P, P, I64, P, I32, P, I32, I32, P],
+    "gb_slot_count_h": [P, P, P, I64, P, U64, P, I32, P, I32, I32, P],
+    "gb_slots_top": [P, I32, U32, P, P, I32, P, P],
+    "gb_cand_count_m": [P, P, I64, I32, P, P, I32, P, P, P, I64, P, I32, P],
+    "gb_cand_count_h": [P, P, P, I64, P, U64, I32, P, P, I32, P, P, P, I64, P, I32, P],
     "gb_flag_pairs_m": [P, P, I64, U64, P, P],
     "gb_flag_pairs_h": [P, P, P, I64, P, U64, U64, P, P],
     "gb_resolve_overlaps": [P, I64, P],
@@ -37,7 +42,7 @@ SIGNATURES = {
     "gb_merge_compact": [P, I64] + [P] * 6 + [P] * 6 + [P, P, P, U64, U32, P, P, P],
     "gb_write_events": [P, I64, P, P, P, P, P, P, P],
     "gb_verify_flagged_h": [P, I64, P, P, P, I64, U32, U32, P, P],
-    "gb_pack_result": [P, P, P, P, P, P, I32, P, P],
+    "gb_pack_result": [P, P, P, P, P, P, I32, P, P, P],
     "gb_oplog_m": [P, I64, P, P, P, P, I64, P, P, P, P, P],
     "gb_pair_keys_m": [P, P, P, I64, P, P, P],
     "gb_verify_windows_h": [P, I64, P, P, P, I64, U32, U32, P, P],

@@ -67,23 +67,15 @@ __device__ __forceinline__ u64 gb_key_m(u32 cL, u32 g, u32 cR) {
   return ((u64)cL << 45) | ((u64)cR << 27) | (u64)g27;
 }
 
-__device__ __forceinline__ u64 gb_mulmod61(u64 a, u64 b) {
-  u64 lo = a * b, hi = __umul64hi(a, b);
-  u64 r = (lo & GB_P61) + ((lo >> 61) | (hi << 3));
-  r = (r & GB_P61) + (r >> 61);
-  if (r >= GB_P61) r -= GB_P61;
-  return r;
-}
-__device__ __forceinline__ u64 gb_addmod61(u64 a, u64 b) {
-  u64 r = a + b;
-  if (r >= GB_P61) r -= GB_P61;
-  return r;
-}
-// histogram mode: hash of  content(L) . gluesym . content(R);  mR = 2*lenR-1 symbols in R
+// histogram mode: polynomial content hash over Z/2^64 (odd base P, natural wrap-around) of
+//   content(L) . gluesym . content(R);  PpowR = P^(2*lenR-1), the number of symbols in R.
+// Concatenation-stable: H(L.g.R) = (H(L)*P + g)*P^|R| + H(R), so [A][BC] and [AB][C] share a key like the reference's
+// whole-window bin vector does.  Two 64-bit multiplies per pair (the former mod 2^61-1 variant needed two 128-bit
+// products and made K1 ALU-bound).  Every merge still verifies the flagged windows bin by bin (gb_verify_*).
 __device__ __forceinline__ u64 gb_key_h(u64 hL, u32 g, u64 hR, u64 P, u64 PpowR) {
   u64 gs = (u64)(g & 0x3FFFFFFFu) + 1ull;
-  u64 t = gb_addmod61(gb_mulmod61(hL, P), gs);
-  return gb_addmod61(gb_mulmod61(t, PpowR), hR);
+  u64 k = (hL * P + gs) * PpowR + hR;
+  return k == GB_EMPTY_KEY ? k - 1ull : k;     // the all-ones value is reserved for "no pair"
 }
 
 // ---- binary flags block scan (blockDim.x multiple of 32, <= 1024) -------------------------------

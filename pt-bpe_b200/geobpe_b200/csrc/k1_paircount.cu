@@ -6,9 +6,9 @@
 //   tie list.  HBM-bound: cls + glue = 8 B per live token (medoid mode), hsh+glue+len = 16 B (histogram mode),
 //   read once with 128-bit coalesced loads.
 #include "common.cuh"
+#include "k1_keys.cuh"
 
 #define K1_THREADS 512
-#define K1_VEC 4
 #define K1_TILE (K1_THREADS * K1_VEC)
 #define K1_SLOTS 8192           // direct-mapped shared-memory cache per CTA: u64 key + u32 count = 96 KB
 
@@ -50,73 +50,6 @@ __device__ __forceinline__ void warp_agg_count(const SCache& s, const GTable& g,
     else gtable_count(g, key, c);
   }
 }
-
-// ---- key functors: load K1_VEC consecutive tokens per thread + the right neighbour of the last ----
-struct KeysM {
-  const u32* cls; const u32* glue;
-  __device__ __forceinline__ void keys(i64 j0, i64 T, u64 out[K1_VEC]) const {
-    u32 c[K1_VEC + 1], g[K1_VEC];
-    if (j0 + K1_VEC <= T) {
-      uint4 cv = *reinterpret_cast<const uint4*>(cls + j0);
-      uint4 gv = *reinterpret_cast<const uint4*>(glue + j0);
-      c[0] = cv.x; c[1] = cv.y; c[2] = cv.z; c[3] = cv.w;
-      g[0] = gv.x; g[1] = gv.y; g[2] = gv.z; g[3] = gv.w;
-    } else {
-#pragma unroll
-      for (int e = 0; e < K1_VEC; ++e) {
-        bool in = j0 + e < T;
-        c[e] = in ? cls[j0 + e] : 0u;
-        g[e] = in ? glue[j0 + e] : GB_LAST_FLAG;
-      }
-    }
-    // right neighbour of the 4th token: first token of the next lane, or one scalar load for lane 31
-    u32 nxt = __shfl_down_sync(0xffffffffu, c[0], 1);
-    if ((threadIdx.x & 31) == 31) nxt = (j0 + K1_VEC < T) ? cls[j0 + K1_VEC] : 0u;
-    c[K1_VEC] = nxt;
-#pragma unroll
-    for (int e = 0; e < K1_VEC; ++e) {
-      bool valid = (j0 + e + 1 < T) && !(g[e] & GB_LAST_FLAG);
-      out[e] = valid ? gb_key_m(c[e], g[e], c[e + 1]) : GB_EMPTY_KEY;
-    }
-  }
-};
-
-struct KeysH {
-  const u64* hsh; const u32* glue; const u32* len; const u64* powtab; u64 P;
-  __device__ __forceinline__ void keys(i64 j0, i64 T, u64 out[K1_VEC]) const {
-    u64 h[K1_VEC + 1]; u32 g[K1_VEC], l[K1_VEC + 1];
-    if (j0 + K1_VEC <= T) {
-      ulonglong2 h01 = *reinterpret_cast<const ulonglong2*>(hsh + j0);
-      ulonglong2 h23 = *reinterpret_cast<const ulonglong2*>(hsh + j0 + 2);
-      uint4 gv = *reinterpret_cast<const uint4*>(glue + j0);
-      uint4 lv = *reinterpret_cast<const uint4*>(len + j0);
-      h[0] = h01.x; h[1] = h01.y; h[2] = h23.x; h[3] = h23.y;
-      g[0] = gv.x; g[1] = gv.y; g[2] = gv.z; g[3] = gv.w;
-      l[0] = lv.x; l[1] = lv.y; l[2] = lv.z; l[3] = lv.w;
-    } else {
-#pragma unroll
-      for (int e = 0; e < K1_VEC; ++e) {
-        bool in = j0 + e < T;
-        h[e] = in ? hsh[j0 + e] : 0ull;
-        g[e] = in ? glue[j0 + e] : GB_LAST_FLAG;
-        l[e] = in ? len[j0 + e] : 1u;
-      }
-    }
-    u64 nh = __shfl_down_sync(0xffffffffu, h[0], 1);
-    u32 nl = __shfl_down_sync(0xffffffffu, l[0], 1);
-    if ((threadIdx.x & 31) == 31) {
-      bool in = j0 + K1_VEC < T;
-      nh = in ? hsh[j0 + K1_VEC] : 0ull;
-      nl = in ? len[j0 + K1_VEC] : 1u;
-    }
-    h[K1_VEC] = nh; l[K1_VEC] = nl;
-#pragma unroll
-    for (int e = 0; e < K1_VEC; ++e) {
-      bool valid = (j0 + e + 1 < T) && !(g[e] & GB_LAST_FLAG);
-      out[e] = valid ? gb_key_h(h[e], g[e], h[e + 1], P, __ldg(powtab + (2u * l[e + 1] - 1u))) : GB_EMPTY_KEY;
-    }
-  }
-};
 
 struct KeysArr {
   const u64* k;
@@ -314,7 +247,7 @@ __global__ void __launch_bounds__(256) k_table_ties(const u64* __restrict__ tk, 
   for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (i64)gridDim.x * blockDim.x) {
     if (tc[i] == mx) {
       u32 k = atomicAdd(&out4[1], 1u);
-      if (k < (u32)cap) { tie_keys[k] = tk[i]; tie_min[k] = 0xFFFFFFFFu; }
+      if (k < (u32)cap) { tie_keys[k] = tk[i]; tie_min[k] = tm[i]; }   // tm = first position when the insertion tracked it, else 0xFFFFFFFF
     }
   }
 }
@@ -428,9 +361,11 @@ extern "C" int gb_table_dump_marked(const uint64_t* tkeys, const uint32_t* tcnt,
 // {max, #ties, #distinct, 0, overflow, then for the first nfirst ties: key, min position j, pos[j], len[j]+len[j+1]}
 __global__ void k_pack_result(const u32* __restrict__ out4, const int32_t* __restrict__ overflow,
                               const u64* __restrict__ tie_keys, const u32* __restrict__ tie_min,
-                              const u32* __restrict__ pos, const u32* __restrict__ len, int nfirst, long long* __restrict__ res) {
+                              const u32* __restrict__ pos, const u32* __restrict__ len, int nfirst,
+                              const u32* __restrict__ sout, long long* __restrict__ res) {
   int i = threadIdx.x;
   if (i < 4) res[i] = out4[i];
+  if (i == 3 && sout) res[3] = (long long)(((u64)sout[1] << 32) | sout[0]);
   if (i == 4) res[4] = *overflow;
   if (i < nfirst) {
     long long* r = res + 5 + 4 * i;
@@ -444,10 +379,10 @@ __global__ void k_pack_result(const u32* __restrict__ out4, const int32_t* __res
 }
 extern "C" int gb_pack_result(const uint32_t* out4, const int32_t* overflow, const uint64_t* tie_keys,
                               const uint32_t* tie_minpos, const uint32_t* pos, const uint32_t* len, int nfirst,
-                              int64_t* res, void* stream) {
+                              const uint32_t* sout, int64_t* res, void* stream) {
   if (nfirst < 0 || nfirst > 64) { gb_set_error("gb_pack_result: nfirst must be in [0, 64]"); return -2; }
   k_pack_result<<<1, 64, 0, (cudaStream_t)stream>>>(out4, overflow, (const u64*)tie_keys, tie_minpos, pos, len, nfirst,
-                                                   (long long*)res);
+                                                   sout, (long long*)res);
   GB_LAUNCH_CK();
   return 0;
 }

@@ -31,8 +31,8 @@ TWO_PI = 2 * np.pi
 NOBIN = 0x3FF
 LAST = 0x80000000
 EMPTY = 0xFFFFFFFFFFFFFFFF
-P61 = (1 << 61) - 1
-HASH_BASE = 0x1B873593A5C1F3D7 % P61                  # fixed base of the histogram-mode content hash
+M64 = (1 << 64) - 1
+HASH_BASE = 0x1B873593A5C1F3D7                        # odd base of the histogram-mode content hash (mod 2^64)
 
 
 def _angle_between(v1, v2):                           # angles_and_coords.py:746-752
@@ -237,7 +237,7 @@ class PairTable:
             if first_pos is not None:
                 first_pos(self)
             _lib.call("gb_pack_result", _lib.ptr(self.out4), _lib.ptr(self.overflow), _lib.ptr(self.tie_keys),
-                      _lib.ptr(self.tie_min), pos_ptr, len_ptr, self.NFIRST, _lib.ptr(self.res))
+                      _lib.ptr(self.tie_min), pos_ptr, len_ptr, self.NFIRST, None, _lib.ptr(self.res))
             res = self.res.cpu().numpy()
             mx, nt, distinct, ovf = int(res[0]), int(res[1]), int(res[2]), int(res[4])
             if ovf or distinct * 2 > self.M:      # keep the load factor below 1/2
@@ -249,7 +249,7 @@ class PairTable:
             raise RuntimeError(f"{nt} keys tied at count {mx}: tie list capacity {self.TIE_CAP} exceeded")
         if nt <= self.NFIRST:
             r = res[5:5 + 4 * nt].reshape(nt, 4)
-            ties = [(int(np.uint64(k)), int(m), int(p), int(n)) for k, m, p, n in r.tolist()]
+            ties = [(int(k) & M64, int(m), int(p), int(n)) for k, m, p, n in r.tolist()]
             return mx, ties
         tk = self.tie_keys[:nt].cpu().numpy().astype(np.uint64).tolist()
         tm = (self.tie_min[:nt].cpu().numpy().astype(np.int64) & 0xFFFFFFFF).tolist()
@@ -264,6 +264,74 @@ class PairTable:
         _lib.call("gb_table_lookup", *self.ptrs(), _lib.ptr(q), len(keys), _lib.ptr(oc), _lib.ptr(om))
         return ((oc.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).tolist(),
                 (om.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).tolist())
+
+
+class SlotSketch:
+    """K1 driver, sketch design (csrc/k1_slots.cu): pass 1 REDs every pair into key-less slot counters, the scan
+    lists the slots holding the max, pass 2 counts the keys of those slots exactly (small PairTable).  Exact by
+    construction: a key outside the listed slots has count <= its slot's count < the listed threshold."""
+    CAP = 4096               # candidate slots per round (k_cand_count's shared set holds 2 * CAP)
+    STREAM_BYTES = 96 << 20  # token arrays above this size are read with evict-first loads (slots stay in L2)
+
+    def __init__(self, n_pairs_bound, log2ns=None, variant=2, ctas_per_sm=2):
+        if log2ns is None:
+            log2ns = max(16, min(24, (max(n_pairs_bound, 2) - 1).bit_length()))   # NS >= pairs >= distinct; <= 64 MB (L2)
+        self.log2ns = log2ns
+        self.variant = variant
+        self.ctas = ctas_per_sm
+        self.slots = _zeros(1 << log2ns, torch.int32)
+        self.bmax = _zeros(max(1, (1 << log2ns) // 4096), torch.int32)
+        self.sout = _zeros(4, torch.int32)
+        self.cand = _zeros(self.CAP, torch.int32)
+        self.small = PairTable()
+        self.small.ensure(1 << 13)
+        self.small.res = _zeros(5 + 4 * PairTable.NFIRST, torch.int64)
+        self.rounds = [0, 0, 0]      # iterations resolved in one round / two rounds / by the exact-table fallback
+        self.nonzero = 0
+
+    def count(self, pass1, pass2, pos_ptr=None, len_ptr=None):
+        """pass1(slots_ptr, log2ns, variant, ctas) issues k_slot_count; pass2(log2ns, cand_ptr, ncand_ptr, cap, table)
+        issues k_cand_count.  Returns (max_count, ties) like PairTable.count, or None when more than CAP slots tie at
+        the top (flat distributions: the caller falls back to the exact table)."""
+        sm = self.small
+        self.slots.zero_()
+        pass1(_lib.ptr(self.slots), self.log2ns, self.variant, self.ctas)
+        _lib.call("gb_slots_top", _lib.ptr(self.slots), self.log2ns, 0, _lib.ptr(self.sout), _lib.ptr(self.cand), self.CAP,
+                  _lib.ptr(self.bmax))
+        rnd = 0
+        while True:
+            _lib.call("gb_table_clear", *sm.ptrs())
+            sm.overflow.zero_()
+            pass2(self.log2ns, _lib.ptr(self.cand), self.sout.data_ptr() + 4, self.CAP, sm)
+            _lib.call("gb_table_argmax", *sm.ptrs(), _lib.ptr(sm.out4), _lib.ptr(sm.tie_keys), _lib.ptr(sm.tie_min), sm.TIE_CAP)
+            _lib.call("gb_pack_result", _lib.ptr(sm.out4), _lib.ptr(sm.overflow), _lib.ptr(sm.tie_keys), _lib.ptr(sm.tie_min),
+                      pos_ptr, len_ptr, sm.NFIRST, _lib.ptr(self.sout), _lib.ptr(sm.res))
+            res = sm.res.cpu().numpy()
+            m1, nt, nd, ovf = int(res[0]), int(res[1]), int(res[2]), int(res[4])
+            c1, ncand = int(res[3]) & 0xFFFFFFFF, (int(res[3]) >> 32) & 0xFFFFFFFF
+            if c1 == 0:
+                return 0, []
+            if ovf == 2 or ncand > self.CAP:
+                self.rounds[2] += 1
+                return None
+            if ovf == 1 or nd * 2 > sm.M:
+                sm.ensure(sm.M * 4)
+                continue
+            if m1 == c1 or rnd == 1:
+                break
+            # every top slot holds a collision: list all slots that could hold a key with count >= m1 and recount
+            rnd = 1
+            _lib.call("gb_slots_top", _lib.ptr(self.slots), self.log2ns, m1, _lib.ptr(self.sout), _lib.ptr(self.cand), self.CAP,
+                      _lib.ptr(self.bmax))
+        self.rounds[rnd] += 1
+        if nt > sm.TIE_CAP:
+            raise RuntimeError(f"{nt} keys tied at count {m1}: tie list capacity {sm.TIE_CAP} exceeded")
+        if nt <= sm.NFIRST:
+            r = res[5:5 + 4 * nt].reshape(nt, 4)
+            return m1, [(int(k) & M64, int(m), int(p), int(n)) for k, m, p, n in r.tolist()]
+        tk = sm.tie_keys[:nt].cpu().numpy().astype(np.uint64).tolist()
+        tm = (sm.tie_min[:nt].cpu().numpy().astype(np.int64) & 0xFFFFFFFF).tolist()
+        return m1, [(k, m, None, None) for k, m in zip(tk, tm)]
 
 
 class TokenState:
@@ -312,7 +380,8 @@ class Learner:
     """
 
     def __init__(self, vals, offsets, bins, bin_strategy="histogram", std_bonds=True, mode="H",
-                 rmsd_super_res=True, num_partitions=3, max_num_strucs=500, rng=None, verify=True, comm=None):
+                 rmsd_super_res=True, num_partitions=3, max_num_strucs=500, rng=None, verify=True, comm=None,
+                 use_sketch=True):
         self.comm = comm if (comm is not None and comm.world > 1) else None
         if self.comm is not None and mode != "H":
             raise NotImplementedError("multi-GPU medoid mode needs the sampled windows gathered in set order "
@@ -338,6 +407,9 @@ class Learner:
         self.sphere_n = {}
         self.k1_events = None
         self._peek = None
+        self.use_sketch = use_sketch
+        self.k1b_events = None
+        self.sketch = None
         self.th = Thresholds(self.bb, self.bins, bin_strategy, std_bonds, self.comm)
         self.table = PairTable()
         self.tokens = {}            # BPE._tokens
@@ -448,8 +520,8 @@ class Learner:
             maxlen = int(self.comm.all_reduce(torch.tensor([maxlen], device=_dev()), "max").item())
         pw = [1]
         for _ in range(2 * maxlen + 2):
-            pw.append(pw[-1] * HASH_BASE % P61)
-        self.powtab = torch.tensor(pw, dtype=torch.int64, device=_dev())
+            pw.append(pw[-1] * HASH_BASE & M64)
+        self.powtab = torch.from_numpy(np.array(pw, dtype=np.uint64).view(np.int64)).to(_dev())
 
     def _h_key_dicts(self, r0s, nress):
         """compute_geo_key's dict for fully histogram-quantised windows (bpe.py:1225-1298); one batched gather"""
@@ -496,6 +568,35 @@ class Learner:
                 inner(tab)
                 e1.record()
                 self.k1_events.append((e0, e1, ts.T))
+        if self.mode == "H" and self.use_sketch:
+            if self.sketch is None:
+                self.sketch = SlotSketch(ts.T)
+            cs = 1 if 16 * ts.T > SlotSketch.STREAM_BYTES else 0
+
+            def pass1(slots_ptr, log2ns, variant, ctas):
+                ev = self.k1_events
+                if ev is not None:
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                _lib.call("gb_slot_count_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), HASH_BASE,
+                          slots_ptr, log2ns, None, variant | (8 * cs), ctas)
+                if ev is not None:
+                    e1.record()
+                    ev.append((e0, e1, ts.T))
+
+            def pass2(log2ns, cand_ptr, ncand_ptr, cap, tab):
+                ev = self.k1b_events
+                if ev is not None:
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                _lib.call("gb_cand_count_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), HASH_BASE,
+                          log2ns, cand_ptr, ncand_ptr, cap, *tab.ptrs(), _lib.ptr(tab.overflow), cs)
+                if ev is not None:
+                    e1.record()
+                    ev.append((e0, e1, ts.T))
+            r = self.sketch.count(pass1, pass2, ts.p("pos"), ts.p("len"))
+            if r is not None:
+                return r
         if self.mode == "H":
             return self.table.count(launch, ts.T, first_pos, ts.p("pos"), ts.p("len"))
         return self.table.count(launch, ts.T, first_pos)
@@ -540,7 +641,7 @@ class Learner:
         r = self._merge(key, n, None, None, bound=mx)
         if self.verify:
             if int(r[3]):
-                raise RuntimeError("61-bit content-hash collision detected (window bins differ); re-run with another HASH_BASE")
+                raise RuntimeError("64-bit content-hash collision detected (window bins differ); re-run with another HASH_BASE")
             if int(r[4]) != mx:
                 raise RuntimeError(f"flagged {int(r[4])} occurrences, histogram counted {mx}")
         self.n_steps += 1
@@ -604,7 +705,7 @@ class Learner:
         for part in comm.all_gather_object({k: v[0] for k, v in local.items()}):
             for k, v in part.items():
                 if strings.setdefault(k, v) != v:
-                    raise RuntimeError("61-bit content-hash collision across ranks (window bins differ)")
+                    raise RuntimeError("64-bit content-hash collision across ranks (window bins differ)")
         key_str, key = min((strings[k], k) for k in keys)
         n = len(self.tokens)
         self.tokens[n] = json.loads(key_str)
@@ -616,7 +717,7 @@ class Learner:
             _lib.call("gb_verify_windows_h", _lib.ptr(ts.idx), nocc, ts.p("pos"), ts.p("len"), _lib.ptr(self.rbins),
                       self.bb.R, local[key][1], local[key][2], _lib.ptr(ts.u32))
             if int(ts.u32[0].item()):
-                raise RuntimeError("61-bit content-hash collision detected (window bins differ)")
+                raise RuntimeError("64-bit content-hash collision detected (window bins differ)")
         self._merge(key, n, None, None)
         self.n_steps += 1
 
