@@ -218,6 +218,9 @@ def main():
         L.step()
     L.k1_events = []
     T_start = L.ts.T
+    lib = _lib.load()
+    if L.async_steps:
+        lib.gb_h_loop_time_k1(1)      # CUDA events around every k_slot_count launch inside the device-driven loop
     barrier()
     launches0 = _lib.launches
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -227,6 +230,7 @@ def main():
         while done < args.steps:
             L.step()
             done += 1
+        L.sync()            # device-driven loop: drain it (one D2H of the state block + step log) inside the timed region
         e1.record()
         barrier()
     ms = e0.elapsed_time(e1)
@@ -237,6 +241,15 @@ def main():
     launches = _lib.launches - launches0
     k1_ms = [a.elapsed_time(b) for a, b, _ in L.k1_events]
     k1_T = [t for _, _, t in L.k1_events]
+    if L.async_steps:
+        import ctypes
+        buf = (ctypes.c_float * (args.steps + 64))()
+        n = lib.gb_h_loop_k1_times(buf, len(buf))
+        lib.gb_h_loop_time_k1(0)
+        loop_ms = [float(buf[i]) for i in range(n) if buf[i] > 0]
+        nk = [e[2] for e in L.step_events[-args.steps:]]
+        loop_T = (T_start - np.concatenate([[0], np.cumsum(nk)[:-1]])).tolist()[:len(loop_ms)]
+        k1_ms, k1_T = loop_ms + k1_ms, loop_T + k1_T      # + the iterations that fell back to the host path
     bpt = 16 if args.mode == "H" else 8
     k1_avg_ms = float(np.mean(k1_ms))
     k1_bytes = bpt * float(np.mean(k1_T))
@@ -248,6 +261,10 @@ def main():
     distinct = int(sk.sout.cpu()[2]) if sk is not None else L.table.distinct   # sketch: non-zero slots (lower bound)
     k1_name = ("k_slot_count" if sk is not None else "k_pair_count") + ("<KeysH>" if args.mode == "H" else "<KeysM>")
     sk_rounds = list(sk.rounds) if sk is not None else None
+    loop_info = None
+    if L.hl is not None:
+        loop_info = {"device_iterations": L.hl.steps, "second_rounds": L.hl.r2, "halts_by_code": {L.HALT_NAMES[k]: v for k, v in L.hl.halts.items()},
+                     "max_ties": getattr(L.hl, "ntmax", 0), "kernels_per_iteration": lib.gb_h_loop_kernels_per_step()}
     pairs, top = L.ts.T - L.bb.S, L.pop_log[-1][0]
     T_end = L.ts.T
     k1_share = sum(k1_ms) / ms
@@ -305,7 +322,7 @@ def main():
                    "pairs": pairs, "distinct_over_pairs": distinct / max(pairs, 1), "last_top_count": top,
                    "residues_total": R * world},
         "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
-        "roofline": {"bound": "hbm", "kernel": k1_name, "resolve_rounds_1_2_fallback": sk_rounds,
+        "roofline": {"bound": "hbm", "kernel": k1_name, "resolve_rounds_1_2_fallback": sk_rounds, "device_loop": loop_info,
                      "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "avg_ms": k1_avg_ms, "algorithmic_bytes_per_launch": k1_bytes,
                      "bytes_per_token": bpt, "share_of_step": k1_share},

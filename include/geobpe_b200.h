@@ -196,6 +196,22 @@ int gb_pack_result(const uint32_t* out4, const int32_t* overflow, const uint64_t
                    const uint32_t* sout /* nullable: gb_slots_top's sout -> res[3] = sout[0] | sout[1] << 32 */,
                    int64_t* res, void* stream);
 
+/* ---- device-driven histogram-mode learn loop (bpe.py:1792-2166 BPE.step with rmsd_key None, N iterations without a
+ *      host round trip; csrc/k_hloop.cu).  args_host: int64 [gb_h_loop_nargs()] = device pointers and sizes in the order
+ *      of the HA_* enum in k_hloop.cu (state block hs u32[32] + hs64 u64[2], ping-pong token arrays, flags, scan scratch,
+ *      powtab, P, rbins, R, sketch buffers of gb_slot_count_h / gb_slots_top / gb_cand_count_h, tie list, JSON string
+ *      scratch, merge-event log, per-step log, Tmax = upper bound of the live-token count, streaming flag).
+ *      parity = which of the two token buffers is current at the first enqueued iteration.  Per iteration the device
+ *      picks the key with the largest pair count, breaks ties by the python string order of json.dumps(key, sort_keys=True)
+ *      (bpe.py:1149,1469), applies the merge with the left-to-right overlap rule and appends (key, count, example window,
+ *      event range) to the step log.  A condition it cannot resolve sets hs[2] (halt code) and later kernels no-op. */
+int gb_h_loop(const int64_t* args_host, int n_args, int nsteps, int parity, void* stream);
+int gb_h_loop_nargs(void);
+int gb_h_loop_kernels_per_step(void);
+/* CUDA-event timing of the pair-count kernel inside the loop: enable, run, synchronize, then read the per-launch ms */
+int gb_h_loop_time_k1(int enable);
+int gb_h_loop_k1_times(float* ms_host, int cap);
+
 /* ---- K4/K5/K6: NeRF windows, Kabsch RMSD, medoid assignment (tokenizer.py:347-363, nerf.py:84-210,
  *      angles_and_coords.py:238-317, algo.py:8-65,170-181, bpe.py:646-657) -------------------------- */
 /* coords f64 [Q][A][3] for windows starting at residue r0[q] spanning nres residues; A = atoms kept

@@ -49,6 +49,11 @@ SIGNATURES = {
     "gb_window_coords": [P, I64, I64, P, P, P, I64, I32, I32, P, P, F64, F64, F64, P, P, I32, P, P],
     "gb_kabsch_assign": [P, I64, I32, P, I32, P, P, P],
     "gb_rmsd_matrix": [P, I32, I32, P, P],
+    "gb_h_loop": [P, I32, I32, I32, P],
+    "gb_h_loop_nargs": [],
+    "gb_h_loop_kernels_per_step": [],
+    "gb_h_loop_time_k1": [I32],
+    "gb_h_loop_k1_times": [P, I32],
     "gb_last_error": [],
     "gb_abi_version": [],
     "gb_sm_count": [],
@@ -97,6 +102,16 @@ def call(name, *args):
     lib = load()
     rc = getattr(lib, name)(*args, stream())
     launches += KERNELS.get(name, 1)
+    if rc != 0:
+        raise RuntimeError(f"{name} failed ({rc}): {lib.gb_last_error().decode()}")
+
+
+def call_n(name, nkernels, *args):
+    """call() for an entry point that enqueues `nkernels` kernels"""
+    global launches
+    lib = load()
+    rc = getattr(lib, name)(*args, stream())
+    launches += nkernels
     if rc != 0:
         raise RuntimeError(f"{name} failed ({rc}): {lib.gb_last_error().decode()}")
 

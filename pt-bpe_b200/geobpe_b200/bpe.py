@@ -286,15 +286,33 @@ class BPE(_View):
         self._learner = None
         self._export = None
 
+    # `_tokens` is advanced by the device-driven learn loop: reading it drains the loop first
+    @property
+    def _tokens(self):
+        L = self.__dict__.get("_learner")
+        if L is not None:
+            L.sync()
+        return self.__dict__.get("_tokens_")
+
+    @_tokens.setter
+    def _tokens(self, v):
+        self.__dict__["_tokens_"] = v
+
     def __getstate__(self):
         """pickle layout of encode.py:403-427: vocabulary + hyper-parameters + materialised tokenizers; the device
         state (HBM buffers) is not part of the pickle"""
+        if self._learner is not None:
+            self._learner.sync()
         d = dict(self.__dict__)
         for k in ("_learner", "_export", "_ev_cache"):
             d[k] = None
+        d["_tokens"] = d.pop("_tokens_", None)
         return d
 
     def __setstate__(self, d):
+        d = dict(d)
+        if "_tokens" in d:
+            d["_tokens_"] = d.pop("_tokens")
         self.__dict__.update(d)
         for t in self.tokenizers:
             if getattr(t, "_mat", None) is None:

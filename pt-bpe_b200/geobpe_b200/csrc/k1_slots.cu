@@ -13,79 +13,7 @@
 //                          first position) in a small open-addressing table.  A key outside the candidate slots has
 //                          count <= its slot count < c1, so if the best exact count m1 equals c1 the exact ties are
 //                          all in the table; otherwise the host asks for the slots >= m1 and runs pass 2 once more.
-#include "common.cuh"
-#include "k1_keys.cuh"
-
-#define KS_THREADS 512
-#define KS_TILE (KS_THREADS * K1_VEC)
-#define KS_CACHE 8192                 // shared-memory hot stage per CTA: u32 tag + u32 count = 64 KB
-#define KS_EMPTY 0xFFFFFFFFu
-
-__device__ __forceinline__ u32 gb_slot_of(u64 key, int shift) {
-  return (u32)((key * 0x9E3779B97F4A7C15ull) >> shift);       // Fibonacci hashing: top log2(NS) bits
-}
-
-// CACHE: 0 none, 1 dynamic first-come claim, 2 static hot list (hot_tags u32 [KS_CACHE], KS_EMPTY = unused)
-template <class KF, bool AGG, int CACHE, bool DRY>
-__global__ void __launch_bounds__(KS_THREADS, 2) k_slot_count(KF kf, i64 T, u32* __restrict__ slots, int shift,
-                                                              const u32* __restrict__ hot_tags) {
-  extern __shared__ __align__(16) u32 ks_smem[];
-  u32* s_tag = ks_smem;
-  u32* s_cnt = ks_smem + KS_CACHE;
-  if (CACHE) {
-    for (int i = threadIdx.x; i < KS_CACHE; i += KS_THREADS) {
-      s_tag[i] = (CACHE == 2) ? hot_tags[i] : KS_EMPTY;
-      s_cnt[i] = 0;
-    }
-    __syncthreads();
-  }
-  u32 dry = 0;
-  // two tiles per iteration: both tiles' 128-bit loads are issued before the first shuffle waits on them
-  for (i64 base = (i64)blockIdx.x * (2 * KS_TILE); base < T; base += (i64)gridDim.x * (2 * KS_TILE)) {
-    const i64 ja = base + (i64)threadIdx.x * K1_VEC, jb = ja + KS_TILE;
-    typename KF::Raw ra, rb;
-    kf.ld(ja, T, ra);
-    kf.ld(jb, T, rb);
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      u64 key[K1_VEC];
-      if (half == 0) kf.fin(ja, T, ra, key); else kf.fin(jb, T, rb, key);
-#pragma unroll
-      for (int e = 0; e < K1_VEC; ++e) {
-        bool valid = key[e] != GB_EMPTY_KEY;
-        u32 slot = gb_slot_of(key[e], shift);
-        u32 c = 1;
-        if (AGG) {
-          unsigned grp = __match_any_sync(0xffffffffu, valid ? slot : KS_EMPTY);
-          c = __popc(grp);
-          valid = valid && ((unsigned)(__ffs(grp) - 1) == (threadIdx.x & 31));
-        }
-        if (DRY) { dry ^= slot * c; continue; }
-        if (!valid) continue;
-        if (CACHE) {
-          u32 cs = slot & (KS_CACHE - 1);
-          u32 tag = s_tag[cs];
-          if (CACHE == 1 && tag == KS_EMPTY) {
-            tag = atomicCAS(&s_tag[cs], KS_EMPTY, slot);
-            if (tag == KS_EMPTY) tag = slot;
-          }
-          if (tag == slot) atomicAdd(&s_cnt[cs], c);
-          else atomicAdd(slots + slot, c);
-        } else {
-          atomicAdd(slots + slot, c);
-        }
-      }
-    }
-  }
-  if (DRY) { if (dry == 0x12345u) slots[0] = dry; return; }
-  if (CACHE) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < KS_CACHE; i += KS_THREADS) {
-      u32 c = s_cnt[i];
-      if (c) atomicAdd(slots + s_tag[i], c);
-    }
-  }
-}
+#include "k1_sketch.cuh"
 
 template <class KF>
 static int launch_slot_count(KF kf, i64 T, u32* slots, int log2ns, const u32* hot_tags, int variant, int ctas_per_sm,
@@ -104,7 +32,7 @@ static int launch_slot_count(KF kf, i64 T, u32* slots, int log2ns, const u32* ho
 #define KS_LAUNCH(AGG, CACHE, DRY)                                                                                 \
   do {                                                                                                             \
     if (smem) GB_CK(cudaFuncSetAttribute(k_slot_count<KF, AGG, CACHE, DRY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    k_slot_count<KF, AGG, CACHE, DRY><<<blocks, KS_THREADS, smem, st>>>(kf, T, slots, shift, hot_tags);            \
+    k_slot_count<KF, AGG, CACHE, DRY><<<blocks, KS_THREADS, smem, st>>>(kf, T, slots, shift, hot_tags, nullptr);            \
   } while (0)
   if (dry) { if (agg) KS_LAUNCH(true, 0, true); else KS_LAUNCH(false, 0, true); }
   else if (cache == 0) { if (agg) KS_LAUNCH(true, 0, false); else KS_LAUNCH(false, 0, false); }
@@ -135,7 +63,6 @@ extern "C" int gb_slot_count_h(const uint64_t* hsh, const uint32_t* glue, const 
 // ---- scan: sout u32 [4] = {max slot count c1, #candidate slots, #non-zero slots, 0} --------------------------
 // One block per chunk of KS_CHUNK slots; the per-chunk maxima (bmax) let the collect pass skip every chunk that
 // cannot hold a candidate, so listing the top slots costs one read of the counters, not two.
-#define KS_CHUNK 4096
 __global__ void __launch_bounds__(256) k_slots_max(const uint4* __restrict__ slots4, u32* __restrict__ bmax,
                                                     u32* __restrict__ sout) {
   __shared__ u32 s_mx[8], s_nz[8];
@@ -201,66 +128,6 @@ extern "C" int gb_slots_top(const uint32_t* slots, int log2ns, uint32_t thr_host
 }
 
 // ---- pass 2: exact (key, count, first position) of the pairs that fall into candidate slots ------------------
-#define KC_SET 8192          // shared open-addressing set of candidate slot ids (load <= 1/2 at cap 4096)
-#define KC_LINEAR 8
-template <class KF>
-__global__ void __launch_bounds__(KS_THREADS, 2) k_cand_count(KF kf, i64 T, int shift, const u32* __restrict__ cand,
-                                                              const u32* __restrict__ n_cand_dev, u32 cap,
-                                                              u64* __restrict__ tk, u32* __restrict__ tc, u32* __restrict__ tm,
-                                                              u64 mask, int32_t* __restrict__ overflow) {
-  __shared__ u32 s_set[KC_SET];
-  __shared__ u32 s_lin[KC_LINEAR];
-  u32 n = *n_cand_dev;
-  if (n == 0) return;
-  if (n > cap) { if (blockIdx.x == 0 && threadIdx.x == 0) atomicExch(overflow, 2); return; }
-  const bool linear = n <= KC_LINEAR;
-  if (linear) {
-    if (threadIdx.x < KC_LINEAR) s_lin[threadIdx.x] = threadIdx.x < n ? cand[threadIdx.x] : KS_EMPTY;
-  } else {
-    for (int i = threadIdx.x; i < KC_SET; i += KS_THREADS) s_set[i] = KS_EMPTY;
-    __syncthreads();
-    for (u32 i = threadIdx.x; i < n; i += KS_THREADS) {
-      u32 v = cand[i], s = (v * 0x9E3779B1u) >> 19;       // 13 bits
-      while (true) {
-        u32 prev = atomicCAS(&s_set[s], KS_EMPTY, v);
-        if (prev == KS_EMPTY || prev == v) break;
-        s = (s + 1) & (KC_SET - 1);
-      }
-    }
-  }
-  __syncthreads();
-  for (i64 base = (i64)blockIdx.x * (2 * KS_TILE); base < T; base += (i64)gridDim.x * (2 * KS_TILE)) {
-    const i64 ja = base + (i64)threadIdx.x * K1_VEC, jb = ja + KS_TILE;
-    typename KF::Raw ra, rb;
-    kf.ld(ja, T, ra);
-    kf.ld(jb, T, rb);
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      u64 key[K1_VEC];
-      const i64 j0 = half ? jb : ja;
-      if (half == 0) kf.fin(ja, T, ra, key); else kf.fin(jb, T, rb, key);
-#pragma unroll
-      for (int e = 0; e < K1_VEC; ++e) {
-        if (key[e] == GB_EMPTY_KEY) continue;
-        u32 slot = gb_slot_of(key[e], shift);
-        bool hit = false;
-        if (linear) {
-#pragma unroll
-          for (int i = 0; i < KC_LINEAR; ++i) hit |= (s_lin[i] == slot);
-        } else {
-          u32 s = (slot * 0x9E3779B1u) >> 19;
-          while (true) {
-            u32 v = s_set[s];
-            if (v == slot) { hit = true; break; }
-            if (v == KS_EMPTY) break;
-            s = (s + 1) & (KC_SET - 1);
-          }
-        }
-        if (hit && !gb_gtable_add(tk, tc, tm, mask, key[e], 1u, (u32)(j0 + e))) atomicExch(overflow, 1);
-      }
-    }
-  }
-}
 template <class KF>
 static int launch_cand_count(KF kf, i64 T, int log2ns, const u32* cand, const u32* n_cand_dev, int cap, u64* tk, u32* tc,
                              u32* tm, i64 M, int32_t* overflow, cudaStream_t st) {
@@ -270,7 +137,7 @@ static int launch_cand_count(KF kf, i64 T, int log2ns, const u32* cand, const u3
   int sms = gb_sm_count();
   if (sms <= 0) sms = 148;
   int blocks = gb_blocks_for(T, 2 * KS_TILE, sms * 2);
-  k_cand_count<KF><<<blocks, KS_THREADS, 0, st>>>(kf, T, 64 - log2ns, cand, n_cand_dev, (u32)cap, tk, tc, tm, (u64)(M - 1), overflow);
+  k_cand_count<KF><<<blocks, KS_THREADS, 0, st>>>(kf, T, 64 - log2ns, cand, n_cand_dev, (u32)cap, tk, tc, tm, (u64)(M - 1), overflow, nullptr, 1);
   GB_LAUNCH_CK();
   return 0;
 }

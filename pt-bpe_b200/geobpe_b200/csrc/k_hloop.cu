@@ -1,0 +1,518 @@
+// Device-driven histogram-mode learn loop: BPE.step (bpe.py:1792-2166 with rmsd_key None) for N iterations without a
+// host round trip.  Everything the host used to decide per iteration lives in a device state block `hs`
+// (k1_sketch.cuh): the live-token count, the popped key, the reference's tie-break (python string order of
+// json.dumps(key_dict, sort_keys=True), bpe.py:1149,1469 -- evaluated here by materialising the tied keys' JSON
+// strings), the overlap rule, the merge-event log and a per-step record the host reads back in bulk.
+// Any condition the device cannot resolve (more ties than HL_TB_CAP, more candidate slots than the cap, a content-hash
+// collision, a full log) sets hs[HS_HALT]; every later kernel then returns immediately, the host handles that one
+// iteration on its own path and re-enters the loop.
+#include "k1_sketch.cuh"
+
+#define HL_TB_CAP 128           // ties resolved on the device
+#define HL_TIE_LIST 256         // tie list entries kept (>= HL_TB_CAP)
+
+enum { HALT_TIES = 1, HALT_CAND = 2, HALT_COLLISION = 3, HALT_TABLE = 4, HALT_EVLOG = 5, HALT_EMPTY = 6, HALT_STEPS = 7,
+       HALT_COUNT = 8 };
+
+__device__ __forceinline__ void hl_halt(u32* hs, u32 code) {
+  if (atomicCAS(&hs[HS_HALT], 0u, code) == 0u) hs[HS_HALT_STEP] = hs[HS_STEP];
+}
+
+// ---- per-iteration reset ---------------------------------------------------------------------------------------
+__global__ void hl_begin(u32* __restrict__ hs) {
+  if (hs[HS_HALT]) return;
+  if (hs[HS_STEP] >= hs[HS_MAXSTEPS]) { hl_halt(hs, HALT_STEPS); return; }
+  hs[HS_C1] = 0; hs[HS_NCAND] = 0; hs[HS_NZ] = 0; hs[HS_PAD0] = 0;
+  hs[HS_M1] = 0; hs[HS_NT] = 0; hs[HS_ND] = 0; hs[HS_ROUND2] = 0;
+  hs[HS_MISMATCH] = 0; hs[HS_FLAGGED] = 0; hs[HS_OVF] = 0; hs[HS_NEWT] = 0;
+}
+
+// ---- slot scan -----------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) hl_slots_max(const uint4* __restrict__ slots4, u32* __restrict__ bmax, u32* __restrict__ hs) {
+  if (hs[HS_HALT]) return;
+  __shared__ u32 s_mx[8], s_nz[8];
+  const uint4* p = slots4 + (i64)blockIdx.x * (KS_CHUNK / 4);
+  uint4 v[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) v[k] = p[k * 256 + threadIdx.x];
+  u32 mx = 0, nz = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    mx = max(max(mx, v[k].x), max(max(v[k].y, v[k].z), v[k].w));
+    nz += (v[k].x != 0) + (v[k].y != 0) + (v[k].z != 0) + (v[k].w != 0);
+  }
+  for (int o = 16; o; o >>= 1) {
+    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    nz += __shfl_xor_sync(0xffffffffu, nz, o);
+  }
+  if ((threadIdx.x & 31) == 0) { s_mx[threadIdx.x >> 5] = mx; s_nz[threadIdx.x >> 5] = nz; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w) { mx = max(mx, s_mx[w]); nz += s_nz[w]; }
+    bmax[blockIdx.x] = mx;
+    if (mx) atomicMax(&hs[HS_C1], mx);
+    if (nz) atomicAdd(&hs[HS_NZ], nz);
+  }
+}
+// round 1: thr = min(c1, 0.9 * previous max) -- the max count never grows from one iteration to the next, so the exact
+// max is almost always >= thr and one candidate pass is conclusive.  round 2: thr = best exact count of round 1.
+__device__ __forceinline__ u32 hl_thr(const u32* hs, int round) {
+  if (round == 2) return hs[HS_THR];
+  u32 c1 = hs[HS_C1], mp = hs[HS_MPREV];
+  u32 t = mp ? max(1u, (u32)(((u64)mp * 9ull) / 10ull)) : c1;
+  return min(c1, t);
+}
+__global__ void __launch_bounds__(256) hl_slots_collect(const uint4* __restrict__ slots4, const u32* __restrict__ bmax,
+                                                         u32* __restrict__ hs, int round, u32* __restrict__ cand, u32 cap) {
+  if (hs[HS_HALT] || (round == 2 && !hs[HS_ROUND2])) return;
+  const u32 thr = hl_thr(hs, round);
+  if (round == 1 && blockIdx.x == 0 && threadIdx.x == 0) hs[HS_THR] = thr;
+  if (thr == 0 || bmax[blockIdx.x] < thr) return;
+  const i64 base4 = (i64)blockIdx.x * (KS_CHUNK / 4);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    i64 i = base4 + k * 256 + threadIdx.x;
+    uint4 v = slots4[i];
+    u32 a[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e)
+      if (a[e] >= thr) {
+        u32 q = atomicAdd(&hs[HS_NCAND], 1u);
+        if (q < cap) cand[q] = (u32)(4 * i + e);
+      }
+  }
+}
+__global__ void __launch_bounds__(256) hl_table_clear(u64* __restrict__ tk, u32* __restrict__ tc, u32* __restrict__ tm, i64 M,
+                                                       const u32* __restrict__ hs, int round) {
+  if (hs[HS_HALT] || (round == 2 && !hs[HS_ROUND2])) return;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (i64)gridDim.x * blockDim.x) {
+    tk[i] = GB_EMPTY_KEY; tc[i] = 0u; tm[i] = 0xFFFFFFFFu;
+  }
+}
+
+// ---- exact argmax over the small table + conclusiveness test (one block) -----------------------------------------
+__global__ void __launch_bounds__(1024) hl_decide(const u64* __restrict__ tk, const u32* __restrict__ tc, const u32* __restrict__ tm,
+                                                   i64 M, u32* __restrict__ hs, int round, u64* __restrict__ tie_keys,
+                                                   u32* __restrict__ tie_min, u32 cap) {
+  if (hs[HS_HALT] || (round == 2 && !hs[HS_ROUND2])) return;
+  __shared__ u32 s_mx[32], s_nd[32], s_nt;
+  u32 mx = 0, nd = 0;
+  for (i64 i = threadIdx.x; i < M; i += blockDim.x) { u32 c = tc[i]; mx = max(mx, c); nd += c != 0; }
+  for (int o = 16; o; o >>= 1) { mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o)); nd += __shfl_xor_sync(0xffffffffu, nd, o); }
+  if ((threadIdx.x & 31) == 0) { s_mx[threadIdx.x >> 5] = mx; s_nd[threadIdx.x >> 5] = nd; }
+  if (threadIdx.x == 0) s_nt = 0;
+  __syncthreads();
+  mx = 0; nd = 0;
+  for (int w = 0; w < 32; ++w) { mx = max(mx, s_mx[w]); nd += s_nd[w]; }
+  if (mx) {
+    for (i64 i = threadIdx.x; i < M; i += blockDim.x)
+      if (tc[i] == mx) {
+        u32 k = atomicAdd(&s_nt, 1u);
+        if (k < HL_TIE_LIST) { tie_keys[k] = tk[i]; tie_min[k] = tm[i]; }
+      }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    hs[HS_M1] = mx; hs[HS_NT] = s_nt; hs[HS_ND] = nd;
+    if (hs[HS_C1] == 0) { hl_halt(hs, HALT_EMPTY); return; }
+    if (hs[HS_OVF] == 1 || (u64)nd * 2 > (u64)M) { hl_halt(hs, HALT_TABLE); return; }
+    const bool cand_over = hs[HS_NCAND] > cap || hs[HS_OVF] == 2;
+    if (round == 1) {
+      if (cand_over) {                        // too many slots above 0.9 * previous max: retry with the top slots only
+        hs[HS_ROUND2] = 1; hs[HS_THR] = hs[HS_C1]; hs[HS_NCAND] = 0; hs[HS_OVF] = 0; hs[HS_R2COUNT] += 1;
+      } else if (mx < hs[HS_THR]) {           // inconclusive: a key outside the candidates could reach mx
+        hs[HS_ROUND2] = 1; hs[HS_THR] = max(mx, 1u); hs[HS_NCAND] = 0; hs[HS_R2COUNT] += 1;
+      }
+    } else {
+      if (cand_over || mx < hs[HS_THR]) hl_halt(hs, HALT_CAND);
+    }
+  }
+}
+
+// ---- the reference's tie-break on the device -------------------------------------------------------------------
+// json.dumps(compute_geo_key's dict, sort_keys=True) of a fully histogram-quantised window (bpe.py:1225-1298, 1149):
+//   {"0C:1N": [0 x m], "C:1N:1CA": [..], "CA:C": [0 x nres], "CA:C:1N": [..m], "N:CA": [0 x nres], "omega": [..],
+//    "phi": [..], "psi": [..m], "tau": [..nres]}      (omega / C:1N:1CA / phi only when nres > 1; bond bins are 0
+// with std_bonds; m = nres - 1 when the window ends its backbone).  Residue-major rbins slots: 3 tau, 4 CA:C:1N,
+// 5 psi, 6 omega, 7 C:1N:1CA, 8 phi(r+1).
+__device__ __forceinline__ int hl_puts(char* p, int o, const char* s) {
+  while (*s) p[o++] = *s++;
+  return o;
+}
+__device__ __forceinline__ int hl_putu(char* p, int o, u32 v) {
+  char d[10];
+  int n = 0;
+  do { d[n++] = (char)('0' + v % 10u); v /= 10u; } while (v);
+  while (n) p[o++] = d[--n];
+  return o;
+}
+__device__ __forceinline__ int hl_zero_list(char* p, int o, u32 n) {
+  p[o++] = '[';
+  for (u32 k = 0; k < n; ++k) { if (k) { p[o++] = ','; p[o++] = ' '; } p[o++] = '0'; }
+  p[o++] = ']';
+  return o;
+}
+__device__ __forceinline__ int hl_bin_list(char* p, int o, const u16* __restrict__ row, u32 n) {
+  p[o++] = '[';
+  for (u32 k = 0; k < n; ++k) { if (k) { p[o++] = ','; p[o++] = ' '; } o = hl_putu(p, o, row[k]); }
+  p[o++] = ']';
+  return o;
+}
+__device__ int hl_json_key(char* p, const u16* __restrict__ rbins, i64 R, u32 r0, u32 nres) {
+  const u32 m = (rbins[4 * R + r0 + nres - 1] == GB_NOBIN) ? nres - 1 : nres;
+  int o = 0;
+  o = hl_puts(p, o, "{\"0C:1N\": ");      o = hl_zero_list(p, o, m);
+  if (nres > 1) { o = hl_puts(p, o, ", \"C:1N:1CA\": "); o = hl_bin_list(p, o, rbins + 7 * R + r0, nres - 1); }
+  o = hl_puts(p, o, ", \"CA:C\": ");      o = hl_zero_list(p, o, nres);
+  o = hl_puts(p, o, ", \"CA:C:1N\": ");   o = hl_bin_list(p, o, rbins + 4 * R + r0, m);
+  o = hl_puts(p, o, ", \"N:CA\": ");      o = hl_zero_list(p, o, nres);
+  if (nres > 1) {
+    o = hl_puts(p, o, ", \"omega\": ");   o = hl_bin_list(p, o, rbins + 6 * R + r0, nres - 1);
+    o = hl_puts(p, o, ", \"phi\": ");     o = hl_bin_list(p, o, rbins + 8 * R + r0, nres - 1);
+  }
+  o = hl_puts(p, o, ", \"psi\": ");       o = hl_bin_list(p, o, rbins + 5 * R + r0, m);
+  o = hl_puts(p, o, ", \"tau\": ");       o = hl_bin_list(p, o, rbins + 3 * R + r0, nres);
+  p[o++] = '}';
+  const int end = (o + 127) & ~127;       // zero padding to the next 128-byte boundary (warp-wide compare)
+  for (int k = o; k < end; ++k) p[k] = 0;
+  return o;
+}
+// warp-cooperative strcmp of two zero-padded, 128-byte aligned strings: true when a < b
+__device__ __forceinline__ bool hl_less(const char* a, const char* b, int la, int lb) {
+  const unsigned lane = threadIdx.x & 31;
+  const int n = (min(la, lb) + 127) & ~127;
+  for (int off = 0; off < n; off += 128) {
+    u32 wa = reinterpret_cast<const u32*>(a + off)[lane], wb = reinterpret_cast<const u32*>(b + off)[lane];
+    unsigned diff = __ballot_sync(0xffffffffu, wa != wb);
+    if (diff) {
+      int l = __ffs(diff) - 1;
+      u32 xa = __byte_perm(__shfl_sync(0xffffffffu, wa, l), 0, 0x0123);   // memory order -> most significant first
+      u32 xb = __byte_perm(__shfl_sync(0xffffffffu, wb, l), 0, 0x0123);
+      return xa < xb;
+    }
+  }
+  return la < lb;
+}
+__global__ void __launch_bounds__(HL_TB_CAP) hl_tiebreak(u32* __restrict__ hs, u64* __restrict__ hs64, const u64* __restrict__ tie_keys,
+                                                         const u32* __restrict__ tie_min, const u32* __restrict__ pos,
+                                                         const u32* __restrict__ len, const u16* __restrict__ rbins, i64 R,
+                                                         char* __restrict__ strbuf, int stride) {
+  if (hs[HS_HALT]) return;
+  __shared__ int s_best[HL_TB_CAP], s_len[HL_TB_CAP];
+  const u32 nt = hs[HS_NT];
+  if (nt == 0) { if (threadIdx.x == 0) hl_halt(hs, HALT_EMPTY); return; }
+  if (nt > HL_TB_CAP) { if (threadIdx.x == 0) { hs[HS_NTMAX] = max(hs[HS_NTMAX], nt); hl_halt(hs, HALT_TIES); } return; }
+  const u32 i = threadIdx.x;
+  if (nt > 1) {
+    if (i < nt) {
+      u32 j = tie_min[i];
+      u32 nres = len[j] + len[j + 1];
+      int need = 39 * (int)nres + 200;
+      if (need > stride) { hl_halt(hs, HALT_TIES); s_len[i] = 0; }
+      else s_len[i] = hl_json_key(strbuf + (size_t)i * stride, rbins, R, pos[j], nres);
+    }
+    s_best[i] = (int)i;
+    __syncthreads();
+    if (hs[HS_HALT]) return;
+    const unsigned warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (u32 s = 1; s < nt; s <<= 1) {
+      for (u32 a = warp * 2 * s; a + s < nt; a += nw * 2 * s) {
+        int ia = s_best[a], ib = s_best[a + s];
+        bool b_less = hl_less(strbuf + (size_t)ib * stride, strbuf + (size_t)ia * stride, s_len[ib], s_len[ia]);
+        if ((threadIdx.x & 31) == 0 && b_less) s_best[a] = ib;
+      }
+      __syncthreads();
+    }
+  }
+  if (threadIdx.x == 0) {
+    int w = nt > 1 ? s_best[0] : 0;
+    u32 j = tie_min[w];
+    hs64[0] = tie_keys[w];
+    hs[HS_WIN_J] = j; hs[HS_WIN_R0] = pos[j]; hs[HS_WIN_NRES] = len[j] + len[j + 1]; hs[HS_WIN_CNT] = hs[HS_M1];
+    hs[HS_NTMAX] = max(hs[HS_NTMAX], nt);
+  }
+}
+
+// ---- K2 on the device state: flag the winner's occurrences + exact window check, overlap rule, compaction ---------
+template <bool CS>
+__global__ void __launch_bounds__(KS_THREADS, 2) hl_flag_verify(KeysHT<CS> kf, u32* __restrict__ hs, const u64* __restrict__ hs64,
+                                                                u8* __restrict__ flags, const u32* __restrict__ pos,
+                                                                const u32* __restrict__ len, const u16* __restrict__ rbins, i64 R) {
+  if (hs[HS_HALT]) return;
+  const i64 T = (i64)hs[HS_T];
+  const u64 win = hs64[0];
+  const u32 ref_r0 = hs[HS_WIN_R0], nres = hs[HS_WIN_NRES];
+  for (i64 base = (i64)blockIdx.x * (2 * KS_TILE); base < T; base += (i64)gridDim.x * (2 * KS_TILE)) {
+    const i64 ja = base + (i64)threadIdx.x * K1_VEC, jb = ja + KS_TILE;
+    typename KeysHT<CS>::Raw ra, rb;
+    kf.ld(ja, T, ra);
+    kf.ld(jb, T, rb);
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      u64 key[K1_VEC];
+      const i64 j0 = half ? jb : ja;
+      if (half == 0) kf.fin(ja, T, ra, key); else kf.fin(jb, T, rb, key);
+      u8 f[K1_VEC];
+#pragma unroll
+      for (int e = 0; e < K1_VEC; ++e) f[e] = (key[e] == win) ? 1 : 0;
+      if (j0 + K1_VEC <= T) *reinterpret_cast<uchar4*>(flags + j0) = make_uchar4(f[0], f[1], f[2], f[3]);
+      else {
+#pragma unroll
+        for (int e = 0; e < K1_VEC; ++e) if (j0 + e < T) flags[j0 + e] = f[e];
+      }
+#pragma unroll
+      for (int e = 0; e < K1_VEC; ++e) {
+        if (!f[e]) continue;
+        const i64 j = j0 + e;
+        atomicAdd(&hs[HS_FLAGGED], 1u);
+        const u32 r0 = pos[j];
+        bool bad = (len[j] + len[j + 1]) != nres;
+        for (u32 slot = 3; slot < 9 && !bad; ++slot) {
+          const u32 n = (slot >= 6) ? nres - 1 : nres;   // glue of the last residue lies outside the window
+          for (u32 k = 0; k < n; ++k)
+            if (rbins[(i64)slot * R + r0 + k] != rbins[(i64)slot * R + ref_r0 + k]) { bad = true; break; }
+        }
+        if (bad) atomicAdd(&hs[HS_MISMATCH], 1u);
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) hl_resolve(u32* __restrict__ hs, u8* __restrict__ flags) {
+  if (hs[HS_HALT]) return;
+  const bool t0 = blockIdx.x == 0 && threadIdx.x == 0;
+  if (hs[HS_MISMATCH]) { if (t0) hl_halt(hs, HALT_COLLISION); return; }
+  if (hs[HS_FLAGGED] != hs[HS_WIN_CNT]) { if (t0) hl_halt(hs, HALT_COUNT); return; }
+  if (hs[HS_EVN] + hs[HS_FLAGGED] > hs[HS_EVCAP]) { if (t0) hl_halt(hs, HALT_EVLOG); return; }
+  const i64 T = (i64)hs[HS_T];
+  for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < T; j += (i64)gridDim.x * blockDim.x) {
+    if ((flags[j] & 1) && !(j > 0 && (flags[j - 1] & 1))) {
+      i64 i = j;
+      bool keep = true;
+      while (i < T && (flags[i] & 1)) {      // runs never cross a backbone: the last token's pair is never flagged
+        if (keep) flags[i] = 3;
+        keep = !keep;
+        ++i;
+      }
+    }
+  }
+}
+
+#define HL_CH_THREADS 256
+#define HL_CH_ITEMS 8
+#define HL_CHUNK (HL_CH_THREADS * HL_CH_ITEMS)
+// token i survives unless pair (i-1, i) was kept (flags bit1 on i-1)
+__device__ __forceinline__ bool hl_survives(const u8* __restrict__ f, i64 i) { return !(i > 0 && (f[i - 1] & 2)); }
+
+__global__ void __launch_bounds__(HL_CH_THREADS) hl_count(const u32* __restrict__ hs, const u8* __restrict__ flags, u32* __restrict__ bsum) {
+  if (hs[HS_HALT]) return;
+  const i64 T = (i64)hs[HS_T];
+  const i64 base = (i64)blockIdx.x * HL_CHUNK;
+  if (base >= T) return;
+  __shared__ u32 wsum[HL_CH_THREADS / 32];
+  u32 c = 0;
+#pragma unroll
+  for (int it = 0; it < HL_CH_ITEMS; ++it) {
+    i64 i = base + it * HL_CH_THREADS + threadIdx.x;
+    if (i < T && hl_survives(flags, i)) ++c;
+  }
+  for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    u32 t = 0;
+    for (int w = 0; w < HL_CH_THREADS / 32; ++w) t += wsum[w];
+    bsum[blockIdx.x] = t;
+  }
+}
+// in-place exclusive scan of bsum[0..nb), total -> hs[HS_NEWT] (single block)
+__global__ void __launch_bounds__(1024) hl_scan(u32* __restrict__ hs, u32* __restrict__ bsum) {
+  if (hs[HS_HALT]) return;
+  const i64 nb = ((i64)hs[HS_T] + HL_CHUNK - 1) / HL_CHUNK;
+  __shared__ u32 wtot[32];
+  __shared__ u32 carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (i64 base = 0; base < nb; base += 1024) {
+    i64 i = base + threadIdx.x;
+    u32 v = (i < nb) ? bsum[i] : 0u;
+    u32 x = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      u32 y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= (unsigned)o) x += y;
+    }
+    if (lane == 31) wtot[warp] = x;
+    __syncthreads();
+    u32 woff = 0, tot = 0;
+    for (unsigned w = 0; w < 32; ++w) {
+      u32 t = wtot[w];
+      if (w < warp) woff += t;
+      tot += t;
+    }
+    u32 carry = carry_s;
+    if (i < nb) bsum[i] = carry + woff + x - v;
+    __syncthreads();
+    if (threadIdx.x == 0) carry_s = carry + tot;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) hs[HS_NEWT] = carry_s;
+}
+struct HLTok { const u64* hsh; const u32* glue; const u32* pos; const u32* len; const u32* tid;
+               u64* hsh_o; u32* glue_o; u32* pos_o; u32* len_o; u32* tid_o; };
+// compaction + merge + event log: the k-th kept occurrence (in token order) is the (i - o)-th, because every kept
+// occurrence before token i removed exactly one token
+__global__ void __launch_bounds__(HL_CH_THREADS) hl_scatter(const u32* __restrict__ hs, const u64* __restrict__ hs64,
+                                                            const u8* __restrict__ flags, HLTok a, const u32* __restrict__ boff,
+                                                            u32* __restrict__ ev_left, u32* __restrict__ ev_right, u32* __restrict__ ev_p) {
+  if (hs[HS_HALT]) return;
+  const i64 T = (i64)hs[HS_T];
+  const i64 base = (i64)blockIdx.x * HL_CHUNK;
+  if (base >= T) return;
+  __shared__ u32 wsum[HL_CH_THREADS / 32];
+  const u64 key = hs64[0];
+  const u32 new_tid = hs[HS_NTOK], ev0 = hs[HS_EVN];
+  u32 run = boff[blockIdx.x];
+#pragma unroll
+  for (int it = 0; it < HL_CH_ITEMS; ++it) {
+    i64 i = base + it * HL_CH_THREADS + threadIdx.x;
+    bool f = (i < T) && hl_survives(flags, i);
+    u32 tot;
+    u32 ex = gb_block_excl_scan_flag(f, wsum, tot);
+    if (f) {
+      u32 o = run + ex;
+      a.pos_o[o] = a.pos[i];
+      if (flags[i] & 2) {                    // token i absorbs token i+1
+        a.glue_o[o] = a.glue[i + 1];
+        a.len_o[o] = a.len[i] + a.len[i + 1];
+        a.tid_o[o] = new_tid;
+        a.hsh_o[o] = key;
+        u32 q = ev0 + (u32)(i - o);
+        ev_left[q] = a.pos[i]; ev_right[q] = a.pos[i + 1]; ev_p[q] = 0u;
+      } else {
+        a.glue_o[o] = a.glue[i];
+        a.len_o[o] = a.len[i];
+        a.tid_o[o] = a.tid[i];
+        a.hsh_o[o] = a.hsh[i];
+      }
+    }
+    run += tot;
+  }
+}
+__global__ void hl_end(u32* __restrict__ hs, const u64* __restrict__ hs64, u64* __restrict__ log_key, u32* __restrict__ log_cnt,
+                       u32* __restrict__ log_r0, u32* __restrict__ log_nres, u32* __restrict__ log_evstart, u32* __restrict__ log_nk) {
+  if (hs[HS_HALT]) return;
+  const u32 s = hs[HS_STEP], T = hs[HS_T], newT = hs[HS_NEWT], nk = T - newT;
+  log_key[s] = hs64[0]; log_cnt[s] = hs[HS_WIN_CNT]; log_r0[s] = hs[HS_WIN_R0]; log_nres[s] = hs[HS_WIN_NRES];
+  log_evstart[s] = hs[HS_EVN]; log_nk[s] = nk;
+  hs[HS_EVN] += nk; hs[HS_T] = newT; hs[HS_MPREV] = hs[HS_WIN_CNT]; hs[HS_STEP] = s + 1; hs[HS_NTOK] += 1;
+}
+
+// ---- host entry: enqueue `nsteps` iterations -------------------------------------------------------------------------
+enum { HA_HS = 0, HA_HS64, HA_HSH0, HA_HSH1, HA_GLUE0, HA_GLUE1, HA_POS0, HA_POS1, HA_LEN0, HA_LEN1, HA_TID0, HA_TID1,
+       HA_FLAGS, HA_SCRATCH, HA_POWTAB, HA_P, HA_RBINS, HA_R, HA_SLOTS, HA_LOG2NS, HA_BMAX, HA_CAND, HA_CAP, HA_VARIANT,
+       HA_CTAS, HA_TK, HA_TC, HA_TM, HA_M, HA_TIEK, HA_TIEM, HA_STRBUF, HA_STRIDE, HA_EVL, HA_EVR, HA_EVP, HA_LKEY,
+       HA_LCNT, HA_LR0, HA_LNRES, HA_LEVS, HA_LNK, HA_TMAX, HA_STREAMING, HA_N };
+
+// optional CUDA-event timing of the pair-count kernel inside the loop (bench.py's roofline leg)
+#include <vector>
+static bool g_time_k1 = false;
+static std::vector<cudaEvent_t> g_ev;
+static size_t g_ev_used = 0;
+static cudaEvent_t hl_event() {
+  if (g_ev_used == g_ev.size()) { cudaEvent_t e; cudaEventCreate(&e); g_ev.push_back(e); }
+  return g_ev[g_ev_used++];
+}
+
+template <bool CS>
+static int h_loop_impl(const int64_t* a, int nsteps, int parity, cudaStream_t st) {
+  u32* hs = (u32*)a[HA_HS];
+  u64* hs64 = (u64*)a[HA_HS64];
+  u64* hsh[2] = {(u64*)a[HA_HSH0], (u64*)a[HA_HSH1]};
+  u32* glue[2] = {(u32*)a[HA_GLUE0], (u32*)a[HA_GLUE1]};
+  u32* pos[2] = {(u32*)a[HA_POS0], (u32*)a[HA_POS1]};
+  u32* len[2] = {(u32*)a[HA_LEN0], (u32*)a[HA_LEN1]};
+  u32* tid[2] = {(u32*)a[HA_TID0], (u32*)a[HA_TID1]};
+  u8* flags = (u8*)a[HA_FLAGS];
+  u32* scratch = (u32*)a[HA_SCRATCH];
+  const u64* powtab = (const u64*)a[HA_POWTAB];
+  const u64 P = (u64)a[HA_P];
+  const u16* rbins = (const u16*)a[HA_RBINS];
+  const i64 R = a[HA_R];
+  u32* slots = (u32*)a[HA_SLOTS];
+  const int log2ns = (int)a[HA_LOG2NS];
+  u32* bmax = (u32*)a[HA_BMAX];
+  u32* cand = (u32*)a[HA_CAND];
+  const int cap = (int)a[HA_CAP];
+  const int cache = ((int)a[HA_VARIANT] >> 1) & 3;
+  const int ctas = a[HA_CTAS] > 0 ? (int)a[HA_CTAS] : 2;
+  u64* tk = (u64*)a[HA_TK]; u32* tc = (u32*)a[HA_TC]; u32* tm = (u32*)a[HA_TM];
+  const i64 M = a[HA_M];
+  u64* tie_keys = (u64*)a[HA_TIEK]; u32* tie_min = (u32*)a[HA_TIEM];
+  char* strbuf = (char*)a[HA_STRBUF];
+  const int stride = (int)a[HA_STRIDE];
+  const i64 Tmax = a[HA_TMAX];
+  if (log2ns < 12 || log2ns > 30 || M <= 0 || (M & (M - 1)) || cap > KC_SET / 2 || cache > 1 || (stride & 127) || Tmax < 2) {
+    gb_set_error("gb_h_loop: bad arguments (log2ns %d, M %lld, cap %d, cache %d, stride %d, Tmax %lld)", log2ns, (long long)M, cap,
+                 cache, stride, (long long)Tmax);
+    return -2;
+  }
+  int sms = gb_sm_count();
+  if (sms <= 0) sms = 148;
+  const int shift = 64 - log2ns;
+  const unsigned scan_blocks = (unsigned)(((i64)1 << log2ns) / KS_CHUNK);
+  const int count_blocks = gb_blocks_for(Tmax, 2 * KS_TILE, sms * ctas);
+  const int pass_blocks = gb_blocks_for(Tmax, 2 * KS_TILE, sms * 2);
+  const int clear_blocks = gb_blocks_for(M, 1024, 64);
+  const int res_blocks = gb_blocks_for(Tmax, 1024, sms * 8);
+  const unsigned nb = (unsigned)((Tmax + HL_CHUNK - 1) / HL_CHUNK);
+  const size_t smem = cache ? 2 * sizeof(u32) * KS_CACHE : 0;
+  if (cache) GB_CK(cudaFuncSetAttribute(k_slot_count<KeysHT<CS>, false, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  for (int s = 0; s < nsteps; ++s) {
+    const int p = (parity + s) & 1, q = p ^ 1;
+    KeysHT<CS> kf{hsh[p], glue[p], len[p], powtab, P};
+    hl_begin<<<1, 1, 0, st>>>(hs);
+    GB_CK(cudaMemsetAsync(slots, 0, sizeof(u32) << log2ns, st));
+    if (g_time_k1) GB_CK(cudaEventRecord(hl_event(), st));
+    if (cache) k_slot_count<KeysHT<CS>, false, 1, false><<<count_blocks, KS_THREADS, smem, st>>>(kf, Tmax, slots, shift, nullptr, hs);
+    else k_slot_count<KeysHT<CS>, false, 0, false><<<count_blocks, KS_THREADS, 0, st>>>(kf, Tmax, slots, shift, nullptr, hs);
+    if (g_time_k1) GB_CK(cudaEventRecord(hl_event(), st));
+    hl_slots_max<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs);
+    for (int round = 1; round <= 2; ++round) {
+      hl_slots_collect<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs, round, cand, (u32)cap);
+      hl_table_clear<<<clear_blocks, 256, 0, st>>>(tk, tc, tm, M, hs, round);
+      k_cand_count<KeysHT<CS>><<<pass_blocks, KS_THREADS, 0, st>>>(kf, Tmax, shift, cand, hs + HS_NCAND, (u32)cap, tk, tc, tm, (u64)(M - 1),
+                                                                  (int32_t*)(hs + HS_OVF), hs, round);
+      hl_decide<<<1, 1024, 0, st>>>(tk, tc, tm, M, hs, round, tie_keys, tie_min, (u32)cap);
+    }
+    hl_tiebreak<<<1, HL_TB_CAP, 0, st>>>(hs, hs64, tie_keys, tie_min, pos[p], len[p], rbins, R, strbuf, stride);
+    hl_flag_verify<CS><<<pass_blocks, KS_THREADS, 0, st>>>(kf, hs, hs64, flags, pos[p], len[p], rbins, R);
+    hl_resolve<<<res_blocks, 256, 0, st>>>(hs, flags);
+    hl_count<<<nb, HL_CH_THREADS, 0, st>>>(hs, flags, scratch);
+    hl_scan<<<1, 1024, 0, st>>>(hs, scratch);
+    HLTok tok{hsh[p], glue[p], pos[p], len[p], tid[p], hsh[q], glue[q], pos[q], len[q], tid[q]};
+    hl_scatter<<<nb, HL_CH_THREADS, 0, st>>>(hs, hs64, flags, tok, scratch, (u32*)a[HA_EVL], (u32*)a[HA_EVR], (u32*)a[HA_EVP]);
+    hl_end<<<1, 1, 0, st>>>(hs, hs64, (u64*)a[HA_LKEY], (u32*)a[HA_LCNT], (u32*)a[HA_LR0], (u32*)a[HA_LNRES], (u32*)a[HA_LEVS],
+                            (u32*)a[HA_LNK]);
+    GB_LAUNCH_CK();
+  }
+  return 0;
+}
+
+extern "C" int gb_h_loop(const int64_t* args_host, int n_args, int nsteps, int parity, void* stream) {
+  if (n_args != HA_N) { gb_set_error("gb_h_loop: expected %d arguments, got %d", (int)HA_N, n_args); return -2; }
+  if (nsteps <= 0) return 0;
+  return args_host[HA_STREAMING] ? h_loop_impl<true>(args_host, nsteps, parity, (cudaStream_t)stream)
+                                 : h_loop_impl<false>(args_host, nsteps, parity, (cudaStream_t)stream);
+}
+extern "C" int gb_h_loop_time_k1(int enable) { g_time_k1 = enable != 0; g_ev_used = 0; return 0; }
+// elapsed ms of every timed k_slot_count launch since gb_h_loop_time_k1(1) (call after a synchronize); returns the count
+extern "C" int gb_h_loop_k1_times(float* ms_host, int cap) {
+  int n = 0;
+  for (size_t i = 0; i + 1 < g_ev_used && n < cap; i += 2, ++n)
+    if (cudaEventElapsedTime(&ms_host[n], g_ev[i], g_ev[i + 1]) != cudaSuccess) { cudaGetLastError(); ms_host[n] = -1.f; }
+  g_ev_used = 0;
+  return n;
+}
+extern "C" int gb_h_loop_nargs(void) { return (int)HA_N; }
+extern "C" int gb_h_loop_kernels_per_step(void) { return 18; }

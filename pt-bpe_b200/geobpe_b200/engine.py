@@ -8,6 +8,7 @@ matrix (algo.py:184-211).
 """
 import ctypes as C
 import json
+import types
 import math
 
 import numpy as np
@@ -381,7 +382,7 @@ class Learner:
 
     def __init__(self, vals, offsets, bins, bin_strategy="histogram", std_bonds=True, mode="H",
                  rmsd_super_res=True, num_partitions=3, max_num_strucs=500, rng=None, verify=True, comm=None,
-                 use_sketch=True):
+                 use_sketch=True, async_steps=True):
         self.comm = comm if (comm is not None and comm.world > 1) else None
         if self.comm is not None and mode != "H":
             raise NotImplementedError("multi-GPU medoid mode needs the sampled windows gathered in set order "
@@ -412,21 +413,54 @@ class Learner:
         self.sketch = None
         self.th = Thresholds(self.bb, self.bins, bin_strategy, std_bonds, self.comm)
         self.table = PairTable()
-        self.tokens = {}            # BPE._tokens
-        self.pop_log = []           # (count, key string) per popped key
-        self.step_events = []       # (token id / n, ev_start, ev_count, key)
+        self._tokens = {}           # BPE._tokens
+        self._pop_log = []          # (count, key string) per popped key
+        self._step_events = []      # (token id / n, ev_start, ev_count, key)
         self.n_steps = 0
+        self.hl = None              # device-driven loop state (histogram mode, single GPU)
+        self._pending = 0           # iterations enqueued on the device and not yet read back
+        self.async_steps = async_steps and mode == "H" and self.comm is None and use_sketch
         self._quantize()
-        self.ts = TokenState(self.bb.R, mode)
+        self._ts = TokenState(self.bb.R, mode)
         R = self.bb.R
         self.ev_left = _empty(R, torch.int32)
         self.ev_right = _empty(R, torch.int32)
         self.ev_p = _empty(R, torch.int32)
-        self.ev_n = 0
+        self._ev_n = 0
         if mode == "H":
             self._init_tokens_h()
         else:
             self._init_tokens_m()
+
+
+    # ---- state that the device-driven loop advances: reading it first drains the loop -------------------------
+    def _drain(self):
+        if self._pending:
+            self.sync()
+
+    @property
+    def tokens(self):
+        self._drain(); return self._tokens
+
+    @property
+    def pop_log(self):
+        self._drain(); return self._pop_log
+
+    @property
+    def step_events(self):
+        self._drain(); return self._step_events
+
+    @property
+    def ts(self):
+        self._drain(); return self._ts
+
+    @property
+    def ev_n(self):
+        self._drain(); return self._ev_n
+
+    @ev_n.setter
+    def ev_n(self, v):
+        self._ev_n = v
 
     # ---- K3 ------------------------------------------------------------------------------------
     def _quantize(self, bond_mode=None):
@@ -615,9 +649,16 @@ class Learner:
 
     def step_h(self):
         """one merge iteration, histogram mode (bpe.py:1792-2166 with rmsd_key None)"""
-        ts = self.ts
         if self.comm is not None:
             return self._step_h_dist()
+        if self.async_steps:
+            return self.enqueue(1)
+        return self._step_h_host()
+
+    def _step_h_host(self):
+        """host-driven iteration: K1 -> one D2H -> tie-break on the json strings -> K2 (also the fallback of the
+        device-driven loop for iterations it halts on)"""
+        ts = self.ts
         mx, ties = self._count_pairs()
         if mx == 0:
             raise IndexError("no adjacent pairs left (the reference's peekitem(0) raises here too)")
@@ -645,6 +686,123 @@ class Learner:
             if int(r[4]) != mx:
                 raise RuntimeError(f"flagged {int(r[4])} occurrences, histogram counted {mx}")
         self.n_steps += 1
+
+    # ---- device-driven loop (csrc/k_hloop.cu): iterations are enqueued, the host reads the step log in bulk -------
+    HL_LOG_CAP = 1 << 16
+    HL_TB_CAP = 128
+    HS = dict(T=0, STEP=1, HALT=2, EVN=3, MPREV=4, THR=5, C1=6, NCAND=7, NZ=8, M1=10, NT=11, ND=12, ROUND2=13,
+              WIN_R0=14, WIN_NRES=15, WIN_CNT=16, WIN_J=17, MISMATCH=18, FLAGGED=19, NEWT=20, NTOK=21, OVF=22,
+              R2COUNT=23, MAXSTEPS=24, EVCAP=25, HALT_STEP=26, NTMAX=27)
+    HALT_NAMES = {1: "ties", 2: "candidates", 3: "collision", 4: "table", 5: "event log", 6: "empty", 7: "step log",
+                  8: "count"}
+
+    def _hl_init(self):
+        ts = self._ts
+        if self.sketch is None:
+            self.sketch = SlotSketch(ts.T)
+        sk = self.sketch
+        maxwin = int(self.bb.lens_host.max()) if self.bb.S else 2
+        hl = types.SimpleNamespace()
+        hl.hs = _zeros(32, torch.int32)
+        hl.hs64 = _zeros(2, torch.int64)
+        hl.tie_keys = _empty(256, torch.int64)
+        hl.tie_min = _empty(256, torch.int32)
+        hl.stride = ((39 * maxwin + 200) + 127) // 128 * 128
+        hl.strbuf = _zeros(self.HL_TB_CAP * hl.stride, torch.uint8)
+        cap = self.HL_LOG_CAP
+        hl.log_key = _empty(cap, torch.int64)
+        hl.log = {k: _empty(cap, torch.int32) for k in ("cnt", "r0", "nres", "evstart", "nk")}
+        hl.nargs = _lib.load().gb_h_loop_nargs()
+        hl.enq = 0                    # iterations enqueued since the last sync (buffer parity on the host side)
+        hl.Tmax = ts.T
+        hl.halts = {}
+        hl.r2 = 0
+        hl.steps = 0
+        self.hl = hl
+
+    def _hl_args(self):
+        ts, sk, hl = self._ts, self.sketch, self.hl
+        a, b = ts.a, ts.b
+        P = _lib.ptr
+        vals = [P(hl.hs), P(hl.hs64), P(a["hsh"]), P(b["hsh"]), P(a["glue"]), P(b["glue"]), P(a["pos"]), P(b["pos"]),
+                P(a["len"]), P(b["len"]), P(a["tid"]), P(b["tid"]), P(ts.flags), P(ts.scratch), P(self.powtab), HASH_BASE,
+                P(self.rbins), self.bb.R, P(sk.slots), sk.log2ns, P(sk.bmax), P(sk.cand), sk.CAP, sk.variant, sk.ctas,
+                P(sk.small.keys), P(sk.small.cnt), P(sk.small.min), sk.small.M, P(hl.tie_keys), P(hl.tie_min),
+                P(hl.strbuf), hl.stride, P(self.ev_left), P(self.ev_right), P(self.ev_p), P(hl.log_key),
+                P(hl.log["cnt"]), P(hl.log["r0"]), P(hl.log["nres"]), P(hl.log["evstart"]), P(hl.log["nk"]), hl.Tmax,
+                1 if 16 * hl.Tmax > SlotSketch.STREAM_BYTES else 0]
+        assert len(vals) == hl.nargs, (len(vals), hl.nargs)
+        return (C.c_int64 * len(vals))(*[v if v < (1 << 63) else v - (1 << 64) for v in vals])
+
+    def _hl_push_state(self):
+        """host state -> device state block (after construction, after a host-side iteration)"""
+        hl, H = self.hl, self.HS
+        h = np.zeros(32, dtype=np.int64)
+        h[H["T"]] = self._ts.T
+        h[H["EVN"]] = self._ev_n
+        h[H["MPREV"]] = self._pop_log[-1][0] if self._pop_log else 0
+        h[H["NTOK"]] = len(self._tokens)
+        h[H["MAXSTEPS"]] = self.HL_LOG_CAP
+        h[H["EVCAP"]] = self.ev_left.numel()
+        hl.hs.copy_(torch.from_numpy(h.astype(np.int32)))
+        hl.enq = 0
+        hl.Tmax = self._ts.T
+        hl.args = self._hl_args()
+
+    def enqueue(self, nsteps):
+        """enqueue `nsteps` merge iterations on the device; nothing is read back until sync()"""
+        if self.hl is None:
+            self._hl_init()
+            self._hl_push_state()
+        hl = self.hl
+        _lib.call_n("gb_h_loop", nsteps * 18, hl.args, hl.nargs, nsteps, hl.enq & 1)
+        hl.enq += nsteps
+        self._pending += nsteps
+        self.n_steps += nsteps
+
+    def sync(self):
+        """drain the device loop: read the state block and the step log, materialise vocabulary entries / pop log;
+        an iteration the device could not resolve runs once on the host path, the rest is re-enqueued"""
+        while self._pending:
+            hl, H = self.hl, self.HS
+            h = hl.hs.cpu().numpy().astype(np.int64) & 0xFFFFFFFF            # the one blocking read
+            done, halt = int(h[H["STEP"]]), int(h[H["HALT"]])
+            want = self._pending
+            self._pending = 0
+            self.n_steps -= want
+            if done:
+                keys = hl.log_key[:done].cpu().numpy().astype(np.uint64).tolist()
+                lg = {k: _u32(v[:done]) for k, v in hl.log.items()}
+                dicts = self._h_key_dicts(lg["r0"].tolist(), lg["nres"].tolist())
+                for s in range(done):
+                    key_str = json.dumps(dicts[s], sort_keys=True)
+                    n = len(self._tokens)
+                    self._tokens[n] = json.loads(key_str)
+                    self._pop_log.append((int(lg["cnt"][s]), key_str))
+                    self._step_events.append((n, int(lg["evstart"][s]), int(lg["nk"][s]), keys[s]))
+                if done & 1:
+                    self._ts.swap()
+                self._ts.T = int(h[H["T"]])
+                self._ev_n = int(h[H["EVN"]])
+                self.n_steps += done
+            hl.steps += done
+            hl.r2 += int(h[H["R2COUNT"]])
+            hl.ntmax = max(getattr(hl, "ntmax", 0), int(h[H["NTMAX"]]))
+            rest = want - done
+            if halt in (3, 5, 8):
+                raise RuntimeError({3: "64-bit content-hash collision detected (window bins differ); re-run with another HASH_BASE",
+                                    5: "merge-event log overflow",
+                                    8: "flagged occurrences differ from the histogram count"}[halt])
+            if halt == 6:
+                raise IndexError("no adjacent pairs left (the reference's peekitem(0) raises here too)")
+            if halt:
+                hl.halts[halt] = hl.halts.get(halt, 0) + 1
+                if halt != 7:                      # ties / candidates / table: this one iteration on the host path
+                    self._step_h_host()
+                    rest -= 1
+            self._hl_push_state()
+            if rest > 0:
+                self.enqueue(rest)
 
     NS = 1 << 20      # direct-mapped slot counters exchanged per iteration (4 MB allreduce)
 
@@ -1158,7 +1316,8 @@ class Inducer(Learner):
         self.mode = "M"
         self.std_bonds = std_bonds
         self.size0 = 1
-        self.tokens = tokens
+        self._pending, self.hl, self.async_steps, self.use_sketch, self.sketch, self.k1b_events = 0, None, False, False, None, None
+        self._tokens = tokens
         self.token_keys = list(tokens)
         self.sphere_dict = sphere_dict
         self.bb = Backbones(vals, offsets)
@@ -1166,15 +1325,15 @@ class Inducer(Learner):
         self.th = Thresholds.__new__(Thresholds)
         self.th.thresholds = {1: thresholds[1]}
         self.k1_events = None
-        self.pop_log, self.step_events, self.n_steps = [], [], 0
+        self._pop_log, self._step_events, self.n_steps = [], [], 0
         self.class_of, self.class_geo, self.class_f3, self._f3_dirty = {}, [], [], True
         self.d_f3 = (0.0, 0.0, INIT_TAU)
         self._quantize(bond_mode=2)
         R, S = self.bb.R, self.bb.S
         self.failed = (self.status_host & 3) != 0          # glue angle outside the training range -> ValueError
-        self.ts = TokenState(R, "M")
+        self._ts = TokenState(R, "M")
         self.ev_left = _empty(R, torch.int32); self.ev_right = _empty(R, torch.int32); self.ev_p = _empty(R, torch.int32)
-        self.ev_n = 0
+        self._ev_n = 0
         th1 = thresholds[1]
         B = max(len(th1[k]) for k in BOND_TYPES)
         bc = np.zeros((3, B))
