@@ -198,15 +198,23 @@ int gb_pack_result(const uint32_t* out4, const int32_t* overflow, const uint64_t
 
 /* ---- device-driven histogram-mode learn loop (bpe.py:1792-2166 BPE.step with rmsd_key None, N iterations without a
  *      host round trip; csrc/k_hloop.cu).  args_host: int64 [gb_h_loop_nargs()] = device pointers and sizes in the order
- *      of the HA_* enum in k_hloop.cu (state block hs u32[32] + hs64 u64[2], ping-pong token arrays, flags, scan scratch,
- *      powtab, P, rbins, R, sketch buffers of gb_slot_count_h / gb_slots_top / gb_cand_count_h, tie list, JSON string
- *      scratch, merge-event log, per-step log, Tmax = upper bound of the live-token count, streaming flag).
- *      parity = which of the two token buffers is current at the first enqueued iteration.  Per iteration the device
- *      picks the key with the largest pair count, breaks ties by the python string order of json.dumps(key, sort_keys=True)
- *      (bpe.py:1149,1469), applies the merge with the left-to-right overlap rule and appends (key, count, example window,
- *      event range) to the step log.  A condition it cannot resolve sets hs[2] (halt code) and later kernels no-op. */
-int gb_h_loop(const int64_t* args_host, int n_args, int nsteps, int parity, void* stream);
+ *      of the HA_* enum in k_hloop.cu (state block hs u32[32] + hs64 u64[2], ping-pong token arrays, flags + rmark u8,
+ *      scan scratch, powtab, P, rbins, R, sketch buffers of gb_slot_count_h / gb_slots_top / gb_cand_count_h, tie list,
+ *      JSON string scratch, merge-event log, per-step log, candidate-pair list, Nmax = upper bound of the array extent,
+ *      streaming flag, compaction period).
+ *      Per iteration the device picks the key with the largest pair count, breaks ties by the python string order of
+ *      json.dumps(key, sort_keys=True) (bpe.py:1149,1469), merges its occurrences IN PLACE with the left-to-right overlap
+ *      rule (the `len` arrays hold len | extra << 16 inside the loop: extra = dead entries up to the right neighbour) and
+ *      appends (key, count, example window, event range) to the step log; the arrays are physically compacted every
+ *      `period` iterations and, with compact_after, at the end (then len is plain again).  parity = which of the two
+ *      token buffers is current on entry, *parity_out_host = on exit; step0 = iterations enqueued since the state block
+ *      was last written by the host.  A condition the device cannot resolve sets hs[2] (halt code) and later
+ *      iterations no-op. */
+int gb_h_loop(const int64_t* args_host, int n_args, int nsteps, int parity, int step0, int compact_after,
+              int* parity_out_host, void* stream);
 int gb_h_loop_nargs(void);
+/* whole compaction periods are replayed from captured CUDA graphs (default on) */
+int gb_h_loop_use_graphs(int enable);
 int gb_h_loop_kernels_per_step(void);
 /* CUDA-event timing of the pair-count kernel inside the loop: enable, run, synchronize, then read the per-launch ms */
 int gb_h_loop_time_k1(int enable);

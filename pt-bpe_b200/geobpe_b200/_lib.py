@@ -49,8 +49,9 @@ SIGNATURES = {
     "gb_window_coords": [P, I64, I64, P, P, P, I64, I32, I32, P, P, F64, F64, F64, P, P, I32, P, P],
     "gb_kabsch_assign": [P, I64, I32, P, I32, P, P, P],
     "gb_rmsd_matrix": [P, I32, I32, P, P],
-    "gb_h_loop": [P, I32, I32, I32, P],
+    "gb_h_loop": [P, I32, I32, I32, I32, I32, P, P],
     "gb_h_loop_nargs": [],
+    "gb_h_loop_use_graphs": [I32],
     "gb_h_loop_kernels_per_step": [],
     "gb_h_loop_time_k1": [I32],
     "gb_h_loop_k1_times": [P, I32],

@@ -21,7 +21,9 @@ enum {
   HS_T = 0, HS_STEP, HS_HALT, HS_EVN, HS_MPREV, HS_THR,
   HS_C1, HS_NCAND, HS_NZ, HS_PAD0,            // = gb_slots_top's sout[4]
   HS_M1, HS_NT, HS_ND, HS_ROUND2, HS_WIN_R0, HS_WIN_NRES, HS_WIN_CNT, HS_WIN_J, HS_MISMATCH, HS_FLAGGED,
-  HS_NEWT, HS_NTOK, HS_OVF, HS_R2COUNT, HS_MAXSTEPS, HS_EVCAP, HS_HALT_STEP, HS_NTMAX, HS_WORDS = 32
+  HS_NEWT, HS_NTOK, HS_OVF, HS_R2COUNT, HS_MAXSTEPS, HS_EVCAP, HS_HALT_STEP, HS_NTMAX,
+  HS_N /* array extent incl. dead entries */, HS_NCL /* candidate-pair list length */, HS_CLCAP, HS_CMPT /* compaction total */,
+  HS_WORDS = 32
 };
 
 // ---- pass 1 -----------------------------------------------------------------------------------------------------
@@ -29,7 +31,7 @@ enum {
 template <class KF, bool AGG, int CACHE, bool DRY>
 __global__ void __launch_bounds__(KS_THREADS, 2) k_slot_count(KF kf, i64 T, u32* __restrict__ slots, int shift,
                                                               const u32* __restrict__ hot_tags, const u32* __restrict__ hs) {
-  if (hs) { if (hs[HS_HALT]) return; T = (i64)hs[HS_T]; }      // device-driven loop: live-token count lives on the device
+  if (hs) { if (hs[HS_HALT]) return; T = (i64)hs[HS_N]; }      // device-driven loop: the array extent lives on the device
   extern __shared__ __align__(16) u32 ks_smem[];
   u32* s_tag = ks_smem;
   u32* s_cnt = ks_smem + KS_CACHE;
@@ -97,7 +99,7 @@ __global__ void __launch_bounds__(KS_THREADS, 2) k_cand_count(KF kf, i64 T, int 
                                                               u64 mask, int32_t* __restrict__ overflow, const u32* __restrict__ hs, int round) {
   if (hs) {
     if (hs[HS_HALT] || (round == 2 && !hs[HS_ROUND2])) return;
-    T = (i64)hs[HS_T];
+    T = (i64)hs[HS_N];
   }
   __shared__ u32 s_set[KC_SET];
   __shared__ u32 s_lin[KC_LINEAR];

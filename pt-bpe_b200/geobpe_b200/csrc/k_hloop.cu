@@ -10,6 +10,7 @@
 
 #define HL_TB_CAP 128           // ties resolved on the device
 #define HL_TIE_LIST 256         // tie list entries kept (>= HL_TB_CAP)
+#define HL_BLK_LIST 512         // candidate pairs staged per CTA before one append to the global list
 
 enum { HALT_TIES = 1, HALT_CAND = 2, HALT_COLLISION = 3, HALT_TABLE = 4, HALT_EVLOG = 5, HALT_EMPTY = 6, HALT_STEPS = 7,
        HALT_COUNT = 8 };
@@ -24,7 +25,7 @@ __global__ void hl_begin(u32* __restrict__ hs) {
   if (hs[HS_STEP] >= hs[HS_MAXSTEPS]) { hl_halt(hs, HALT_STEPS); return; }
   hs[HS_C1] = 0; hs[HS_NCAND] = 0; hs[HS_NZ] = 0; hs[HS_PAD0] = 0;
   hs[HS_M1] = 0; hs[HS_NT] = 0; hs[HS_ND] = 0; hs[HS_ROUND2] = 0;
-  hs[HS_MISMATCH] = 0; hs[HS_FLAGGED] = 0; hs[HS_OVF] = 0; hs[HS_NEWT] = 0;
+  hs[HS_MISMATCH] = 0; hs[HS_FLAGGED] = 0; hs[HS_OVF] = 0; hs[HS_NEWT] = 0; hs[HS_NCL] = 0;
 }
 
 // ---- slot scan -----------------------------------------------------------------------------------------------------
@@ -119,9 +120,9 @@ __global__ void __launch_bounds__(1024) hl_decide(const u64* __restrict__ tk, co
     const bool cand_over = hs[HS_NCAND] > cap || hs[HS_OVF] == 2;
     if (round == 1) {
       if (cand_over) {                        // too many slots above 0.9 * previous max: retry with the top slots only
-        hs[HS_ROUND2] = 1; hs[HS_THR] = hs[HS_C1]; hs[HS_NCAND] = 0; hs[HS_OVF] = 0; hs[HS_R2COUNT] += 1;
+        hs[HS_ROUND2] = 1; hs[HS_THR] = hs[HS_C1]; hs[HS_NCAND] = 0; hs[HS_OVF] = 0; hs[HS_NCL] = 0; hs[HS_R2COUNT] += 1;
       } else if (mx < hs[HS_THR]) {           // inconclusive: a key outside the candidates could reach mx
-        hs[HS_ROUND2] = 1; hs[HS_THR] = max(mx, 1u); hs[HS_NCAND] = 0; hs[HS_R2COUNT] += 1;
+        hs[HS_ROUND2] = 1; hs[HS_THR] = max(mx, 1u); hs[HS_NCAND] = 0; hs[HS_NCL] = 0; hs[HS_R2COUNT] += 1;
       }
     } else {
       if (cand_over || mx < hs[HS_THR]) hl_halt(hs, HALT_CAND);
@@ -193,6 +194,11 @@ __device__ __forceinline__ bool hl_less(const char* a, const char* b, int la, in
   }
   return la < lb;
 }
+// residues of the pair whose left token is entry j (lazy layout: ls = len | extra << 16, right neighbour j + 1 + extra)
+__device__ __forceinline__ u32 hl_pair_res(const u32* __restrict__ ls, u32 j) {
+  const u32 l = ls[j];
+  return (l & 0xFFFFu) + (ls[j + 1u + (l >> 16)] & 0xFFFFu);
+}
 __global__ void __launch_bounds__(HL_TB_CAP) hl_tiebreak(u32* __restrict__ hs, u64* __restrict__ hs64, const u64* __restrict__ tie_keys,
                                                          const u32* __restrict__ tie_min, const u32* __restrict__ pos,
                                                          const u32* __restrict__ len, const u16* __restrict__ rbins, i64 R,
@@ -206,7 +212,7 @@ __global__ void __launch_bounds__(HL_TB_CAP) hl_tiebreak(u32* __restrict__ hs, u
   if (nt > 1) {
     if (i < nt) {
       u32 j = tie_min[i];
-      u32 nres = len[j] + len[j + 1];
+      u32 nres = hl_pair_res(len, j);
       int need = 39 * (int)nres + 200;
       if (need > stride) { hl_halt(hs, HALT_TIES); s_len[i] = 0; }
       else s_len[i] = hl_json_key(strbuf + (size_t)i * stride, rbins, R, pos[j], nres);
@@ -228,93 +234,198 @@ __global__ void __launch_bounds__(HL_TB_CAP) hl_tiebreak(u32* __restrict__ hs, u
     int w = nt > 1 ? s_best[0] : 0;
     u32 j = tie_min[w];
     hs64[0] = tie_keys[w];
-    hs[HS_WIN_J] = j; hs[HS_WIN_R0] = pos[j]; hs[HS_WIN_NRES] = len[j] + len[j + 1]; hs[HS_WIN_CNT] = hs[HS_M1];
+    hs[HS_WIN_J] = j; hs[HS_WIN_R0] = pos[j]; hs[HS_WIN_NRES] = hl_pair_res(len, j); hs[HS_WIN_CNT] = hs[HS_M1];
     hs[HS_NTMAX] = max(hs[HS_NTMAX], nt);
   }
 }
 
-// ---- K2 on the device state: flag the winner's occurrences + exact window check, overlap rule, compaction ---------
+
+// ---- pass 2 on the lazy layout: exact counts of the candidate slots' keys + the list of those pairs ---------------
 template <bool CS>
-__global__ void __launch_bounds__(KS_THREADS, 2) hl_flag_verify(KeysHT<CS> kf, u32* __restrict__ hs, const u64* __restrict__ hs64,
-                                                                u8* __restrict__ flags, const u32* __restrict__ pos,
-                                                                const u32* __restrict__ len, const u16* __restrict__ rbins, i64 R) {
-  if (hs[HS_HALT]) return;
-  const i64 T = (i64)hs[HS_T];
-  const u64 win = hs64[0];
-  const u32 ref_r0 = hs[HS_WIN_R0], nres = hs[HS_WIN_NRES];
-  for (i64 base = (i64)blockIdx.x * (2 * KS_TILE); base < T; base += (i64)gridDim.x * (2 * KS_TILE)) {
+__global__ void __launch_bounds__(KS_THREADS, 2) hl_cand_count(KeysHLT<CS> kf, int shift, const u32* __restrict__ cand, u32 cap,
+                                                               u64* __restrict__ tk, u32* __restrict__ tc, u32* __restrict__ tm, u64 mask,
+                                                               u32* __restrict__ hs, int round, u64* __restrict__ cl_key, u32* __restrict__ cl_j) {
+  if (hs[HS_HALT] || (round == 2 && !hs[HS_ROUND2])) return;
+  __shared__ u32 s_set[KC_SET];
+  __shared__ u32 s_lin[KC_LINEAR];
+  __shared__ u64 s_key[HL_BLK_LIST];
+  __shared__ u32 s_j[HL_BLK_LIST];
+  __shared__ u32 s_n, s_base;
+  if (threadIdx.x == 0) s_n = 0;
+  const i64 N = (i64)hs[HS_N];
+  const u32 n = hs[HS_NCAND], clcap = hs[HS_CLCAP];
+  if (n == 0) return;
+  if (n > cap) { if (blockIdx.x == 0 && threadIdx.x == 0) hs[HS_OVF] = 2; return; }
+  const bool linear = n <= KC_LINEAR;
+  if (linear) {
+    if (threadIdx.x < KC_LINEAR) s_lin[threadIdx.x] = threadIdx.x < n ? cand[threadIdx.x] : KS_EMPTY;
+  } else {
+    for (int i = threadIdx.x; i < KC_SET; i += KS_THREADS) s_set[i] = KS_EMPTY;
+    __syncthreads();
+    for (u32 i = threadIdx.x; i < n; i += KS_THREADS) {
+      u32 v = cand[i], s = (v * 0x9E3779B1u) >> 19;
+      while (true) {
+        u32 prev = atomicCAS(&s_set[s], KS_EMPTY, v);
+        if (prev == KS_EMPTY || prev == v) break;
+        s = (s + 1) & (KC_SET - 1);
+      }
+    }
+  }
+  __syncthreads();
+  for (i64 base = (i64)blockIdx.x * (2 * KS_TILE); base < N; base += (i64)gridDim.x * (2 * KS_TILE)) {
     const i64 ja = base + (i64)threadIdx.x * K1_VEC, jb = ja + KS_TILE;
-    typename KeysHT<CS>::Raw ra, rb;
-    kf.ld(ja, T, ra);
-    kf.ld(jb, T, rb);
+    typename KeysHLT<CS>::Raw ra, rb;
+    kf.ld(ja, N, ra);
+    kf.ld(jb, N, rb);
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
       u64 key[K1_VEC];
       const i64 j0 = half ? jb : ja;
-      if (half == 0) kf.fin(ja, T, ra, key); else kf.fin(jb, T, rb, key);
-      u8 f[K1_VEC];
-#pragma unroll
-      for (int e = 0; e < K1_VEC; ++e) f[e] = (key[e] == win) ? 1 : 0;
-      if (j0 + K1_VEC <= T) *reinterpret_cast<uchar4*>(flags + j0) = make_uchar4(f[0], f[1], f[2], f[3]);
-      else {
-#pragma unroll
-        for (int e = 0; e < K1_VEC; ++e) if (j0 + e < T) flags[j0 + e] = f[e];
-      }
+      if (half == 0) kf.fin(ja, N, ra, key); else kf.fin(jb, N, rb, key);
 #pragma unroll
       for (int e = 0; e < K1_VEC; ++e) {
-        if (!f[e]) continue;
-        const i64 j = j0 + e;
-        atomicAdd(&hs[HS_FLAGGED], 1u);
-        const u32 r0 = pos[j];
-        bool bad = (len[j] + len[j + 1]) != nres;
-        for (u32 slot = 3; slot < 9 && !bad; ++slot) {
-          const u32 n = (slot >= 6) ? nres - 1 : nres;   // glue of the last residue lies outside the window
-          for (u32 k = 0; k < n; ++k)
-            if (rbins[(i64)slot * R + r0 + k] != rbins[(i64)slot * R + ref_r0 + k]) { bad = true; break; }
+        if (key[e] == GB_EMPTY_KEY) continue;
+        u32 slot = gb_slot_of(key[e], shift);
+        bool hit = false;
+        if (linear) {
+#pragma unroll
+          for (int i = 0; i < KC_LINEAR; ++i) hit |= (s_lin[i] == slot);
+        } else {
+          u32 s = (slot * 0x9E3779B1u) >> 19;
+          while (true) {
+            u32 v = s_set[s];
+            if (v == slot) { hit = true; break; }
+            if (v == KS_EMPTY) break;
+            s = (s + 1) & (KC_SET - 1);
+          }
         }
-        if (bad) atomicAdd(&hs[HS_MISMATCH], 1u);
+        if (!hit) continue;
+        if (!gb_gtable_add(tk, tc, tm, mask, key[e], 1u, (u32)(j0 + e))) hs[HS_OVF] = 1;
+        u32 q = atomicAdd(&s_n, 1u);                 // block-local list first: one global atomic per CTA at the end
+        if (q < HL_BLK_LIST) { s_key[q] = key[e]; s_j[q] = (u32)(j0 + e); }
+        else {
+          u32 g = atomicAdd(&hs[HS_NCL], 1u);
+          if (g < clcap) { cl_key[g] = key[e]; cl_j[g] = (u32)(j0 + e); }
+        }
       }
+    }
+  }
+  __syncthreads();
+  const u32 m = min(s_n, (u32)HL_BLK_LIST);
+  if (m) {
+    if (threadIdx.x == 0) s_base = atomicAdd(&hs[HS_NCL], m);
+    __syncthreads();
+    for (u32 i = threadIdx.x; i < m; i += KS_THREADS) {
+      u32 g = s_base + i;
+      if (g < clcap) { cl_key[g] = s_key[i]; cl_j[g] = s_j[i]; }
     }
   }
 }
 
-__global__ void __launch_bounds__(256) hl_resolve(u32* __restrict__ hs, u8* __restrict__ flags) {
+// ---- K2 in place, driven by the candidate-pair list ---------------------------------------------------------------
+// flags[j] = 1: pair (j, right(j)) is an occurrence of the winner; rmark[r] = 1: entry r is the right token of one.
+// cl_r keeps right(j) so the marks can be removed after the merges changed ls.
+__global__ void __launch_bounds__(256) hl_flag_list(u32* __restrict__ hs, const u64* __restrict__ hs64, const u64* __restrict__ cl_key,
+                                                     const u32* __restrict__ cl_j, u32* __restrict__ cl_r, u8* __restrict__ flags,
+                                                     u8* __restrict__ rmark, const u32* __restrict__ pos, const u32* __restrict__ ls,
+                                                     const u16* __restrict__ rbins, i64 R) {
+  if (hs[HS_HALT]) return;
+  const u32 n = hs[HS_NCL];
+  if (n > hs[HS_CLCAP]) { if (blockIdx.x == 0 && threadIdx.x == 0) hl_halt(hs, HALT_CAND); return; }
+  const u64 win = hs64[0];
+  const u32 ref_r0 = hs[HS_WIN_R0], nres = hs[HS_WIN_NRES];
+  u32 nflag = 0, nbad = 0;
+  for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    if (cl_key[i] != win) continue;
+    const u32 j = cl_j[i], l = ls[j], r = j + 1u + (l >> 16);
+    cl_r[i] = r;
+    flags[j] = 1; rmark[r] = 1;
+    ++nflag;
+    const u32 r0 = pos[j];
+    bool bad = ((l & 0xFFFFu) + (ls[r] & 0xFFFFu)) != nres;
+    for (u32 slot = 3; slot < 9 && !bad; ++slot) {
+      const u32 m = (slot >= 6) ? nres - 1 : nres;     // glue of the last residue lies outside the window
+      for (u32 k = 0; k < m; ++k)
+        if (rbins[(i64)slot * R + r0 + k] != rbins[(i64)slot * R + ref_r0 + k]) { bad = true; break; }
+    }
+    nbad += bad;
+  }
+  for (int o = 16; o; o >>= 1) { nflag += __shfl_xor_sync(0xffffffffu, nflag, o); nbad += __shfl_xor_sync(0xffffffffu, nbad, o); }
+  if ((threadIdx.x & 31) == 0) {
+    if (nflag) atomicAdd(&hs[HS_FLAGGED], nflag);
+    if (nbad) atomicAdd(&hs[HS_MISMATCH], nbad);
+  }
+}
+// overlap rule (bpe.py:1909-1914) + merge: the head of every maximal run of flagged pairs walks it left to right and
+// merges the 1st, 3rd, ... occurrence in place; merge events are appended in arbitrary order (the host sorts each
+// iteration's events by position when it reads the log)
+__global__ void __launch_bounds__(256) hl_apply_list(u32* __restrict__ hs, const u64* __restrict__ hs64, const u64* __restrict__ cl_key,
+                                                      const u32* __restrict__ cl_j, const u8* __restrict__ flags,
+                                                      const u8* __restrict__ rmark, u64* __restrict__ hsh, u32* __restrict__ glue,
+                                                      u32* __restrict__ ls, u32* __restrict__ tid, const u32* __restrict__ pos,
+                                                      u32* __restrict__ ev_left, u32* __restrict__ ev_right, u32* __restrict__ ev_p) {
   if (hs[HS_HALT]) return;
   const bool t0 = blockIdx.x == 0 && threadIdx.x == 0;
   if (hs[HS_MISMATCH]) { if (t0) hl_halt(hs, HALT_COLLISION); return; }
   if (hs[HS_FLAGGED] != hs[HS_WIN_CNT]) { if (t0) hl_halt(hs, HALT_COUNT); return; }
   if (hs[HS_EVN] + hs[HS_FLAGGED] > hs[HS_EVCAP]) { if (t0) hl_halt(hs, HALT_EVLOG); return; }
-  const i64 T = (i64)hs[HS_T];
-  for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < T; j += (i64)gridDim.x * blockDim.x) {
-    if ((flags[j] & 1) && !(j > 0 && (flags[j - 1] & 1))) {
-      i64 i = j;
-      bool keep = true;
-      while (i < T && (flags[i] & 1)) {      // runs never cross a backbone: the last token's pair is never flagged
-        if (keep) flags[i] = 3;
-        keep = !keep;
-        ++i;
+  const u32 n = hs[HS_NCL], ev0 = hs[HS_EVN], new_tid = hs[HS_NTOK];
+  const u64 win = hs64[0];
+  for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    if (cl_key[i] != win) continue;
+    u32 j = cl_j[i];
+    if (rmark[j]) continue;                      // not a run head: the pair to its left is an occurrence too
+    bool keep = true;
+    u32 l = ls[j];                                 // carried along the run: a merged right token's ls is zeroed below
+    while (flags[j]) {
+      const u32 r = j + 1u + (l >> 16), lr = ls[r];
+      if (keep) {
+        hsh[j] = win;
+        glue[j] = glue[r];
+        ls[j] = ((l & 0xFFFFu) + (lr & 0xFFFFu)) | (((l >> 16) + 1u + (lr >> 16)) << 16);
+        tid[j] = new_tid;
+        ls[r] = 0u;                                // dead until the next compaction
+        u32 q = ev0 + atomicAdd(&hs[HS_NEWT], 1u);   // HS_NEWT counts this iteration's merges
+        ev_left[q] = pos[j]; ev_right[q] = pos[r]; ev_p[q] = 0u;
       }
+      keep = !keep;
+      j = r; l = lr;                               // runs never cross a backbone: the last token's pair is never flagged
     }
   }
 }
+__global__ void __launch_bounds__(256) hl_unflag_list(const u32* __restrict__ hs, const u64* __restrict__ hs64,
+                                                       const u64* __restrict__ cl_key, const u32* __restrict__ cl_j,
+                                                       const u32* __restrict__ cl_r, u8* __restrict__ flags, u8* __restrict__ rmark) {
+  if (hs[HS_HALT]) return;
+  const u32 n = hs[HS_NCL];
+  const u64 win = hs64[0];
+  for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    if (cl_key[i] == win) { flags[cl_j[i]] = 0; rmark[cl_r[i]] = 0; }
+}
+// commit the iteration (step log, counters) and reset the per-iteration words for the next one
+__global__ void hl_end(u32* __restrict__ hs, const u64* __restrict__ hs64, u64* __restrict__ log_key, u32* __restrict__ log_cnt,
+                       u32* __restrict__ log_r0, u32* __restrict__ log_nres, u32* __restrict__ log_evstart, u32* __restrict__ log_nk) {
+  if (hs[HS_HALT]) return;
+  const u32 s = hs[HS_STEP], nk = hs[HS_NEWT];
+  log_key[s] = hs64[0]; log_cnt[s] = hs[HS_WIN_CNT]; log_r0[s] = hs[HS_WIN_R0]; log_nres[s] = hs[HS_WIN_NRES];
+  log_evstart[s] = hs[HS_EVN]; log_nk[s] = nk;
+  hs[HS_EVN] += nk; hs[HS_T] -= nk; hs[HS_MPREV] = hs[HS_WIN_CNT]; hs[HS_STEP] = s + 1; hs[HS_NTOK] += 1;
+}
 
+// ---- occasional physical compaction of the lazily compacted arrays (runs between iterations, ignores the halt flag) --
 #define HL_CH_THREADS 256
 #define HL_CH_ITEMS 8
 #define HL_CHUNK (HL_CH_THREADS * HL_CH_ITEMS)
-// token i survives unless pair (i-1, i) was kept (flags bit1 on i-1)
-__device__ __forceinline__ bool hl_survives(const u8* __restrict__ f, i64 i) { return !(i > 0 && (f[i - 1] & 2)); }
-
-__global__ void __launch_bounds__(HL_CH_THREADS) hl_count(const u32* __restrict__ hs, const u8* __restrict__ flags, u32* __restrict__ bsum) {
-  if (hs[HS_HALT]) return;
-  const i64 T = (i64)hs[HS_T];
+__global__ void __launch_bounds__(HL_CH_THREADS) hl_cmp_count(const u32* __restrict__ hs, const u32* __restrict__ ls, u32* __restrict__ bsum) {
+  const i64 N = (i64)hs[HS_N];
   const i64 base = (i64)blockIdx.x * HL_CHUNK;
-  if (base >= T) return;
+  if (base >= N) return;
   __shared__ u32 wsum[HL_CH_THREADS / 32];
   u32 c = 0;
 #pragma unroll
   for (int it = 0; it < HL_CH_ITEMS; ++it) {
     i64 i = base + it * HL_CH_THREADS + threadIdx.x;
-    if (i < T && hl_survives(flags, i)) ++c;
+    if (i < N && ls[i] != 0u) ++c;
   }
   for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
   if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = c;
@@ -325,10 +436,9 @@ __global__ void __launch_bounds__(HL_CH_THREADS) hl_count(const u32* __restrict_
     bsum[blockIdx.x] = t;
   }
 }
-// in-place exclusive scan of bsum[0..nb), total -> hs[HS_NEWT] (single block)
-__global__ void __launch_bounds__(1024) hl_scan(u32* __restrict__ hs, u32* __restrict__ bsum) {
-  if (hs[HS_HALT]) return;
-  const i64 nb = ((i64)hs[HS_T] + HL_CHUNK - 1) / HL_CHUNK;
+// in-place exclusive scan of bsum[0..nb), total -> hs[HS_CMPT] (single block)
+__global__ void __launch_bounds__(1024) hl_cmp_scan(u32* __restrict__ hs, u32* __restrict__ bsum) {
+  const i64 nb = ((i64)hs[HS_N] + HL_CHUNK - 1) / HL_CHUNK;
   __shared__ u32 wtot[32];
   __shared__ u32 carry_s;
   if (threadIdx.x == 0) carry_s = 0;
@@ -356,67 +466,44 @@ __global__ void __launch_bounds__(1024) hl_scan(u32* __restrict__ hs, u32* __res
     if (threadIdx.x == 0) carry_s = carry + tot;
     __syncthreads();
   }
-  if (threadIdx.x == 0) hs[HS_NEWT] = carry_s;
+  if (threadIdx.x == 0) hs[HS_CMPT] = carry_s;
 }
-struct HLTok { const u64* hsh; const u32* glue; const u32* pos; const u32* len; const u32* tid;
-               u64* hsh_o; u32* glue_o; u32* pos_o; u32* len_o; u32* tid_o; };
-// compaction + merge + event log: the k-th kept occurrence (in token order) is the (i - o)-th, because every kept
-// occurrence before token i removed exactly one token
-__global__ void __launch_bounds__(HL_CH_THREADS) hl_scatter(const u32* __restrict__ hs, const u64* __restrict__ hs64,
-                                                            const u8* __restrict__ flags, HLTok a, const u32* __restrict__ boff,
-                                                            u32* __restrict__ ev_left, u32* __restrict__ ev_right, u32* __restrict__ ev_p) {
-  if (hs[HS_HALT]) return;
-  const i64 T = (i64)hs[HS_T];
+struct HLTok { const u64* hsh; const u32* glue; const u32* pos; const u32* ls; const u32* tid;
+               u64* hsh_o; u32* glue_o; u32* pos_o; u32* ls_o; u32* tid_o; };
+__global__ void __launch_bounds__(HL_CH_THREADS) hl_cmp_scatter(const u32* __restrict__ hs, HLTok a, const u32* __restrict__ boff) {
+  const i64 N = (i64)hs[HS_N];
   const i64 base = (i64)blockIdx.x * HL_CHUNK;
-  if (base >= T) return;
+  if (base >= N) return;
   __shared__ u32 wsum[HL_CH_THREADS / 32];
-  const u64 key = hs64[0];
-  const u32 new_tid = hs[HS_NTOK], ev0 = hs[HS_EVN];
   u32 run = boff[blockIdx.x];
 #pragma unroll
   for (int it = 0; it < HL_CH_ITEMS; ++it) {
     i64 i = base + it * HL_CH_THREADS + threadIdx.x;
-    bool f = (i < T) && hl_survives(flags, i);
+    u32 l = (i < N) ? a.ls[i] : 0u;
+    bool f = l != 0u;
     u32 tot;
     u32 ex = gb_block_excl_scan_flag(f, wsum, tot);
     if (f) {
       u32 o = run + ex;
-      a.pos_o[o] = a.pos[i];
-      if (flags[i] & 2) {                    // token i absorbs token i+1
-        a.glue_o[o] = a.glue[i + 1];
-        a.len_o[o] = a.len[i] + a.len[i + 1];
-        a.tid_o[o] = new_tid;
-        a.hsh_o[o] = key;
-        u32 q = ev0 + (u32)(i - o);
-        ev_left[q] = a.pos[i]; ev_right[q] = a.pos[i + 1]; ev_p[q] = 0u;
-      } else {
-        a.glue_o[o] = a.glue[i];
-        a.len_o[o] = a.len[i];
-        a.tid_o[o] = a.tid[i];
-        a.hsh_o[o] = a.hsh[i];
-      }
+      a.hsh_o[o] = a.hsh[i]; a.glue_o[o] = a.glue[i]; a.pos_o[o] = a.pos[i]; a.tid_o[o] = a.tid[i];
+      a.ls_o[o] = l & 0xFFFFu;                 // every live token's right neighbour is the next entry again
     }
     run += tot;
   }
 }
-__global__ void hl_end(u32* __restrict__ hs, const u64* __restrict__ hs64, u64* __restrict__ log_key, u32* __restrict__ log_cnt,
-                       u32* __restrict__ log_r0, u32* __restrict__ log_nres, u32* __restrict__ log_evstart, u32* __restrict__ log_nk) {
-  if (hs[HS_HALT]) return;
-  const u32 s = hs[HS_STEP], T = hs[HS_T], newT = hs[HS_NEWT], nk = T - newT;
-  log_key[s] = hs64[0]; log_cnt[s] = hs[HS_WIN_CNT]; log_r0[s] = hs[HS_WIN_R0]; log_nres[s] = hs[HS_WIN_NRES];
-  log_evstart[s] = hs[HS_EVN]; log_nk[s] = nk;
-  hs[HS_EVN] += nk; hs[HS_T] = newT; hs[HS_MPREV] = hs[HS_WIN_CNT]; hs[HS_STEP] = s + 1; hs[HS_NTOK] += 1;
-}
+__global__ void hl_cmp_end(u32* __restrict__ hs) { hs[HS_N] = hs[HS_CMPT]; }
 
 // ---- host entry: enqueue `nsteps` iterations -------------------------------------------------------------------------
 enum { HA_HS = 0, HA_HS64, HA_HSH0, HA_HSH1, HA_GLUE0, HA_GLUE1, HA_POS0, HA_POS1, HA_LEN0, HA_LEN1, HA_TID0, HA_TID1,
-       HA_FLAGS, HA_SCRATCH, HA_POWTAB, HA_P, HA_RBINS, HA_R, HA_SLOTS, HA_LOG2NS, HA_BMAX, HA_CAND, HA_CAP, HA_VARIANT,
-       HA_CTAS, HA_TK, HA_TC, HA_TM, HA_M, HA_TIEK, HA_TIEM, HA_STRBUF, HA_STRIDE, HA_EVL, HA_EVR, HA_EVP, HA_LKEY,
-       HA_LCNT, HA_LR0, HA_LNRES, HA_LEVS, HA_LNK, HA_TMAX, HA_STREAMING, HA_N };
+       HA_FLAGS, HA_RMARK, HA_SCRATCH, HA_POWTAB, HA_P, HA_RBINS, HA_R, HA_SLOTS, HA_LOG2NS, HA_BMAX, HA_CAND, HA_CAP,
+       HA_VARIANT, HA_CTAS, HA_TK, HA_TC, HA_TM, HA_M, HA_TIEK, HA_TIEM, HA_STRBUF, HA_STRIDE, HA_EVL, HA_EVR, HA_EVP,
+       HA_LKEY, HA_LCNT, HA_LR0, HA_LNRES, HA_LEVS, HA_LNK, HA_CLKEY, HA_CLJ, HA_CLR, HA_NMAX, HA_STREAMING,
+       HA_PERIOD, HA_N };
 
 // optional CUDA-event timing of the pair-count kernel inside the loop (bench.py's roofline leg)
 #include <vector>
 static bool g_time_k1 = false;
+static cudaStream_t g_cap_stream = nullptr;   // private stream the CUDA graphs are captured on
 static std::vector<cudaEvent_t> g_ev;
 static size_t g_ev_used = 0;
 static cudaEvent_t hl_event() {
@@ -425,7 +512,7 @@ static cudaEvent_t hl_event() {
 }
 
 template <bool CS>
-static int h_loop_impl(const int64_t* a, int nsteps, int parity, cudaStream_t st) {
+static int h_loop_impl(const int64_t* a, int nsteps, int parity, int step0, int compact_after, int* parity_out, cudaStream_t st) {
   u32* hs = (u32*)a[HA_HS];
   u64* hs64 = (u64*)a[HA_HS64];
   u64* hsh[2] = {(u64*)a[HA_HSH0], (u64*)a[HA_HSH1]};
@@ -434,6 +521,7 @@ static int h_loop_impl(const int64_t* a, int nsteps, int parity, cudaStream_t st
   u32* len[2] = {(u32*)a[HA_LEN0], (u32*)a[HA_LEN1]};
   u32* tid[2] = {(u32*)a[HA_TID0], (u32*)a[HA_TID1]};
   u8* flags = (u8*)a[HA_FLAGS];
+  u8* rmark = (u8*)a[HA_RMARK];
   u32* scratch = (u32*)a[HA_SCRATCH];
   const u64* powtab = (const u64*)a[HA_POWTAB];
   const u64 P = (u64)a[HA_P];
@@ -451,59 +539,126 @@ static int h_loop_impl(const int64_t* a, int nsteps, int parity, cudaStream_t st
   u64* tie_keys = (u64*)a[HA_TIEK]; u32* tie_min = (u32*)a[HA_TIEM];
   char* strbuf = (char*)a[HA_STRBUF];
   const int stride = (int)a[HA_STRIDE];
-  const i64 Tmax = a[HA_TMAX];
-  if (log2ns < 12 || log2ns > 30 || M <= 0 || (M & (M - 1)) || cap > KC_SET / 2 || cache > 1 || (stride & 127) || Tmax < 2) {
-    gb_set_error("gb_h_loop: bad arguments (log2ns %d, M %lld, cap %d, cache %d, stride %d, Tmax %lld)", log2ns, (long long)M, cap,
-                 cache, stride, (long long)Tmax);
+  u64* cl_key = (u64*)a[HA_CLKEY]; u32* cl_j = (u32*)a[HA_CLJ]; u32* cl_r = (u32*)a[HA_CLR];
+  const i64 Nmax = a[HA_NMAX];
+  const int period = a[HA_PERIOD] > 0 ? (int)a[HA_PERIOD] : 64;
+  if (log2ns < 12 || log2ns > 30 || M <= 0 || (M & (M - 1)) || cap > KC_SET / 2 || cache > 1 || (stride & 127) || Nmax < 2) {
+    gb_set_error("gb_h_loop: bad arguments (log2ns %d, M %lld, cap %d, cache %d, stride %d, Nmax %lld)", log2ns, (long long)M, cap,
+                 cache, stride, (long long)Nmax);
     return -2;
   }
   int sms = gb_sm_count();
   if (sms <= 0) sms = 148;
   const int shift = 64 - log2ns;
   const unsigned scan_blocks = (unsigned)(((i64)1 << log2ns) / KS_CHUNK);
-  const int count_blocks = gb_blocks_for(Tmax, 2 * KS_TILE, sms * ctas);
-  const int pass_blocks = gb_blocks_for(Tmax, 2 * KS_TILE, sms * 2);
+  const int count_blocks = gb_blocks_for(Nmax, 2 * KS_TILE, sms * ctas);
+  const int pass_blocks = gb_blocks_for(Nmax, 2 * KS_TILE, sms * 2);
   const int clear_blocks = gb_blocks_for(M, 1024, 64);
-  const int res_blocks = gb_blocks_for(Tmax, 1024, sms * 8);
-  const unsigned nb = (unsigned)((Tmax + HL_CHUNK - 1) / HL_CHUNK);
+  const int list_blocks = sms * 2;
+  const unsigned nb = (unsigned)((Nmax + HL_CHUNK - 1) / HL_CHUNK);
   const size_t smem = cache ? 2 * sizeof(u32) * KS_CACHE : 0;
-  if (cache) GB_CK(cudaFuncSetAttribute(k_slot_count<KeysHT<CS>, false, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (cache && !(g_cap_stream && st == g_cap_stream))
+    GB_CK(cudaFuncSetAttribute(k_slot_count<KeysHLT<CS>, false, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int p = parity & 1;
+  bool dirty = false;              // dead entries may exist since the last compaction
+  auto compact = [&]() -> int {
+    const int q = p ^ 1;
+    hl_cmp_count<<<nb, HL_CH_THREADS, 0, st>>>(hs, len[p], scratch);
+    hl_cmp_scan<<<1, 1024, 0, st>>>(hs, scratch);
+    HLTok tok{hsh[p], glue[p], pos[p], len[p], tid[p], hsh[q], glue[q], pos[q], len[q], tid[q]};
+    hl_cmp_scatter<<<nb, HL_CH_THREADS, 0, st>>>(hs, tok, scratch);
+    hl_cmp_end<<<1, 1, 0, st>>>(hs);
+    GB_LAUNCH_CK();
+    p = q;
+    dirty = false;
+    return 0;
+  };
   for (int s = 0; s < nsteps; ++s) {
-    const int p = (parity + s) & 1, q = p ^ 1;
-    KeysHT<CS> kf{hsh[p], glue[p], len[p], powtab, P};
+    KeysHLT<CS> kf{hsh[p], glue[p], len[p], powtab, P};
     hl_begin<<<1, 1, 0, st>>>(hs);
     GB_CK(cudaMemsetAsync(slots, 0, sizeof(u32) << log2ns, st));
     if (g_time_k1) GB_CK(cudaEventRecord(hl_event(), st));
-    if (cache) k_slot_count<KeysHT<CS>, false, 1, false><<<count_blocks, KS_THREADS, smem, st>>>(kf, Tmax, slots, shift, nullptr, hs);
-    else k_slot_count<KeysHT<CS>, false, 0, false><<<count_blocks, KS_THREADS, 0, st>>>(kf, Tmax, slots, shift, nullptr, hs);
+    if (cache) k_slot_count<KeysHLT<CS>, false, 1, false><<<count_blocks, KS_THREADS, smem, st>>>(kf, Nmax, slots, shift, nullptr, hs);
+    else k_slot_count<KeysHLT<CS>, false, 0, false><<<count_blocks, KS_THREADS, 0, st>>>(kf, Nmax, slots, shift, nullptr, hs);
     if (g_time_k1) GB_CK(cudaEventRecord(hl_event(), st));
     hl_slots_max<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs);
     for (int round = 1; round <= 2; ++round) {
       hl_slots_collect<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs, round, cand, (u32)cap);
       hl_table_clear<<<clear_blocks, 256, 0, st>>>(tk, tc, tm, M, hs, round);
-      k_cand_count<KeysHT<CS>><<<pass_blocks, KS_THREADS, 0, st>>>(kf, Tmax, shift, cand, hs + HS_NCAND, (u32)cap, tk, tc, tm, (u64)(M - 1),
-                                                                  (int32_t*)(hs + HS_OVF), hs, round);
+      hl_cand_count<CS><<<pass_blocks, KS_THREADS, 0, st>>>(kf, shift, cand, (u32)cap, tk, tc, tm, (u64)(M - 1), hs, round, cl_key, cl_j);
       hl_decide<<<1, 1024, 0, st>>>(tk, tc, tm, M, hs, round, tie_keys, tie_min, (u32)cap);
     }
     hl_tiebreak<<<1, HL_TB_CAP, 0, st>>>(hs, hs64, tie_keys, tie_min, pos[p], len[p], rbins, R, strbuf, stride);
-    hl_flag_verify<CS><<<pass_blocks, KS_THREADS, 0, st>>>(kf, hs, hs64, flags, pos[p], len[p], rbins, R);
-    hl_resolve<<<res_blocks, 256, 0, st>>>(hs, flags);
-    hl_count<<<nb, HL_CH_THREADS, 0, st>>>(hs, flags, scratch);
-    hl_scan<<<1, 1024, 0, st>>>(hs, scratch);
-    HLTok tok{hsh[p], glue[p], pos[p], len[p], tid[p], hsh[q], glue[q], pos[q], len[q], tid[q]};
-    hl_scatter<<<nb, HL_CH_THREADS, 0, st>>>(hs, hs64, flags, tok, scratch, (u32*)a[HA_EVL], (u32*)a[HA_EVR], (u32*)a[HA_EVP]);
+    hl_flag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark, pos[p], len[p], rbins, R);
+    hl_apply_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, flags, rmark, hsh[p], glue[p], len[p], tid[p], pos[p],
+                                               (u32*)a[HA_EVL], (u32*)a[HA_EVR], (u32*)a[HA_EVP]);
+    hl_unflag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark);
     hl_end<<<1, 1, 0, st>>>(hs, hs64, (u64*)a[HA_LKEY], (u32*)a[HA_LCNT], (u32*)a[HA_LR0], (u32*)a[HA_LNRES], (u32*)a[HA_LEVS],
                             (u32*)a[HA_LNK]);
     GB_LAUNCH_CK();
+    dirty = true;
+    if ((step0 + s + 1) % period == 0) { int rc = compact(); if (rc) return rc; }
   }
+  if (compact_after && (dirty || nsteps == 0)) { int rc = compact(); if (rc) return rc; }
+  if (parity_out) *parity_out = p;
   return 0;
 }
 
-extern "C" int gb_h_loop(const int64_t* args_host, int n_args, int nsteps, int parity, void* stream) {
+// CUDA graphs: one graph per buffer parity holding `period` iterations + the compaction that ends the period, captured
+// once per argument set and replayed (the loop is launch-bound otherwise: ~17 launches per ~100 us iteration)
+static std::vector<int64_t> g_graph_args;
+static cudaGraphExec_t g_graph_exec[2] = {nullptr, nullptr};
+static bool g_use_graphs = true;
+extern "C" int gb_h_loop_use_graphs(int enable) { g_use_graphs = enable != 0; return 0; }
+
+template <bool CS>
+static int h_loop_graphs(const int64_t* a, int period, cudaStream_t st) {
+  std::vector<int64_t> key(a, a + HA_N);
+  if (g_graph_exec[0] && key == g_graph_args) return 0;
+  for (int p = 0; p < 2; ++p)
+    if (g_graph_exec[p]) { cudaGraphExecDestroy(g_graph_exec[p]); g_graph_exec[p] = nullptr; }
+  if (!g_cap_stream) GB_CK(cudaStreamCreateWithFlags(&g_cap_stream, cudaStreamNonBlocking));
+  if (((int)a[HA_VARIANT] >> 1) & 3)    // function attributes are set outside the capture
+    GB_CK(cudaFuncSetAttribute(k_slot_count<KeysHLT<CS>, false, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)(2 * sizeof(u32) * KS_CACHE)));
+  for (int p = 0; p < 2; ++p) {
+    cudaGraph_t graph = nullptr;
+    int pout = 0;
+    GB_CK(cudaStreamBeginCapture(g_cap_stream, cudaStreamCaptureModeThreadLocal));
+    int rc = h_loop_impl<CS>(a, period, p, 0, 0, &pout, g_cap_stream);
+    cudaError_t e = cudaStreamEndCapture(g_cap_stream, &graph);
+    if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+    GB_CK(e);
+    GB_CK(cudaGraphInstantiate(&g_graph_exec[p], graph, 0));
+    GB_CK(cudaGraphDestroy(graph));
+  }
+  g_graph_args = key;
+  (void)st;
+  return 0;
+}
+
+extern "C" int gb_h_loop(const int64_t* args_host, int n_args, int nsteps, int parity, int step0, int compact_after,
+                         int* parity_out_host, void* stream) {
   if (n_args != HA_N) { gb_set_error("gb_h_loop: expected %d arguments, got %d", (int)HA_N, n_args); return -2; }
-  if (nsteps <= 0) return 0;
-  return args_host[HA_STREAMING] ? h_loop_impl<true>(args_host, nsteps, parity, (cudaStream_t)stream)
-                                 : h_loop_impl<false>(args_host, nsteps, parity, (cudaStream_t)stream);
+  if (nsteps < 0) return -2;
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool cs = args_host[HA_STREAMING] != 0;
+  const int period = args_host[HA_PERIOD] > 0 ? (int)args_host[HA_PERIOD] : 64;
+  int p = parity & 1;
+  // whole periods through the captured graphs
+  if (g_use_graphs && !g_time_k1 && step0 % period == 0 && nsteps >= period) {
+    int rc = cs ? h_loop_graphs<true>(args_host, period, st) : h_loop_graphs<false>(args_host, period, st);
+    if (rc) return rc;
+    while (nsteps >= period) {
+      GB_CK(cudaGraphLaunch(g_graph_exec[p], st));
+      p ^= 1; nsteps -= period; step0 += period;
+    }
+    if (nsteps == 0 && !compact_after) { if (parity_out_host) *parity_out_host = p; return 0; }
+    if (nsteps == 0) compact_after = 0;      // the last period ended with a compaction
+    if (nsteps == 0) { if (parity_out_host) *parity_out_host = p; return 0; }
+  }
+  return cs ? h_loop_impl<true>(args_host, nsteps, p, step0, compact_after, parity_out_host, st)
+            : h_loop_impl<false>(args_host, nsteps, p, step0, compact_after, parity_out_host, st);
 }
 extern "C" int gb_h_loop_time_k1(int enable) { g_time_k1 = enable != 0; g_ev_used = 0; return 0; }
 // elapsed ms of every timed k_slot_count launch since gb_h_loop_time_k1(1) (call after a synchronize); returns the count
@@ -515,4 +670,4 @@ extern "C" int gb_h_loop_k1_times(float* ms_host, int cap) {
   return n;
 }
 extern "C" int gb_h_loop_nargs(void) { return (int)HA_N; }
-extern "C" int gb_h_loop_kernels_per_step(void) { return 18; }
+extern "C" int gb_h_loop_kernels_per_step(void) { return 16; }

@@ -692,7 +692,7 @@ class Learner:
     HL_TB_CAP = 128
     HS = dict(T=0, STEP=1, HALT=2, EVN=3, MPREV=4, THR=5, C1=6, NCAND=7, NZ=8, M1=10, NT=11, ND=12, ROUND2=13,
               WIN_R0=14, WIN_NRES=15, WIN_CNT=16, WIN_J=17, MISMATCH=18, FLAGGED=19, NEWT=20, NTOK=21, OVF=22,
-              R2COUNT=23, MAXSTEPS=24, EVCAP=25, HALT_STEP=26, NTMAX=27)
+              R2COUNT=23, MAXSTEPS=24, EVCAP=25, HALT_STEP=26, NTMAX=27, N=28, NCL=29, CLCAP=30)
     HALT_NAMES = {1: "ties", 2: "candidates", 3: "collision", 4: "table", 5: "event log", 6: "empty", 7: "step log",
                   8: "count"}
 
@@ -713,8 +713,15 @@ class Learner:
         hl.log_key = _empty(cap, torch.int64)
         hl.log = {k: _empty(cap, torch.int32) for k in ("cnt", "r0", "nres", "evstart", "nk")}
         hl.nargs = _lib.load().gb_h_loop_nargs()
-        hl.enq = 0                    # iterations enqueued since the last sync (buffer parity on the host side)
+        hl.enq = 0                    # iterations enqueued since the state block was last written
+        hl.parity = 0                 # which token buffer is current on the device (0 = ts.a)
         hl.Tmax = ts.T
+        hl.rmark = _zeros(ts.cap, torch.uint8)
+        hl.cl_key = _empty(ts.cap, torch.int64)
+        hl.cl_j = _empty(ts.cap, torch.int32)
+        hl.cl_r = _empty(ts.cap, torch.int32)
+        hl.period = 64
+        hl.lazy = 0
         hl.halts = {}
         hl.r2 = 0
         hl.steps = 0
@@ -725,12 +732,12 @@ class Learner:
         a, b = ts.a, ts.b
         P = _lib.ptr
         vals = [P(hl.hs), P(hl.hs64), P(a["hsh"]), P(b["hsh"]), P(a["glue"]), P(b["glue"]), P(a["pos"]), P(b["pos"]),
-                P(a["len"]), P(b["len"]), P(a["tid"]), P(b["tid"]), P(ts.flags), P(ts.scratch), P(self.powtab), HASH_BASE,
+                P(a["len"]), P(b["len"]), P(a["tid"]), P(b["tid"]), P(ts.flags), P(hl.rmark), P(ts.scratch), P(self.powtab), HASH_BASE,
                 P(self.rbins), self.bb.R, P(sk.slots), sk.log2ns, P(sk.bmax), P(sk.cand), sk.CAP, sk.variant, sk.ctas,
                 P(sk.small.keys), P(sk.small.cnt), P(sk.small.min), sk.small.M, P(hl.tie_keys), P(hl.tie_min),
                 P(hl.strbuf), hl.stride, P(self.ev_left), P(self.ev_right), P(self.ev_p), P(hl.log_key),
-                P(hl.log["cnt"]), P(hl.log["r0"]), P(hl.log["nres"]), P(hl.log["evstart"]), P(hl.log["nk"]), hl.Tmax,
-                1 if 16 * hl.Tmax > SlotSketch.STREAM_BYTES else 0]
+                P(hl.log["cnt"]), P(hl.log["r0"]), P(hl.log["nres"]), P(hl.log["evstart"]), P(hl.log["nk"]),
+                P(hl.cl_key), P(hl.cl_j), P(hl.cl_r), hl.Tmax, 1 if 16 * hl.Tmax > SlotSketch.STREAM_BYTES else 0, hl.period]
         assert len(vals) == hl.nargs, (len(vals), hl.nargs)
         return (C.c_int64 * len(vals))(*[v if v < (1 << 63) else v - (1 << 64) for v in vals])
 
@@ -739,6 +746,8 @@ class Learner:
         hl, H = self.hl, self.HS
         h = np.zeros(32, dtype=np.int64)
         h[H["T"]] = self._ts.T
+        h[H["N"]] = self._ts.T
+        h[H["CLCAP"]] = self._ts.cap
         h[H["EVN"]] = self._ev_n
         h[H["MPREV"]] = self._pop_log[-1][0] if self._pop_log else 0
         h[H["NTOK"]] = len(self._tokens)
@@ -746,7 +755,8 @@ class Learner:
         h[H["EVCAP"]] = self.ev_left.numel()
         hl.hs.copy_(torch.from_numpy(h.astype(np.int32)))
         hl.enq = 0
-        hl.Tmax = self._ts.T
+        hl.parity = 0
+        self._ts.flags.zero_()      # (hl.Tmax stays the initial upper bound: same arguments -> the captured graphs are reused)
         hl.args = self._hl_args()
 
     def enqueue(self, nsteps):
@@ -755,16 +765,33 @@ class Learner:
             self._hl_init()
             self._hl_push_state()
         hl = self.hl
-        _lib.call_n("gb_h_loop", nsteps * 18, hl.args, hl.nargs, nsteps, hl.enq & 1)
-        hl.enq += nsteps
+        hl.lazy += nsteps                   # launched in whole compaction periods (CUDA-graph replays), the rest at sync()
         self._pending += nsteps
         self.n_steps += nsteps
+        if hl.lazy >= 4 * hl.period:
+            self._hl_flush(hl.lazy // hl.period * hl.period)
+
+    def _hl_flush(self, n):
+        hl = self.hl
+        if n > 0:
+            self._hl_call(n, 0)
+            hl.enq += n
+            hl.lazy -= n
+
+    def _hl_call(self, nsteps, compact_after):
+        hl = self.hl
+        out = C.c_int(0)
+        _lib.call_n("gb_h_loop", nsteps * 16 + 4 * (nsteps // hl.period + compact_after), hl.args, hl.nargs, nsteps, hl.parity,
+                    hl.enq, compact_after, C.byref(out))
+        hl.parity = out.value
 
     def sync(self):
         """drain the device loop: read the state block and the step log, materialise vocabulary entries / pop log;
         an iteration the device could not resolve runs once on the host path, the rest is re-enqueued"""
         while self._pending:
             hl, H = self.hl, self.HS
+            self._hl_flush(hl.lazy)
+            self._hl_call(0, 1)                                              # physical compaction: `len` is plain again
             h = hl.hs.cpu().numpy().astype(np.int64) & 0xFFFFFFFF            # the one blocking read
             done, halt = int(h[H["STEP"]]), int(h[H["HALT"]])
             want = self._pending
@@ -780,11 +807,21 @@ class Learner:
                     self._tokens[n] = json.loads(key_str)
                     self._pop_log.append((int(lg["cnt"][s]), key_str))
                     self._step_events.append((n, int(lg["evstart"][s]), int(lg["nk"][s]), keys[s]))
-                if done & 1:
-                    self._ts.swap()
+                # the device appends an iteration's merge events in arbitrary order: sort each iteration's range by position
+                e0, e1 = self._ev_n, int(h[H["EVN"]])
+                if e1 > e0:
+                    el, er = _u32(self.ev_left[e0:e1]), _u32(self.ev_right[e0:e1])
+                    seg = np.repeat(np.arange(done), lg["nk"])
+                    order = np.lexsort((el, seg))
+                    self.ev_left[e0:e1] = torch.from_numpy(el[order].astype(np.int32)).to(_dev())
+                    self.ev_right[e0:e1] = torch.from_numpy(er[order].astype(np.int32)).to(_dev())
                 self._ts.T = int(h[H["T"]])
-                self._ev_n = int(h[H["EVN"]])
+                self._ev_n = e1
                 self.n_steps += done
+            if hl.parity:
+                self._ts.swap()
+            if int(h[H["N"]]) != int(h[H["T"]]):
+                raise RuntimeError(f"compaction left {int(h[H['N']])} entries for {int(h[H['T']])} live tokens")
             hl.steps += done
             hl.r2 += int(h[H["R2COUNT"]])
             hl.ntmax = max(getattr(hl, "ntmax", 0), int(h[H["NTMAX"]]))
