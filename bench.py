@@ -136,6 +136,7 @@ def k1_scale_probe(learner, mode, reps=20, target_tokens=48_000_000):
     T = T0 * rep
     pad = lambda t: torch.cat([t, torch.zeros(8, dtype=t.dtype, device=t.device)])
     sk = E.SlotSketch(T0)          # same slot count as the learner's own sketch: the tiled data has the same distinct keys
+    sk.variant = 2                 # 48 M tokens: shared-memory hot stage on
     if mode == "H":
         h = pad(ts.a["hsh"][:T0].repeat(rep)); g = pad(ts.a["glue"][:T0].repeat(rep)); l = pad(ts.a["len"][:T0].repeat(rep))
         l[T:] = 1
@@ -299,6 +300,7 @@ def main():
         for _ in range(args.steps):
             L2.step()
         ts = L2.ts
+        n_vocab = len(L2.tokens)                       # formats the vocabulary entries / pop log of every iteration
         out = [ts.a[f][:ts.T].cpu() for f in ("pos", "len", "tid")]
         n_ev = L2.ev_n
         out += [L2.ev_left[:n_ev].cpu(), L2.ev_right[:n_ev].cpu()]
@@ -311,7 +313,7 @@ def main():
         d2h = sum(o.numel() * o.element_size() for o in out)
         e2e = {"value": args.steps / dt, "unit": "merge_iters/s", "h2d_bytes_per_step": L2.bb.h2d_bytes / args.steps,
                "d2h_bytes_per_step": d2h / args.steps, "seconds": dt,
-               "note": "Learner(host arrays): H2D of 72 B/residue, K3 thresholds+binning, residue tokens, K merges, D2H of segmentation + merge events"}
+               "note": "Learner(host arrays): H2D of 72 B/residue, K3 thresholds+binning, residue tokens, K merges, D2H of the step log + vocabulary entries formatted on the host, D2H of segmentation + merge events"}
         del L2
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

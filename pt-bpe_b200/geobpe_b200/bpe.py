@@ -291,7 +291,7 @@ class BPE(_View):
     def _tokens(self):
         L = self.__dict__.get("_learner")
         if L is not None:
-            L.sync()
+            L.tokens                    # drains the device loop and formats the entries it logged (same dict object)
         return self.__dict__.get("_tokens_")
 
     @_tokens.setter
@@ -302,7 +302,7 @@ class BPE(_View):
         """pickle layout of encode.py:403-427: vocabulary + hyper-parameters + materialised tokenizers; the device
         state (HBM buffers) is not part of the pickle"""
         if self._learner is not None:
-            self._learner.sync()
+            self._learner.tokens
         d = dict(self.__dict__)
         for k in ("_learner", "_export", "_ev_cache"):
             d[k] = None

@@ -19,28 +19,39 @@ __device__ __forceinline__ void hl_halt(u32* hs, u32 code) {
   if (atomicCAS(&hs[HS_HALT], 0u, code) == 0u) hs[HS_HALT_STEP] = hs[HS_STEP];
 }
 
-// ---- per-iteration reset ---------------------------------------------------------------------------------------
-__global__ void hl_begin(u32* __restrict__ hs) {
-  if (hs[HS_HALT]) return;
-  if (hs[HS_STEP] >= hs[HS_MAXSTEPS]) { hl_halt(hs, HALT_STEPS); return; }
-  hs[HS_C1] = 0; hs[HS_NCAND] = 0; hs[HS_NZ] = 0; hs[HS_PAD0] = 0;
-  hs[HS_M1] = 0; hs[HS_NT] = 0; hs[HS_ND] = 0; hs[HS_ROUND2] = 0;
-  hs[HS_MISMATCH] = 0; hs[HS_FLAGGED] = 0; hs[HS_OVF] = 0; hs[HS_NEWT] = 0; hs[HS_NCL] = 0;
-}
-
 // ---- slot scan -----------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) hl_slots_max(const uint4* __restrict__ slots4, u32* __restrict__ bmax, u32* __restrict__ hs) {
+// one pass over the slot counters: per-chunk maxima (bmax), global max c1, non-zero count, and the round-1 candidate
+// list = slots with count >= thr1 = 0.9 * (previous iteration's max count).  The max count never grows from one
+// iteration to the next, so the exact max is almost always >= thr1 and one candidate pass is conclusive; otherwise
+// hl_decide asks for a second round (thr = c1 when nothing / too much was collected, else the best exact count).
+__device__ __forceinline__ u32 hl_thr1(const u32* hs) {
+  const u32 mp = hs[HS_MPREV];
+  return mp ? max(1u, (u32)(((u64)mp * 9ull) / 10ull)) : 0xFFFFFFFFu;
+}
+__global__ void __launch_bounds__(256) hl_slots_scan(const uint4* __restrict__ slots4, u32* __restrict__ bmax, u32* __restrict__ hs,
+                                                      u32* __restrict__ cand, u32 cap) {
   if (hs[HS_HALT]) return;
   __shared__ u32 s_mx[8], s_nz[8];
-  const uint4* p = slots4 + (i64)blockIdx.x * (KS_CHUNK / 4);
+  const u32 thr = hl_thr1(hs);
+  if (blockIdx.x == 0 && threadIdx.x == 0) hs[HS_THR] = thr;
+  const i64 base4 = (i64)blockIdx.x * (KS_CHUNK / 4);
   uint4 v[4];
 #pragma unroll
-  for (int k = 0; k < 4; ++k) v[k] = p[k * 256 + threadIdx.x];
+  for (int k = 0; k < 4; ++k) v[k] = slots4[base4 + k * 256 + threadIdx.x];
   u32 mx = 0, nz = 0;
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    mx = max(max(mx, v[k].x), max(max(v[k].y, v[k].z), v[k].w));
-    nz += (v[k].x != 0) + (v[k].y != 0) + (v[k].z != 0) + (v[k].w != 0);
+    u32 a[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+    mx = max(max(mx, a[0]), max(max(a[1], a[2]), a[3]));
+    nz += (a[0] != 0) + (a[1] != 0) + (a[2] != 0) + (a[3] != 0);
+    if (max(max(a[0], a[1]), max(a[2], a[3])) >= thr) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        if (a[e] >= thr) {
+          u32 q = atomicAdd(&hs[HS_NCAND], 1u);
+          if (q < cap) cand[q] = (u32)(4 * (base4 + k * 256 + threadIdx.x) + e);
+        }
+    }
   }
   for (int o = 16; o; o >>= 1) {
     mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
@@ -55,19 +66,11 @@ __global__ void __launch_bounds__(256) hl_slots_max(const uint4* __restrict__ sl
     if (nz) atomicAdd(&hs[HS_NZ], nz);
   }
 }
-// round 1: thr = min(c1, 0.9 * previous max) -- the max count never grows from one iteration to the next, so the exact
-// max is almost always >= thr and one candidate pass is conclusive.  round 2: thr = best exact count of round 1.
-__device__ __forceinline__ u32 hl_thr(const u32* hs, int round) {
-  if (round == 2) return hs[HS_THR];
-  u32 c1 = hs[HS_C1], mp = hs[HS_MPREV];
-  u32 t = mp ? max(1u, (u32)(((u64)mp * 9ull) / 10ull)) : c1;
-  return min(c1, t);
-}
 __global__ void __launch_bounds__(256) hl_slots_collect(const uint4* __restrict__ slots4, const u32* __restrict__ bmax,
                                                          u32* __restrict__ hs, int round, u32* __restrict__ cand, u32 cap) {
-  if (hs[HS_HALT] || (round == 2 && !hs[HS_ROUND2])) return;
-  const u32 thr = hl_thr(hs, round);
-  if (round == 1 && blockIdx.x == 0 && threadIdx.x == 0) hs[HS_THR] = thr;
+  if (hs[HS_HALT] || !hs[HS_ROUND2]) return;       // second round only (round 1 is collected by hl_slots_scan)
+  const u32 thr = hs[HS_THR];
+  (void)round;
   if (thr == 0 || bmax[blockIdx.x] < thr) return;
   const i64 base4 = (i64)blockIdx.x * (KS_CHUNK / 4);
 #pragma unroll
@@ -83,16 +86,8 @@ __global__ void __launch_bounds__(256) hl_slots_collect(const uint4* __restrict_
       }
   }
 }
-__global__ void __launch_bounds__(256) hl_table_clear(u64* __restrict__ tk, u32* __restrict__ tc, u32* __restrict__ tm, i64 M,
-                                                       const u32* __restrict__ hs, int round) {
-  if (hs[HS_HALT] || (round == 2 && !hs[HS_ROUND2])) return;
-  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (i64)gridDim.x * blockDim.x) {
-    tk[i] = GB_EMPTY_KEY; tc[i] = 0u; tm[i] = 0xFFFFFFFFu;
-  }
-}
-
 // ---- exact argmax over the small table + conclusiveness test (one block) -----------------------------------------
-__global__ void __launch_bounds__(1024) hl_decide(const u64* __restrict__ tk, const u32* __restrict__ tc, const u32* __restrict__ tm,
+__global__ void __launch_bounds__(1024) hl_decide(u64* __restrict__ tk, u32* __restrict__ tc, u32* __restrict__ tm,
                                                    i64 M, u32* __restrict__ hs, int round, u64* __restrict__ tie_keys,
                                                    u32* __restrict__ tie_min, u32 cap) {
   if (hs[HS_HALT] || (round == 2 && !hs[HS_ROUND2])) return;
@@ -119,7 +114,7 @@ __global__ void __launch_bounds__(1024) hl_decide(const u64* __restrict__ tk, co
     if (hs[HS_OVF] == 1 || (u64)nd * 2 > (u64)M) { hl_halt(hs, HALT_TABLE); return; }
     const bool cand_over = hs[HS_NCAND] > cap || hs[HS_OVF] == 2;
     if (round == 1) {
-      if (cand_over) {                        // too many slots above 0.9 * previous max: retry with the top slots only
+      if (cand_over || hs[HS_NCAND] == 0) {   // too many / no slots above 0.9 * previous max: retry with the top slots only
         hs[HS_ROUND2] = 1; hs[HS_THR] = hs[HS_C1]; hs[HS_NCAND] = 0; hs[HS_OVF] = 0; hs[HS_NCL] = 0; hs[HS_R2COUNT] += 1;
       } else if (mx < hs[HS_THR]) {           // inconclusive: a key outside the candidates could reach mx
         hs[HS_ROUND2] = 1; hs[HS_THR] = max(mx, 1u); hs[HS_NCAND] = 0; hs[HS_NCL] = 0; hs[HS_R2COUNT] += 1;
@@ -128,6 +123,8 @@ __global__ void __launch_bounds__(1024) hl_decide(const u64* __restrict__ tk, co
       if (cand_over || mx < hs[HS_THR]) hl_halt(hs, HALT_CAND);
     }
   }
+  // the table is consumed (ties are copied out): leave it cleared for the next candidate pass
+  for (i64 i = threadIdx.x; i < M; i += blockDim.x) { tk[i] = GB_EMPTY_KEY; tc[i] = 0u; tm[i] = 0xFFFFFFFFu; }
 }
 
 // ---- the reference's tie-break on the device -------------------------------------------------------------------
@@ -410,6 +407,11 @@ __global__ void hl_end(u32* __restrict__ hs, const u64* __restrict__ hs64, u64* 
   log_key[s] = hs64[0]; log_cnt[s] = hs[HS_WIN_CNT]; log_r0[s] = hs[HS_WIN_R0]; log_nres[s] = hs[HS_WIN_NRES];
   log_evstart[s] = hs[HS_EVN]; log_nk[s] = nk;
   hs[HS_EVN] += nk; hs[HS_T] -= nk; hs[HS_MPREV] = hs[HS_WIN_CNT]; hs[HS_STEP] = s + 1; hs[HS_NTOK] += 1;
+  // reset of the per-iteration words (the host writes them as zeros when it (re)starts the loop)
+  hs[HS_C1] = 0; hs[HS_NCAND] = 0; hs[HS_NZ] = 0; hs[HS_PAD0] = 0;
+  hs[HS_M1] = 0; hs[HS_NT] = 0; hs[HS_ND] = 0; hs[HS_ROUND2] = 0;
+  hs[HS_MISMATCH] = 0; hs[HS_FLAGGED] = 0; hs[HS_OVF] = 0; hs[HS_NEWT] = 0; hs[HS_NCL] = 0;
+  if (s + 1 >= hs[HS_MAXSTEPS]) hl_halt(hs, HALT_STEPS);
 }
 
 // ---- occasional physical compaction of the lazily compacted arrays (runs between iterations, ignores the halt flag) --
@@ -553,7 +555,6 @@ static int h_loop_impl(const int64_t* a, int nsteps, int parity, int step0, int 
   const unsigned scan_blocks = (unsigned)(((i64)1 << log2ns) / KS_CHUNK);
   const int count_blocks = gb_blocks_for(Nmax, 2 * KS_TILE, sms * ctas);
   const int pass_blocks = gb_blocks_for(Nmax, 2 * KS_TILE, sms * 2);
-  const int clear_blocks = gb_blocks_for(M, 1024, 64);
   const int list_blocks = sms * 2;
   const unsigned nb = (unsigned)((Nmax + HL_CHUNK - 1) / HL_CHUNK);
   const size_t smem = cache ? 2 * sizeof(u32) * KS_CACHE : 0;
@@ -575,16 +576,14 @@ static int h_loop_impl(const int64_t* a, int nsteps, int parity, int step0, int 
   };
   for (int s = 0; s < nsteps; ++s) {
     KeysHLT<CS> kf{hsh[p], glue[p], len[p], powtab, P};
-    hl_begin<<<1, 1, 0, st>>>(hs);
     GB_CK(cudaMemsetAsync(slots, 0, sizeof(u32) << log2ns, st));
     if (g_time_k1) GB_CK(cudaEventRecord(hl_event(), st));
     if (cache) k_slot_count<KeysHLT<CS>, false, 1, false><<<count_blocks, KS_THREADS, smem, st>>>(kf, Nmax, slots, shift, nullptr, hs);
     else k_slot_count<KeysHLT<CS>, false, 0, false><<<count_blocks, KS_THREADS, 0, st>>>(kf, Nmax, slots, shift, nullptr, hs);
     if (g_time_k1) GB_CK(cudaEventRecord(hl_event(), st));
-    hl_slots_max<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs);
+    hl_slots_scan<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs, cand, (u32)cap);
     for (int round = 1; round <= 2; ++round) {
-      hl_slots_collect<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs, round, cand, (u32)cap);
-      hl_table_clear<<<clear_blocks, 256, 0, st>>>(tk, tc, tm, M, hs, round);
+      if (round == 2) hl_slots_collect<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs, round, cand, (u32)cap);
       hl_cand_count<CS><<<pass_blocks, KS_THREADS, 0, st>>>(kf, shift, cand, (u32)cap, tk, tc, tm, (u64)(M - 1), hs, round, cl_key, cl_j);
       hl_decide<<<1, 1024, 0, st>>>(tk, tc, tm, M, hs, round, tie_keys, tie_min, (u32)cap);
     }
@@ -670,4 +669,4 @@ extern "C" int gb_h_loop_k1_times(float* ms_host, int cap) {
   return n;
 }
 extern "C" int gb_h_loop_nargs(void) { return (int)HA_N; }
-extern "C" int gb_h_loop_kernels_per_step(void) { return 16; }
+extern "C" int gb_h_loop_kernels_per_step(void) { return 12; }

@@ -278,7 +278,8 @@ class SlotSketch:
         if log2ns is None:
             log2ns = max(16, min(24, (max(n_pairs_bound, 2) - 1).bit_length()))   # NS >= pairs >= distinct; <= 64 MB (L2)
         self.log2ns = log2ns
-        self.variant = variant
+        # the per-CTA shared-memory stage only pays when a CTA sees many more pairs than it has cache entries
+        self.variant = variant if n_pairs_bound >= 296 * 32768 else (variant & ~6)
         self.ctas = ctas_per_sm
         self.slots = _zeros(1 << log2ns, torch.int32)
         self.bmax = _zeros(max(1, (1 << log2ns) // 4096), torch.int32)
@@ -440,11 +441,25 @@ class Learner:
 
     @property
     def tokens(self):
-        self._drain(); return self._tokens
+        self._drain(); self._materialise_log(); return self._tokens
 
     @property
     def pop_log(self):
-        self._drain(); return self._pop_log
+        self._drain(); self._materialise_log(); return self._pop_log
+
+    def _materialise_log(self):
+        """vocabulary entries / pop log of the iterations the device loop ran: the device logs (count, example window)
+        per iteration; the reference's key dict and its json string are formatted here, on first use"""
+        raw = getattr(self, "_raw", None)
+        if not raw:
+            return
+        self._raw = []
+        for cnt, r0, nres in raw:
+            dicts = self._h_key_dicts(r0.tolist(), nres.tolist())
+            for s in range(len(cnt)):
+                key_str = json.dumps(dicts[s], sort_keys=True)
+                self._tokens[len(self._tokens)] = json.loads(key_str)
+                self._pop_log.append((int(cnt[s]), key_str))
 
     @property
     def step_events(self):
@@ -674,6 +689,7 @@ class Learner:
         n = len(self.tokens)
         self.tokens[n] = json.loads(key_str)
         self.pop_log.append((mx, key_str))
+        self._ntok, self._last_count = n + 1, mx
         _lib.call("gb_flag_pairs_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), HASH_BASE,
                   key, _lib.ptr(ts.flags))
         if self.verify:                                # checked after the merge's single read-back (u32[3], u32[4])
@@ -722,6 +738,9 @@ class Learner:
         hl.cl_r = _empty(ts.cap, torch.int32)
         hl.period = 64
         hl.lazy = 0
+        self._raw = []
+        self._ntok = len(self.tokens)
+        self._last_count = self.pop_log[-1][0] if self.pop_log else 0
         hl.halts = {}
         hl.r2 = 0
         hl.steps = 0
@@ -749,13 +768,14 @@ class Learner:
         h[H["N"]] = self._ts.T
         h[H["CLCAP"]] = self._ts.cap
         h[H["EVN"]] = self._ev_n
-        h[H["MPREV"]] = self._pop_log[-1][0] if self._pop_log else 0
-        h[H["NTOK"]] = len(self._tokens)
+        h[H["MPREV"]] = self._last_count
+        h[H["NTOK"]] = self._ntok
         h[H["MAXSTEPS"]] = self.HL_LOG_CAP
         h[H["EVCAP"]] = self.ev_left.numel()
         hl.hs.copy_(torch.from_numpy(h.astype(np.int32)))
         hl.enq = 0
         hl.parity = 0
+        _lib.call("gb_table_clear", *self.sketch.small.ptrs())     # hl_decide leaves it cleared from then on
         self._ts.flags.zero_()      # (hl.Tmax stays the initial upper bound: same arguments -> the captured graphs are reused)
         hl.args = self._hl_args()
 
@@ -781,7 +801,7 @@ class Learner:
     def _hl_call(self, nsteps, compact_after):
         hl = self.hl
         out = C.c_int(0)
-        _lib.call_n("gb_h_loop", nsteps * 16 + 4 * (nsteps // hl.period + compact_after), hl.args, hl.nargs, nsteps, hl.parity,
+        _lib.call_n("gb_h_loop", nsteps * 12 + 4 * (nsteps // hl.period + compact_after), hl.args, hl.nargs, nsteps, hl.parity,
                     hl.enq, compact_after, C.byref(out))
         hl.parity = out.value
 
@@ -800,13 +820,11 @@ class Learner:
             if done:
                 keys = hl.log_key[:done].cpu().numpy().astype(np.uint64).tolist()
                 lg = {k: _u32(v[:done]) for k, v in hl.log.items()}
-                dicts = self._h_key_dicts(lg["r0"].tolist(), lg["nres"].tolist())
+                self._raw.append((lg["cnt"], lg["r0"], lg["nres"]))          # formatted lazily (_materialise_log)
                 for s in range(done):
-                    key_str = json.dumps(dicts[s], sort_keys=True)
-                    n = len(self._tokens)
-                    self._tokens[n] = json.loads(key_str)
-                    self._pop_log.append((int(lg["cnt"][s]), key_str))
-                    self._step_events.append((n, int(lg["evstart"][s]), int(lg["nk"][s]), keys[s]))
+                    self._step_events.append((self._ntok + s, int(lg["evstart"][s]), int(lg["nk"][s]), keys[s]))
+                self._ntok += done
+                self._last_count = int(lg["cnt"][-1])
                 # the device appends an iteration's merge events in arbitrary order: sort each iteration's range by position
                 e0, e1 = self._ev_n, int(h[H["EVN"]])
                 if e1 > e0:
