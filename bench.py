@@ -35,7 +35,12 @@ def parse():
     ap.add_argument("--backbones", type=int, default=10000)
     ap.add_argument("--residues", type=int, default=256)
     ap.add_argument("--bins", type=int, default=None)
-    ap.add_argument("--cpu-backbones", type=int, default=320)
+    ap.add_argument("--cpu-backbones", type=int, default=None,
+                    help="backbones of the CPU sample (default: 2500 for --impl reference, 320 for the cpu_baseline leg)")
+    ap.add_argument("--induce-backbones", type=int, default=100000, help="held-out backbones x 512 residues (BASELINE configs[2])")
+    ap.add_argument("--induce-residues", type=int, default=512)
+    ap.add_argument("--induce-merges", type=int, default=2000)
+    ap.add_argument("--no-induce", action="store_true")
     ap.add_argument("--cpu-steps", type=int, default=2000)
     ap.add_argument("--no-scale-probe", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -102,7 +107,7 @@ def reference_arm(args):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import geobpe_oracle as O
     from geobpe_b200 import synthetic
-    S, n = args.cpu_backbones, args.residues
+    S, n = args.cpu_backbones or (2500 if args.impl == "reference" else 320), args.residues
     vals, offs = synthetic.generate(S, n, seed=0)
     strucs = synthetic.to_structures(vals, offs)
     t0 = time.perf_counter()
@@ -171,6 +176,49 @@ def k1_scale_probe(learner, mode, reps=20, target_tokens=48_000_000):
     assert int(sk.small.overflow.item()) == 0
     return {"tokens": T, "bytes_per_token": bpt, "ms": avg, "ms_min": best, "pass2_ms": avg2, "pass2_ms_min": best2,
             "slots": 1 << sk.log2ns, "nonzero_slots": int(so[2]), "top_slot_count": int(so[0])}
+
+
+def induce_arm(args, rank, world, barrier):
+    """BASELINE configs[2]: frozen-vocabulary encode (K7, BPE.tokenize / bin/induce.py) of held-out synthetic backbones
+    against a medoid-mode vocabulary learned here on the configs[1] training set.  Host arrays in, token arrays out;
+    the held-out set is split evenly over the ranks (no collective on this path)."""
+    import torch
+    from geobpe_b200 import engine as E, synthetic
+    hp = hparams("M", None)
+    vals, offs = synthetic.generate(args.backbones, args.residues, seed=0)
+    t0 = time.perf_counter()
+    L = E.Learner(vals, offs, rng=np.random.default_rng(0), verify=True, **hp)
+    while L.n_steps < args.induce_merges:
+        L.step()
+    torch.cuda.synchronize()
+    t_learn = time.perf_counter() - t0
+    tokens, sphere, th = L.tokens, L.sphere_dict, L.th.thresholds
+    del L
+    torch.cuda.empty_cache()
+    S = max(1, args.induce_backbones // world)
+    hv, ho = synthetic.generate(S, args.induce_residues, seed=1000 + rank)
+    R = int(ho[-1])
+    barrier()
+    t0 = time.perf_counter()
+    ind = E.Inducer(hv, ho, tokens, sphere, th, hp["std_bonds"])
+    ts = ind.ts
+    out = [ts.a[f][:ts.T].cpu() for f in ("pos", "len", "tid")]
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([dt], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    return {"metric": "residues_per_s_encoded", "value": R * world / dt, "unit": "residues/s", "seconds": dt,
+            "backbones": S * world, "residues": R * world, "residues_per_backbone": args.induce_residues,
+            "vocabulary_merges": args.induce_merges, "vocabulary_tokens": len(tokens), "tokens_out_per_rank": int(ts.T),
+            "rejected_backbones_rank0": int(ind.failed.sum()), "merges_fired_rank0": int(ind.n_steps),
+            "h2d_bytes": int(hv.nbytes + ho.nbytes), "d2h_bytes": int(sum(o.numel() * o.element_size() for o in out)),
+            "vocabulary_learn_seconds": t_learn,
+            "note": "host arrays -> H2D -> K3 binning -> residue medoid assignment (K4/K5) -> merge replay (K2 + K4/K5 per vocabulary "
+                    "merge) -> D2H of the segmentation; backbones whose glue angles leave the training range are rejected like the "
+                    "reference's ValueError (bpe.py:1105-1108)"}
 
 
 def main():
@@ -315,6 +363,12 @@ def main():
                "d2h_bytes_per_step": d2h / args.steps, "seconds": dt,
                "note": "Learner(host arrays): H2D of 72 B/residue, K3 thresholds+binning, residue tokens, K merges, D2H of the step log + vocabulary entries formatted on the host, D2H of segmentation + merge events"}
         del L2
+    induce = None
+    if not args.no_induce:
+        try:
+            induce = induce_arm(args, rank, world, barrier)
+        except Exception as ex:          # the learn line must survive an induce failure
+            induce = {"error": f"{type(ex).__name__}: {ex}"}
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = reference_arm(args)
@@ -338,7 +392,7 @@ def main():
                      "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "avg_ms": k1_avg_ms, "algorithmic_bytes_per_launch": k1_bytes,
                      "bytes_per_token": bpt, "share_of_step": k1_share, "timing": k1_note},
-        "roofline_at_scale": scale, "cpu_baseline": cpu,
+        "roofline_at_scale": scale, "induce": induce, "cpu_baseline": cpu,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
