@@ -290,7 +290,12 @@ def main():
     k1_ms = [a.elapsed_time(b) for a, b, _ in L.k1_events]
     k1_T = [t for _, _, t in L.k1_events]
     k1_note = "CUDA events around every K1 launch of the timed region"
-    if L.async_steps:
+    if L.async_steps and world > 1:       # sharded loop: events sit around every part-0 call of the timed region (memset + K1)
+        nk = [e[2] for e in L.step_events[-args.steps:]]
+        Ts = (T_start - np.concatenate([[0], np.cumsum(nk)[:-1]])).tolist()
+        k1_T = [Ts[i] if t is None and i < len(Ts) else (t or T_end) for i, t in enumerate(k1_T)]
+        k1_note = "CUDA events around every slots-memset + K1 launch of the timed region (sharded device loop)"
+    elif L.async_steps:
         # the timed region replays CUDA graphs (no events inside); K1 is timed in an instrumented continuation of the
         # same run: the next iterations launched kernel by kernel with CUDA events around every k_slot_count launch
         import ctypes

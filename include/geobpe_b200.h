@@ -213,6 +213,12 @@ int gb_pack_result(const uint32_t* out4, const int32_t* overflow, const uint64_t
 int gb_h_loop(const int64_t* args_host, int n_args, int nsteps, int parity, int step0, int compact_after,
               int* parity_out_host, void* stream);
 int gb_h_loop_nargs(void);
+/* sharded (multi-GPU) run: one iteration = parts 0..4 with a collective issued by the caller after parts 0-3
+ * (allreduce-sum of the slot counters, allgather of the xbuf (key, count) lists twice, allreduce-max of the tie-string
+ * buffer); see csrc/k_hloop_dist.cuh.  Compaction / state read-back go through gb_h_loop(nsteps = 0, compact_after = 1). */
+int gb_h_loop_part(const int64_t* args_host, int n_args, int part, int parity, void* stream);
+int64_t gb_h_loop_xbuf_elems(void);
+int64_t gb_h_loop_sbuf_bytes(int stride);
 /* whole compaction periods are replayed from captured CUDA graphs (default on) */
 int gb_h_loop_use_graphs(int enable);
 int gb_h_loop_kernels_per_step(void);

@@ -51,6 +51,9 @@ SIGNATURES = {
     "gb_rmsd_matrix": [P, I32, I32, P, P],
     "gb_h_loop": [P, I32, I32, I32, I32, I32, P, P],
     "gb_h_loop_nargs": [],
+    "gb_h_loop_part": [P, I32, I32, I32, P],
+    "gb_h_loop_xbuf_elems": [],
+    "gb_h_loop_sbuf_bytes": [I32],
     "gb_h_loop_use_graphs": [I32],
     "gb_h_loop_kernels_per_step": [],
     "gb_h_loop_time_k1": [I32],
@@ -60,7 +63,7 @@ SIGNATURES = {
     "gb_sm_count": [],
     "gb_select_scratch_elems": [I64],
 }
-_RESTYPES = {"gb_last_error": C.c_char_p, "gb_select_scratch_elems": I64}
+_RESTYPES = {"gb_last_error": C.c_char_p, "gb_select_scratch_elems": I64, "gb_h_loop_xbuf_elems": I64, "gb_h_loop_sbuf_bytes": I64}
 
 _lib = None
 launches = 0  # kernels launched through the C ABI (bench.py reports it)

@@ -23,7 +23,7 @@ enum {
   HS_M1, HS_NT, HS_ND, HS_ROUND2, HS_WIN_R0, HS_WIN_NRES, HS_WIN_CNT, HS_WIN_J, HS_MISMATCH, HS_FLAGGED,
   HS_NEWT, HS_NTOK, HS_OVF, HS_R2COUNT, HS_MAXSTEPS, HS_EVCAP, HS_HALT_STEP, HS_NTMAX,
   HS_N /* array extent incl. dead entries */, HS_NCL /* candidate-pair list length */, HS_CLCAP, HS_CMPT /* compaction total */,
-  HS_WORDS = 32
+  HS_DIST /* 1 = sharded run: counts are global, occurrences local */, HS_WORDS = 64
 };
 
 // ---- pass 1 -----------------------------------------------------------------------------------------------------

@@ -237,6 +237,8 @@ __global__ void __launch_bounds__(HL_TB_CAP) hl_tiebreak(u32* __restrict__ hs, u
 }
 
 
+#include "k_hloop_dist.cuh"
+
 // ---- pass 2 on the lazy layout: exact counts of the candidate slots' keys + the list of those pairs ---------------
 template <bool CS>
 __global__ void __launch_bounds__(KS_THREADS, 2) hl_cand_count(KeysHLT<CS> kf, int shift, const u32* __restrict__ cand, u32 cap,
@@ -364,7 +366,7 @@ __global__ void __launch_bounds__(256) hl_apply_list(u32* __restrict__ hs, const
   if (hs[HS_HALT]) return;
   const bool t0 = blockIdx.x == 0 && threadIdx.x == 0;
   if (hs[HS_MISMATCH]) { if (t0) hl_halt(hs, HALT_COLLISION); return; }
-  if (hs[HS_FLAGGED] != hs[HS_WIN_CNT]) { if (t0) hl_halt(hs, HALT_COUNT); return; }
+  if (!hs[HS_DIST] && hs[HS_FLAGGED] != hs[HS_WIN_CNT]) { if (t0) hl_halt(hs, HALT_COUNT); return; }
   if (hs[HS_EVN] + hs[HS_FLAGGED] > hs[HS_EVCAP]) { if (t0) hl_halt(hs, HALT_EVLOG); return; }
   const u32 n = hs[HS_NCL], ev0 = hs[HS_EVN], new_tid = hs[HS_NTOK];
   const u64 win = hs64[0];
@@ -500,7 +502,7 @@ enum { HA_HS = 0, HA_HS64, HA_HSH0, HA_HSH1, HA_GLUE0, HA_GLUE1, HA_POS0, HA_POS
        HA_FLAGS, HA_RMARK, HA_SCRATCH, HA_POWTAB, HA_P, HA_RBINS, HA_R, HA_SLOTS, HA_LOG2NS, HA_BMAX, HA_CAND, HA_CAP,
        HA_VARIANT, HA_CTAS, HA_TK, HA_TC, HA_TM, HA_M, HA_TIEK, HA_TIEM, HA_STRBUF, HA_STRIDE, HA_EVL, HA_EVR, HA_EVP,
        HA_LKEY, HA_LCNT, HA_LR0, HA_LNRES, HA_LEVS, HA_LNK, HA_CLKEY, HA_CLJ, HA_CLR, HA_NMAX, HA_STREAMING,
-       HA_PERIOD, HA_N };
+       HA_PERIOD, HA_XBUF, HA_XALL, HA_WORLD, HA_RANK, HA_TIESK, HA_TIESM, HA_SBUF, HA_LOGSTR, HA_LOGSTRLEN, HA_N };
 
 // optional CUDA-event timing of the pair-count kernel inside the loop (bench.py's roofline leg)
 #include <vector>
@@ -659,6 +661,111 @@ extern "C" int gb_h_loop(const int64_t* args_host, int n_args, int nsteps, int p
   return cs ? h_loop_impl<true>(args_host, nsteps, p, step0, compact_after, parity_out_host, st)
             : h_loop_impl<false>(args_host, nsteps, p, step0, compact_after, parity_out_host, st);
 }
+
+// ---- sharded run: one iteration in five parts; the host issues a collective between consecutive parts -------------
+//   part 0: memset(slots), k_slot_count                         -> allreduce(sum) slots
+//   part 1: scan, pass 2 (round 1), export                      -> allgather x
+//   part 2: import, decide; round 2: collect, pass 2, export    -> allgather x
+//   part 3: import (round 2), decide (round 2), tie strings     -> allreduce(max) sbuf
+//   part 4: tie pick, flag, apply, unflag, end
+template <bool CS>
+static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t st) {
+  u32* hs = (u32*)a[HA_HS];
+  u64* hs64 = (u64*)a[HA_HS64];
+  const int p = parity & 1;
+  u64* hsh = (u64*)a[p ? HA_HSH1 : HA_HSH0];
+  u32* glue = (u32*)a[p ? HA_GLUE1 : HA_GLUE0];
+  u32* pos = (u32*)a[p ? HA_POS1 : HA_POS0];
+  u32* len = (u32*)a[p ? HA_LEN1 : HA_LEN0];
+  u32* tid = (u32*)a[p ? HA_TID1 : HA_TID0];
+  u8* flags = (u8*)a[HA_FLAGS];
+  u8* rmark = (u8*)a[HA_RMARK];
+  const u16* rbins = (const u16*)a[HA_RBINS];
+  const i64 R = a[HA_R];
+  u32* slots = (u32*)a[HA_SLOTS];
+  const int log2ns = (int)a[HA_LOG2NS];
+  u32* bmax = (u32*)a[HA_BMAX];
+  u32* cand = (u32*)a[HA_CAND];
+  const int cap = (int)a[HA_CAP];
+  const int cache = ((int)a[HA_VARIANT] >> 1) & 3;
+  const int ctas = a[HA_CTAS] > 0 ? (int)a[HA_CTAS] : 2;
+  u64* tk = (u64*)a[HA_TK]; u32* tc = (u32*)a[HA_TC]; u32* tm = (u32*)a[HA_TM];
+  const i64 M = a[HA_M];
+  u64* tie_keys = (u64*)a[HA_TIEK]; u32* tie_min = (u32*)a[HA_TIEM];
+  u64* tie_skeys = (u64*)a[HA_TIESK]; u32* tie_smin = (u32*)a[HA_TIESM];
+  char* sbuf = (char*)a[HA_SBUF];
+  const int stride = (int)a[HA_STRIDE];
+  u64* cl_key = (u64*)a[HA_CLKEY]; u32* cl_j = (u32*)a[HA_CLJ]; u32* cl_r = (u32*)a[HA_CLR];
+  u64* x = (u64*)a[HA_XBUF];
+  const u64* xall = (const u64*)a[HA_XALL];
+  const int world = (int)a[HA_WORLD], rank = (int)a[HA_RANK];
+  const i64 Nmax = a[HA_NMAX];
+  if (!x || !xall || !sbuf || world < 1 || log2ns < 12 || M <= 0 || (M & (M - 1)) || cap > KC_SET / 2 || cache > 1 || (stride & 127)) {
+    gb_set_error("gb_h_loop_part: bad arguments");
+    return -2;
+  }
+  int sms = gb_sm_count();
+  if (sms <= 0) sms = 148;
+  const int shift = 64 - log2ns;
+  const unsigned scan_blocks = (unsigned)(((i64)1 << log2ns) / KS_CHUNK);
+  const int count_blocks = gb_blocks_for(Nmax, 2 * KS_TILE, sms * ctas);
+  const int pass_blocks = gb_blocks_for(Nmax, 2 * KS_TILE, sms * 2);
+  const int list_blocks = sms * 2;
+  KeysHLT<CS> kf{hsh, glue, len, (const u64*)a[HA_POWTAB], (u64)a[HA_P]};
+  switch (part) {
+    case 0: {
+      const size_t smem = cache ? 2 * sizeof(u32) * KS_CACHE : 0;
+      GB_CK(cudaMemsetAsync(slots, 0, sizeof(u32) << log2ns, st));
+      if (cache) {
+        GB_CK(cudaFuncSetAttribute(k_slot_count<KeysHLT<CS>, false, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_slot_count<KeysHLT<CS>, false, 1, false><<<count_blocks, KS_THREADS, smem, st>>>(kf, Nmax, slots, shift, nullptr, hs);
+      } else {
+        k_slot_count<KeysHLT<CS>, false, 0, false><<<count_blocks, KS_THREADS, 0, st>>>(kf, Nmax, slots, shift, nullptr, hs);
+      }
+      break;
+    }
+    case 1:
+      hl_slots_scan<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs, cand, (u32)cap);
+      hl_cand_count<CS><<<pass_blocks, KS_THREADS, 0, st>>>(kf, shift, cand, (u32)cap, tk, tc, tm, (u64)(M - 1), hs, 1, cl_key, cl_j);
+      hl_table_export<<<1, 1024, 0, st>>>(tk, tc, M, hs, 1, x);
+      break;
+    case 2:
+      hl_table_import<<<1, 1024, 0, st>>>(tk, tc, tm, (u64)(M - 1), hs, 1, xall, world, rank);
+      hl_decide<<<1, 1024, 0, st>>>(tk, tc, tm, M, hs, 1, tie_keys, tie_min, (u32)cap);
+      hl_slots_collect<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs, 2, cand, (u32)cap);
+      hl_cand_count<CS><<<pass_blocks, KS_THREADS, 0, st>>>(kf, shift, cand, (u32)cap, tk, tc, tm, (u64)(M - 1), hs, 2, cl_key, cl_j);
+      hl_table_export<<<1, 1024, 0, st>>>(tk, tc, M, hs, 2, x);
+      break;
+    case 3:
+      hl_table_import<<<1, 1024, 0, st>>>(tk, tc, tm, (u64)(M - 1), hs, 2, xall, world, rank);
+      hl_decide<<<1, 1024, 0, st>>>(tk, tc, tm, M, hs, 2, tie_keys, tie_min, (u32)cap);
+      GB_CK(cudaMemsetAsync(sbuf, 0, 4 * HL_TB_CAP + (size_t)HL_TB_CAP * stride, st));
+      hl_tie_strings<<<1, HL_TB_CAP, 0, st>>>(hs, tie_keys, tie_min, tie_skeys, tie_smin, pos, len, rbins, R, sbuf, stride);
+      break;
+    case 4:
+      hl_tie_pick<<<1, HL_TB_CAP, 0, st>>>(hs, hs64, tie_skeys, tie_smin, pos, len, sbuf, stride, (char*)a[HA_LOGSTR], (u32*)a[HA_LOGSTRLEN]);
+      hl_flag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark, pos, len, rbins, R);
+      hl_apply_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, flags, rmark, hsh, glue, len, tid, pos,
+                                                 (u32*)a[HA_EVL], (u32*)a[HA_EVR], (u32*)a[HA_EVP]);
+      hl_unflag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark);
+      hl_end<<<1, 1, 0, st>>>(hs, hs64, (u64*)a[HA_LKEY], (u32*)a[HA_LCNT], (u32*)a[HA_LR0], (u32*)a[HA_LNRES], (u32*)a[HA_LEVS],
+                              (u32*)a[HA_LNK]);
+      break;
+    default:
+      gb_set_error("gb_h_loop_part: part %d outside [0, 4]", part);
+      return -2;
+  }
+  GB_LAUNCH_CK();
+  return 0;
+}
+extern "C" int gb_h_loop_part(const int64_t* args_host, int n_args, int part, int parity, void* stream) {
+  if (n_args != HA_N) { gb_set_error("gb_h_loop_part: expected %d arguments, got %d", (int)HA_N, n_args); return -2; }
+  return args_host[HA_STREAMING] ? h_loop_part_impl<true>(args_host, part, parity, (cudaStream_t)stream)
+                                 : h_loop_part_impl<false>(args_host, part, parity, (cudaStream_t)stream);
+}
+extern "C" int64_t gb_h_loop_xbuf_elems(void) { return 1 + 2 * HLX_CAP; }
+extern "C" int64_t gb_h_loop_sbuf_bytes(int stride) { return 4 * HL_TB_CAP + (int64_t)HL_TB_CAP * stride; }
+
 extern "C" int gb_h_loop_time_k1(int enable) { g_time_k1 = enable != 0; g_ev_used = 0; return 0; }
 // elapsed ms of every timed k_slot_count launch since gb_h_loop_time_k1(1) (call after a synchronize); returns the count
 extern "C" int gb_h_loop_k1_times(float* ms_host, int cap) {

@@ -27,6 +27,14 @@ class Comm:
                             group=self.group)
         return t
 
+    def all_gather_into(self, out, t):
+        """out [world * t.numel()] <- every rank's t (enqueued on the device, no host synchronisation)"""
+        if self.world > 1:
+            dist.all_gather_into_tensor(out, t, group=self.group)
+        else:
+            out.copy_(t)
+        return out
+
     def all_gather_padded(self, arr, cap, dtype, device):
         """arr: 1-D numpy array (<= cap entries) -> list of per-rank numpy arrays"""
         n = len(arr)

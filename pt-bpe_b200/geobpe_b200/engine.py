@@ -420,7 +420,7 @@ class Learner:
         self.n_steps = 0
         self.hl = None              # device-driven loop state (histogram mode, single GPU)
         self._pending = 0           # iterations enqueued on the device and not yet read back
-        self.async_steps = async_steps and mode == "H" and self.comm is None and use_sketch
+        self.async_steps = async_steps and mode == "H" and use_sketch
         self._quantize()
         self._ts = TokenState(self.bb.R, mode)
         R = self.bb.R
@@ -455,9 +455,9 @@ class Learner:
             return
         self._raw = []
         for cnt, r0, nres in raw:
-            dicts = self._h_key_dicts(r0.tolist(), nres.tolist())
+            dicts = self._h_key_dicts(r0.tolist(), nres.tolist()) if nres is not None else None
             for s in range(len(cnt)):
-                key_str = json.dumps(dicts[s], sort_keys=True)
+                key_str = json.dumps(dicts[s], sort_keys=True) if dicts is not None else r0[s]
                 self._tokens[len(self._tokens)] = json.loads(key_str)
                 self._pop_log.append((int(cnt[s]), key_str))
 
@@ -664,10 +664,10 @@ class Learner:
 
     def step_h(self):
         """one merge iteration, histogram mode (bpe.py:1792-2166 with rmsd_key None)"""
-        if self.comm is not None:
-            return self._step_h_dist()
         if self.async_steps:
             return self.enqueue(1)
+        if self.comm is not None:
+            return self._step_h_dist()
         return self._step_h_host()
 
     def _step_h_host(self):
@@ -708,26 +708,45 @@ class Learner:
     HL_TB_CAP = 128
     HS = dict(T=0, STEP=1, HALT=2, EVN=3, MPREV=4, THR=5, C1=6, NCAND=7, NZ=8, M1=10, NT=11, ND=12, ROUND2=13,
               WIN_R0=14, WIN_NRES=15, WIN_CNT=16, WIN_J=17, MISMATCH=18, FLAGGED=19, NEWT=20, NTOK=21, OVF=22,
-              R2COUNT=23, MAXSTEPS=24, EVCAP=25, HALT_STEP=26, NTMAX=27, N=28, NCL=29, CLCAP=30)
+              R2COUNT=23, MAXSTEPS=24, EVCAP=25, HALT_STEP=26, NTMAX=27, N=28, NCL=29, CLCAP=30, CMPT=31, DIST=32)
     HALT_NAMES = {1: "ties", 2: "candidates", 3: "collision", 4: "table", 5: "event log", 6: "empty", 7: "step log",
                   8: "count"}
 
     def _hl_init(self):
         ts = self._ts
-        if self.sketch is None:
-            self.sketch = SlotSketch(ts.T)
-        sk = self.sketch
+        comm = self.comm
         maxwin = int(self.bb.lens_host.max()) if self.bb.S else 2
+        Tb = ts.T
+        if comm is not None:      # buffer sizes that take part in collectives must agree on every rank
+            mx = comm.all_reduce(torch.tensor([maxwin, Tb], device=_dev(), dtype=torch.int64), "max").cpu().numpy()
+            maxwin, Tb = int(mx[0]), int(mx[1])
+        if self.sketch is None:
+            self.sketch = SlotSketch(Tb)
+        sk = self.sketch
         hl = types.SimpleNamespace()
-        hl.hs = _zeros(32, torch.int32)
+        hl.hs = _zeros(64, torch.int32)
         hl.hs64 = _zeros(2, torch.int64)
         hl.tie_keys = _empty(256, torch.int64)
         hl.tie_min = _empty(256, torch.int32)
         hl.stride = ((39 * maxwin + 200) + 127) // 128 * 128
         hl.strbuf = _zeros(self.HL_TB_CAP * hl.stride, torch.uint8)
-        cap = self.HL_LOG_CAP
+        cap = self.HL_LOG_CAP if comm is None else min(self.HL_LOG_CAP, 2048)
+        hl.log_cap = cap
         hl.log_key = _empty(cap, torch.int64)
         hl.log = {k: _empty(cap, torch.int32) for k in ("cnt", "r0", "nres", "evstart", "nk")}
+        hl.dist = None
+        if comm is not None:
+            lib = _lib.load()
+            xe = int(lib.gb_h_loop_xbuf_elems())
+            d = types.SimpleNamespace()
+            d.x = _zeros(xe, torch.int64)
+            d.xall = _zeros(xe * comm.world, torch.int64)
+            d.tie_skeys = _zeros(self.HL_TB_CAP, torch.int64)
+            d.tie_smin = _zeros(self.HL_TB_CAP, torch.int32)
+            d.sbuf = _zeros(int(lib.gb_h_loop_sbuf_bytes(hl.stride)), torch.uint8)
+            d.log_str = _zeros(cap * hl.stride, torch.uint8)
+            d.log_strlen = _zeros(cap, torch.int32)
+            hl.dist = d
         hl.nargs = _lib.load().gb_h_loop_nargs()
         hl.enq = 0                    # iterations enqueued since the state block was last written
         hl.parity = 0                 # which token buffer is current on the device (0 = ts.a)
@@ -757,20 +776,24 @@ class Learner:
                 P(hl.strbuf), hl.stride, P(self.ev_left), P(self.ev_right), P(self.ev_p), P(hl.log_key),
                 P(hl.log["cnt"]), P(hl.log["r0"]), P(hl.log["nres"]), P(hl.log["evstart"]), P(hl.log["nk"]),
                 P(hl.cl_key), P(hl.cl_j), P(hl.cl_r), hl.Tmax, 1 if 16 * hl.Tmax > SlotSketch.STREAM_BYTES else 0, hl.period]
+        d = hl.dist
+        vals += ([P(d.x), P(d.xall), self.comm.world, self.comm.rank, P(d.tie_skeys), P(d.tie_smin), P(d.sbuf), P(d.log_str),
+                  P(d.log_strlen)] if d is not None else [0] * 9)
         assert len(vals) == hl.nargs, (len(vals), hl.nargs)
         return (C.c_int64 * len(vals))(*[v if v < (1 << 63) else v - (1 << 64) for v in vals])
 
     def _hl_push_state(self):
         """host state -> device state block (after construction, after a host-side iteration)"""
         hl, H = self.hl, self.HS
-        h = np.zeros(32, dtype=np.int64)
+        h = np.zeros(64, dtype=np.int64)
+        h[H["DIST"]] = 1 if hl.dist is not None else 0
         h[H["T"]] = self._ts.T
         h[H["N"]] = self._ts.T
         h[H["CLCAP"]] = self._ts.cap
         h[H["EVN"]] = self._ev_n
         h[H["MPREV"]] = self._last_count
         h[H["NTOK"]] = self._ntok
-        h[H["MAXSTEPS"]] = self.HL_LOG_CAP
+        h[H["MAXSTEPS"]] = hl.log_cap
         h[H["EVCAP"]] = self.ev_left.numel()
         hl.hs.copy_(torch.from_numpy(h.astype(np.int32)))
         hl.enq = 0
@@ -785,11 +808,41 @@ class Learner:
             self._hl_init()
             self._hl_push_state()
         hl = self.hl
+        if hl.dist is not None:
+            return self._hl_enqueue_dist(nsteps)
         hl.lazy += nsteps                   # launched in whole compaction periods (CUDA-graph replays), the rest at sync()
         self._pending += nsteps
         self.n_steps += nsteps
         if hl.lazy >= 4 * hl.period:
             self._hl_flush(hl.lazy // hl.period * hl.period)
+
+    def _hl_enqueue_dist(self, nsteps):
+        """sharded run: five kernel groups per iteration with a collective after each of the first four (see
+        csrc/k_hloop_dist.cuh); everything is enqueued, nothing is read back"""
+        hl, d, comm, sk = self.hl, self.hl.dist, self.comm, self.sketch
+        for _ in range(nsteps):
+            part = lambda k, n: _lib.call_n("gb_h_loop_part", n, hl.args, hl.nargs, k, hl.parity)
+            ev = self.k1_events
+            if ev is not None:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+            part(0, 1)
+            if ev is not None:
+                e1.record()
+                ev.append((e0, e1, None))          # (the live-token count of that iteration is filled in by bench.py)
+            comm.all_reduce(sk.slots, "sum")
+            part(1, 3)
+            comm.all_gather_into(d.xall, d.x)
+            part(2, 5)
+            comm.all_gather_into(d.xall, d.x)
+            part(3, 3)
+            comm.all_reduce(d.sbuf, "max")
+            part(4, 5)
+            hl.enq += 1
+            if hl.enq % hl.period == 0:
+                self._hl_call(0, 1)
+        self._pending += nsteps
+        self.n_steps += nsteps
 
     def _hl_flush(self, n):
         hl = self.hl
@@ -820,7 +873,12 @@ class Learner:
             if done:
                 keys = hl.log_key[:done].cpu().numpy().astype(np.uint64).tolist()
                 lg = {k: _u32(v[:done]) for k, v in hl.log.items()}
-                self._raw.append((lg["cnt"], lg["r0"], lg["nres"]))          # formatted lazily (_materialise_log)
+                if hl.dist is not None:          # sharded run: the winner's json string itself is logged (the example
+                    sl = _u32(hl.dist.log_strlen[:done])                      # window may live on another rank)
+                    raw = hl.dist.log_str[:done * hl.stride].cpu().numpy().reshape(done, hl.stride)
+                    self._raw.append((lg["cnt"], [raw[s, :sl[s]].tobytes().decode() for s in range(done)], None))
+                else:
+                    self._raw.append((lg["cnt"], lg["r0"], lg["nres"]))      # formatted lazily (_materialise_log)
                 for s in range(done):
                     self._step_events.append((self._ntok + s, int(lg["evstart"][s]), int(lg["nk"][s]), keys[s]))
                 self._ntok += done
@@ -853,7 +911,10 @@ class Learner:
             if halt:
                 hl.halts[halt] = hl.halts.get(halt, 0) + 1
                 if halt != 7:                      # ties / candidates / table: this one iteration on the host path
-                    self._step_h_host()
+                    if hl.dist is not None:
+                        self._step_h_dist()        # (every rank halts at the same iteration)
+                    else:
+                        self._step_h_host()
                     rest -= 1
             self._hl_push_state()
             if rest > 0:
@@ -923,6 +984,7 @@ class Learner:
         n = len(self.tokens)
         self.tokens[n] = json.loads(key_str)
         self.pop_log.append((mx, key_str))
+        self._ntok, self._last_count = n + 1, mx
         _lib.call("gb_flag_pairs_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), HASH_BASE,
                   key, _lib.ptr(ts.flags))
         if self.verify and key in local:

@@ -12,10 +12,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 pytestmark = pytest.mark.gpu
 HP = dict(bins={1: 5}, bin_strategy="histogram", std_bonds=True)
 GEN = (40, 48, 31)
-STEPS = 40
+STEPS = 80          # crosses one compaction period of the device-driven loop
 
 
-def worker(rank, world, port, q):
+def worker(rank, world, port, q, async_steps):
     for p in (os.path.join(ROOT, "pt-bpe_b200"),):
         sys.path.insert(0, p)
     import torch.distributed as dist
@@ -28,7 +28,7 @@ def worker(rank, world, port, q):
     a, b = shard_ranges(np.diff(offs), world)[rank]
     v = vals[:, offs[a]:offs[b]]
     o = offs[a:b + 1] - offs[a]
-    L = E.Learner(v, o, mode="H", comm=Comm(), **HP)
+    L = E.Learner(v, o, mode="H", comm=Comm(), async_steps=async_steps, **HP)
     for _ in range(STEPS):
         L.step()
     ts = L.ts
@@ -43,14 +43,15 @@ def worker(rank, world, port, q):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-def test_two_gpu_h_mode_matches_oracle():
+@pytest.mark.parametrize("async_steps", [True, False], ids=["device-loop", "host-driven"])
+def test_two_gpu_h_mode_matches_oracle(async_steps):
     import torch.multiprocessing as mp
     import geobpe_oracle as O
     from geobpe_b200 import synthetic
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = 29500 + os.getpid() % 1000
-    ps = [ctx.Process(target=worker, args=(r, 2, port, q)) for r in range(2)]
+    ps = [ctx.Process(target=worker, args=(r, 2, port + (7 if async_steps else 0), q, async_steps)) for r in range(2)]
     [p.start() for p in ps]
     res = sorted(q.get(timeout=300) for _ in ps)
     [p.join(60) for p in ps]
