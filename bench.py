@@ -265,7 +265,9 @@ def main():
     L = mk()
     for _ in range(args.warmup):
         L.step()
-    L.k1_events = []
+    L.sync()
+    L.prepare()                                      # warm-up also captures the loop's CUDA graphs
+    L.k1_events = None if L.async_steps else []      # device loop: K1 is timed in an instrumented continuation (below)
     T_start = L.ts.T
     lib = _lib.load()
     barrier()
@@ -287,14 +289,25 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     launches = _lib.launches - launches0
-    k1_ms = [a.elapsed_time(b) for a, b, _ in L.k1_events]
-    k1_T = [t for _, _, t in L.k1_events]
+    k1_ms = [a.elapsed_time(b) for a, b, _ in (L.k1_events or [])]
+    k1_T = [t for _, _, t in (L.k1_events or [])]
     k1_note = "CUDA events around every K1 launch of the timed region"
-    if L.async_steps and world > 1:       # sharded loop: events sit around every part-0 call of the timed region (memset + K1)
-        nk = [e[2] for e in L.step_events[-args.steps:]]
-        Ts = (T_start - np.concatenate([[0], np.cumsum(nk)[:-1]])).tolist()
-        k1_T = [Ts[i] if t is None and i < len(Ts) else (t or T_end) for i, t in enumerate(k1_T)]
-        k1_note = "CUDA events around every slots-memset + K1 launch of the timed region (sharded device loop)"
+    if L.async_steps and world > 1:
+        # sharded loop: the timed region replays CUDA graphs (kernels + NCCL); K1 is timed in the iterations that follow,
+        # launched part by part with CUDA events around every part-0 call (slots memset + k_slot_count)
+        n_inst = min(128, args.steps)
+        T_inst = L.ts.T
+        L.k1_events = []
+        for _ in range(n_inst):
+            L.step()
+        L.sync()
+        torch.cuda.synchronize()
+        k1_ms = [a.elapsed_time(b) for a, b, _ in L.k1_events]
+        nk = [e[2] for e in L.step_events[-n_inst:]]
+        k1_T = (T_inst - np.concatenate([[0], np.cumsum(nk)[:-1]])).tolist()[:len(k1_ms)]
+        L.k1_events = None
+        k1_note = (f"timed region = CUDA-graph replays; K1 (slots memset + k_slot_count) timed with CUDA events in the {n_inst} "
+                   f"iterations that follow it, launched part by part")
     elif L.async_steps:
         # the timed region replays CUDA graphs (no events inside); K1 is timed in an instrumented continuation of the
         # same run: the next iterations launched kernel by kernel with CUDA events around every k_slot_count launch
@@ -332,7 +345,6 @@ def main():
                      "max_ties": getattr(L.hl, "ntmax", 0), "kernels_per_iteration": lib.gb_h_loop_kernels_per_step()}
     pairs = T_end - L.bb.S
     k1_share = k1_avg_ms * args.steps / ms
-    L.k1_events = None
     scale = None
     if not args.no_scale_probe and rank == 0:
         pr = k1_scale_probe(L, args.mode)

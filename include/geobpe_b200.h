@@ -213,14 +213,16 @@ int gb_pack_result(const uint32_t* out4, const int32_t* overflow, const uint64_t
 int gb_h_loop(const int64_t* args_host, int n_args, int nsteps, int parity, int step0, int compact_after,
               int* parity_out_host, void* stream);
 int gb_h_loop_nargs(void);
-/* sharded (multi-GPU) run: one iteration = parts 0..4 with a collective issued by the caller after parts 0-3
- * (allreduce-sum of the slot counters, allgather of the xbuf (key, count) lists twice, allreduce-max of the tie-string
+/* sharded (multi-GPU) run: one iteration = parts 0..3 with a collective issued by the caller after parts 0-2
+ * (allreduce-sum of the slot counters, allgather of the xbuf (key, count) lists, allreduce-max of the tie-string
  * buffer); see csrc/k_hloop_dist.cuh.  Compaction / state read-back go through gb_h_loop(nsteps = 0, compact_after = 1). */
 int gb_h_loop_part(const int64_t* args_host, int n_args, int part, int parity, void* stream);
 int64_t gb_h_loop_xbuf_elems(void);
 int64_t gb_h_loop_sbuf_bytes(int stride);
 /* whole compaction periods are replayed from captured CUDA graphs (default on) */
 int gb_h_loop_use_graphs(int enable);
+/* capture the graphs of both buffer parities now (warm-up) instead of at the first whole period */
+int gb_h_loop_prepare(const int64_t* args_host, int n_args, void* stream);
 int gb_h_loop_kernels_per_step(void);
 /* CUDA-event timing of the pair-count kernel inside the loop: enable, run, synchronize, then read the per-launch ms */
 int gb_h_loop_time_k1(int enable);

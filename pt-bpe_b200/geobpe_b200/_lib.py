@@ -55,6 +55,7 @@ SIGNATURES = {
     "gb_h_loop_xbuf_elems": [],
     "gb_h_loop_sbuf_bytes": [I32],
     "gb_h_loop_use_graphs": [I32],
+    "gb_h_loop_prepare": [P, I32, P],
     "gb_h_loop_kernels_per_step": [],
     "gb_h_loop_time_k1": [I32],
     "gb_h_loop_k1_times": [P, I32],

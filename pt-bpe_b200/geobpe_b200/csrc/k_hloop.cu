@@ -123,6 +123,8 @@ __global__ void __launch_bounds__(1024) hl_decide(u64* __restrict__ tk, u32* __r
       if (cand_over || mx < hs[HS_THR]) hl_halt(hs, HALT_CAND);
     }
   }
+  // sharded run: a second round would need another exchange per iteration for a ~1-in-1000 event: hand it to the host
+  if (threadIdx.x == 0 && round == 1 && hs[HS_DIST] && hs[HS_ROUND2] && !hs[HS_HALT]) hl_halt(hs, HALT_CAND);
   // the table is consumed (ties are copied out): leave it cleared for the next candidate pass
   for (i64 i = threadIdx.x; i < M; i += blockDim.x) { tk[i] = GB_EMPTY_KEY; tc[i] = 0u; tm[i] = 0xFFFFFFFFu; }
 }
@@ -662,12 +664,12 @@ extern "C" int gb_h_loop(const int64_t* args_host, int n_args, int nsteps, int p
             : h_loop_impl<false>(args_host, nsteps, p, step0, compact_after, parity_out_host, st);
 }
 
-// ---- sharded run: one iteration in five parts; the host issues a collective between consecutive parts -------------
-//   part 0: memset(slots), k_slot_count                         -> allreduce(sum) slots
-//   part 1: scan, pass 2 (round 1), export                      -> allgather x
-//   part 2: import, decide; round 2: collect, pass 2, export    -> allgather x
-//   part 3: import (round 2), decide (round 2), tie strings     -> allreduce(max) sbuf
-//   part 4: tie pick, flag, apply, unflag, end
+// ---- sharded run: one iteration in four parts; the host issues a collective between consecutive parts -------------
+//   part 0: memset(slots), k_slot_count            -> allreduce(sum) slots
+//   part 1: scan, pass 2, export                   -> allgather x
+//   part 2: import, decide, tie strings            -> allreduce(max) sbuf
+//   part 3: tie pick, flag, apply, unflag, end
+// (an iteration that would need a second candidate round halts and runs on the host path: ~1 in 1000)
 template <bool CS>
 static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t st) {
   u32* hs = (u32*)a[HA_HS];
@@ -732,17 +734,10 @@ static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t
     case 2:
       hl_table_import<<<1, 1024, 0, st>>>(tk, tc, tm, (u64)(M - 1), hs, 1, xall, world, rank);
       hl_decide<<<1, 1024, 0, st>>>(tk, tc, tm, M, hs, 1, tie_keys, tie_min, (u32)cap);
-      hl_slots_collect<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs, 2, cand, (u32)cap);
-      hl_cand_count<CS><<<pass_blocks, KS_THREADS, 0, st>>>(kf, shift, cand, (u32)cap, tk, tc, tm, (u64)(M - 1), hs, 2, cl_key, cl_j);
-      hl_table_export<<<1, 1024, 0, st>>>(tk, tc, M, hs, 2, x);
-      break;
-    case 3:
-      hl_table_import<<<1, 1024, 0, st>>>(tk, tc, tm, (u64)(M - 1), hs, 2, xall, world, rank);
-      hl_decide<<<1, 1024, 0, st>>>(tk, tc, tm, M, hs, 2, tie_keys, tie_min, (u32)cap);
       GB_CK(cudaMemsetAsync(sbuf, 0, 4 * HL_TB_CAP + (size_t)HL_TB_CAP * stride, st));
       hl_tie_strings<<<1, HL_TB_CAP, 0, st>>>(hs, tie_keys, tie_min, tie_skeys, tie_smin, pos, len, rbins, R, sbuf, stride);
       break;
-    case 4:
+    case 3:
       hl_tie_pick<<<1, HL_TB_CAP, 0, st>>>(hs, hs64, tie_skeys, tie_smin, pos, len, sbuf, stride, (char*)a[HA_LOGSTR], (u32*)a[HA_LOGSTRLEN]);
       hl_flag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark, pos, len, rbins, R);
       hl_apply_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, flags, rmark, hsh, glue, len, tid, pos,
@@ -752,7 +747,7 @@ static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t
                               (u32*)a[HA_LNK]);
       break;
     default:
-      gb_set_error("gb_h_loop_part: part %d outside [0, 4]", part);
+      gb_set_error("gb_h_loop_part: part %d outside [0, 3]", part);
       return -2;
   }
   GB_LAUNCH_CK();
@@ -766,6 +761,14 @@ extern "C" int gb_h_loop_part(const int64_t* args_host, int n_args, int part, in
 extern "C" int64_t gb_h_loop_xbuf_elems(void) { return 1 + 2 * HLX_CAP; }
 extern "C" int64_t gb_h_loop_sbuf_bytes(int stride) { return 4 * HL_TB_CAP + (int64_t)HL_TB_CAP * stride; }
 
+// capture the CUDA graphs of both buffer parities now (warm-up), instead of at the first whole period
+extern "C" int gb_h_loop_prepare(const int64_t* args_host, int n_args, void* stream) {
+  if (n_args != HA_N) { gb_set_error("gb_h_loop_prepare: expected %d arguments, got %d", (int)HA_N, n_args); return -2; }
+  if (!g_use_graphs) return 0;
+  const int period = args_host[HA_PERIOD] > 0 ? (int)args_host[HA_PERIOD] : 64;
+  return args_host[HA_STREAMING] ? h_loop_graphs<true>(args_host, period, (cudaStream_t)stream)
+                                 : h_loop_graphs<false>(args_host, period, (cudaStream_t)stream);
+}
 extern "C" int gb_h_loop_time_k1(int enable) { g_time_k1 = enable != 0; g_ev_used = 0; return 0; }
 // elapsed ms of every timed k_slot_count launch since gb_h_loop_time_k1(1) (call after a synchronize); returns the count
 extern "C" int gb_h_loop_k1_times(float* ms_host, int cap) {

@@ -276,7 +276,7 @@ class SlotSketch:
 
     def __init__(self, n_pairs_bound, log2ns=None, variant=2, ctas_per_sm=2):
         if log2ns is None:
-            log2ns = max(16, min(24, (max(n_pairs_bound, 2) - 1).bit_length()))   # NS >= pairs >= distinct; <= 64 MB (L2)
+            log2ns = max(16, min(24, (max(n_pairs_bound, 2) - 1).bit_length() - 1))   # NS >= pairs / 2; <= 64 MB (L2)
         self.log2ns = log2ns
         # the per-CTA shared-memory stage only pays when a CTA sees many more pairs than it has cache entries
         self.variant = variant if n_pairs_bound >= 296 * 32768 else (variant & ~6)
@@ -421,6 +421,7 @@ class Learner:
         self.hl = None              # device-driven loop state (histogram mode, single GPU)
         self._pending = 0           # iterations enqueued on the device and not yet read back
         self.async_steps = async_steps and mode == "H" and use_sketch
+        self.use_graphs = True
         self._quantize()
         self._ts = TokenState(self.bb.R, mode)
         R = self.bb.R
@@ -729,6 +730,8 @@ class Learner:
         hl.tie_keys = _empty(256, torch.int64)
         hl.tie_min = _empty(256, torch.int32)
         hl.stride = ((39 * maxwin + 200) + 127) // 128 * 128
+        if comm is not None:
+            hl.stride = min(hl.stride, 4096)      # the tie strings travel (allreduce-max): longer windows halt to the host path
         hl.strbuf = _zeros(self.HL_TB_CAP * hl.stride, torch.uint8)
         cap = self.HL_LOG_CAP if comm is None else min(self.HL_LOG_CAP, 2048)
         hl.log_cap = cap
@@ -746,6 +749,7 @@ class Learner:
             d.sbuf = _zeros(int(lib.gb_h_loop_sbuf_bytes(hl.stride)), torch.uint8)
             d.log_str = _zeros(cap * hl.stride, torch.uint8)
             d.log_strlen = _zeros(cap, torch.int32)
+            d.graphs = {}
             hl.dist = d
         hl.nargs = _lib.load().gb_h_loop_nargs()
         hl.enq = 0                    # iterations enqueued since the state block was last written
@@ -801,6 +805,9 @@ class Learner:
         _lib.call("gb_table_clear", *self.sketch.small.ptrs())     # hl_decide leaves it cleared from then on
         self._ts.flags.zero_()      # (hl.Tmax stays the initial upper bound: same arguments -> the captured graphs are reused)
         hl.args = self._hl_args()
+        if hl.dist is not None and getattr(hl, "_args_key", None) != tuple(hl.args):
+            hl.dist.graphs = {}
+        hl._args_key = tuple(hl.args)
 
     def enqueue(self, nsteps):
         """enqueue `nsteps` merge iterations on the device; nothing is read back until sync()"""
@@ -817,38 +824,81 @@ class Learner:
             self._hl_flush(hl.lazy // hl.period * hl.period)
 
     def _hl_enqueue_dist(self, nsteps):
-        """sharded run: five kernel groups per iteration with a collective after each of the first four (see
-        csrc/k_hloop_dist.cuh); everything is enqueued, nothing is read back"""
+        self._pending += nsteps
+        self.n_steps += nsteps
+        self._hl_run_dist(nsteps)
+
+    def _hl_iter_dist(self):
+        """sharded run, one iteration: five kernel groups with a collective after each of the first four (see
+        csrc/k_hloop_dist.cuh); everything is enqueued on the current stream, nothing is read back"""
         hl, d, comm, sk = self.hl, self.hl.dist, self.comm, self.sketch
-        for _ in range(nsteps):
-            part = lambda k, n: _lib.call_n("gb_h_loop_part", n, hl.args, hl.nargs, k, hl.parity)
-            ev = self.k1_events
-            if ev is not None:
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-            part(0, 1)
-            if ev is not None:
-                e1.record()
-                ev.append((e0, e1, None))          # (the live-token count of that iteration is filled in by bench.py)
-            comm.all_reduce(sk.slots, "sum")
-            part(1, 3)
-            comm.all_gather_into(d.xall, d.x)
-            part(2, 5)
-            comm.all_gather_into(d.xall, d.x)
-            part(3, 3)
-            comm.all_reduce(d.sbuf, "max")
-            part(4, 5)
+        part = lambda k, n: _lib.call_n("gb_h_loop_part", n, hl.args, hl.nargs, k, hl.parity)
+        ev = self.k1_events
+        if ev is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        part(0, 1)
+        if ev is not None:
+            e1.record()
+            ev.append((e0, e1, None))          # (the live-token count of that iteration is filled in by bench.py)
+        comm.all_reduce(sk.slots, "sum")
+        part(1, 3)
+        comm.all_gather_into(d.xall, d.x)
+        part(2, 3)
+        comm.all_reduce(d.sbuf, "max")
+        part(3, 5)
+
+    def prepare(self):
+        """warm-up: capture the CUDA graphs of the device-driven loop (both buffer parities) before they are needed"""
+        if not self.async_steps:
+            return
+        self.sync()
+        if self.hl is None:
+            self._hl_init()
+            self._hl_push_state()
+        hl = self.hl
+        if hl.dist is None:
+            _lib.call_n("gb_h_loop_prepare", 0, hl.args, hl.nargs)
+            return
+        p0 = hl.parity
+        for p in (0, 1):
+            if p not in hl.dist.graphs:
+                hl.parity = p
+                self._hl_capture_dist()
+        hl.parity = p0
+
+    def _hl_capture_dist(self):
+        """one iteration (kernels + the three NCCL collectives) as a CUDA graph for the current buffer parity"""
+        hl = self.hl
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._hl_iter_dist()                 # capturing does not execute
+        hl.dist.graphs[hl.parity] = g
+        return g
+
+    def _hl_run_dist(self, n):
+        """n iterations, each one graph replay (unless bench.py is timing K1 with events); the arrays are compacted
+        every `period` iterations"""
+        hl, d = self.hl, self.hl.dist
+        for _ in range(n):
+            if self.use_graphs and self.k1_events is None:
+                g = d.graphs.get(hl.parity) or self._hl_capture_dist()
+                g.replay()
+            else:
+                self._hl_iter_dist()
             hl.enq += 1
             if hl.enq % hl.period == 0:
                 self._hl_call(0, 1)
-        self._pending += nsteps
-        self.n_steps += nsteps
 
     def _hl_flush(self, n):
         hl = self.hl
         if n > 0:
-            self._hl_call(n, 0)
-            hl.enq += n
+            if hl.dist is not None:
+                self._hl_run_dist(n)
+            else:
+                self._hl_call(n, 0)
+                hl.enq += n
             hl.lazy -= n
 
     def _hl_call(self, nsteps, compact_after):
