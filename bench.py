@@ -335,6 +335,10 @@ def main():
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s"
     achieved = k1_bytes / (k1_avg_ms * 1e-3) / 1e9
+    tr = {}
+    tp = os.path.join(ROOT, "profiles", "r1_k1_traffic.json")
+    if os.path.exists(tp) and args.mode == "H":      # dram__bytes_read + write per launch from the committed ncu --set full capture
+        tr = json.load(open(tp))
     sk = getattr(L, "sketch", None)
     distinct = (int(L.hl.hs.cpu()[8]) if L.hl is not None else int(sk.sout.cpu()[2])) if sk is not None else L.table.distinct   # sketch: non-zero slots (lower bound)
     k1_name = ("k_slot_count" if sk is not None else "k_pair_count") + ("<KeysH>" if args.mode == "H" else "<KeysM>")
@@ -350,6 +354,7 @@ def main():
         pr = k1_scale_probe(L, args.mode)
         a2 = pr["bytes_per_token"] * pr["tokens"] / (pr["ms"] * 1e-3) / 1e9
         scale = dict(pr, bound="hbm", achieved=a2, peak=peak, unit="GB/s", frac=a2 / peak,
+                     traffic=(tr["at_scale"]["dram_bytes_per_token"] * pr["tokens"]) if tr else None,
                      pass2_achieved=pr["bytes_per_token"] * pr["tokens"] / (pr["pass2_ms"] * 1e-3) / 1e9,
                      note="K1 pass 1 (k_slot_count) alone on this workload's token arrays tiled to the per-GPU shard of "
                           "BASELINE config 5 (48 M tokens > L2); pass2_* = k_cand_count (exact resolution) on the same arrays")
@@ -407,7 +412,8 @@ def main():
         "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
         "roofline": {"bound": "hbm", "kernel": k1_name, "resolve_rounds_1_2_fallback": sk_rounds, "device_loop": loop_info,
                      "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "avg_ms": k1_avg_ms, "algorithmic_bytes_per_launch": k1_bytes,
+                     "traffic": (tr["in_loop"]["dram_bytes_per_token"] * float(np.mean(k1_T))) if tr else None,
+                     "traffic_source": tr.get("source") if tr else None, "avg_ms": k1_avg_ms, "algorithmic_bytes_per_launch": k1_bytes,
                      "bytes_per_token": bpt, "share_of_step": k1_share, "timing": k1_note},
         "roofline_at_scale": scale, "induce": induce, "cpu_baseline": cpu,
     }
