@@ -98,7 +98,8 @@ def ptr(t):
 
 
 def stream():
-    return torch.cuda.current_stream().cuda_stream
+    """raw handle of torch's current stream (the C accessor: torch.cuda.current_stream() costs ~17 us per call)"""
+    return torch._C._cuda_getCurrentRawStream(torch.cuda.current_device())
 
 
 def call(name, *args):
