@@ -48,7 +48,36 @@ CASES = {
     "m6_sub_sorted": dict(gen=(24, 40, 2, True), steps=20, sorted_sets=True,
                           hp=dict(bins={1: 6}, bin_strategy="histogram", std_bonds=False, rmsd_partition_min_size=0,
                                   rmsd_super_res=True, num_partitions={2: 2, 3: 3, 5: 2, 6: 2, 8: 1}, max_num_strucs=8)),
+    # BASELINE configs[0] inputs: the 72 bundled smoke PDBs (15 640 residues), featurized by geobpe_b200/pdb.py; the arrays
+    # are frozen in tests/golden/pdb72_input.npz because /root/reference does not travel
+    "pdb72_h": dict(gen="pdb72", steps=int(os.environ.get("PDB72_H_STEPS", 500)),
+                    hp=dict(bins={1: 10}, bin_strategy="histogram", std_bonds=True, rmsd_partition_min_size=INF)),
+    "pdb72_m": dict(gen="pdb72", steps=int(os.environ.get("PDB72_M_STEPS", 500)), induce="pdb_heldout",
+                    hp=dict(bins={1: 20}, bin_strategy="histogram", std_bonds=False, rmsd_partition_min_size=0,
+                            rmsd_super_res=True, num_partitions=NUM_P, max_num_strucs=100)),
 }
+
+
+def pdb72_inputs():
+    """featurize the reference's bundled smoke PDBs and freeze the arrays as a fixture"""
+    import glob
+    from geobpe_b200 import pdb
+    files = sorted(glob.glob("/root/reference/data/vqvae_pretrain/train/*.pdb"))
+    vals, offs, names = pdb.featurize_files(files)
+    path = os.path.join(ROOT, "tests", "golden", "pdb72_input.npz")
+    np.savez_compressed(path, vals=vals, offsets=offs, names=np.array(names))
+    return vals, offs
+
+
+def pdb_heldout_inputs():
+    """the reference's bundled CASP14 + CAMEO smoke PDBs (held out from training), frozen like pdb72"""
+    import glob
+    from geobpe_b200 import pdb
+    files = sorted(glob.glob("/root/reference/data/vqvae_pretrain/CASP14/*.pdb")) + \
+        sorted(glob.glob("/root/reference/data/vqvae_pretrain/CAMEO/*.pdb"))
+    vals, offs, names = pdb.featurize_files(files)
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "pdb_heldout_input.npz"), vals=vals, offsets=offs, names=np.array(names))
+    return vals, offs
 
 
 class SortedIterSet(set):
@@ -67,15 +96,18 @@ def tree_repr(node):
 
 def run_case(name, ref):
     c = CASES[name]
-    S, n, seed, ragged = c["gen"]
-    vals, offs = synthetic.generate(S, n, seed=seed, ragged=ragged)
+    if c["gen"] == "pdb72":
+        vals, offs = pdb72_inputs()
+    else:
+        S, n, seed, ragged = c["gen"]
+        vals, offs = synthetic.generate(S, n, seed=seed, ragged=ragged)
     strucs = synthetic.to_structures(vals, offs)
     d = tempfile.mkdtemp(prefix="golden_")
     hp = dict(c["hp"])
     t0 = time.time()
     bpe = ref.BPE(strucs, save_dir=d, res_init=True, seed=0, **hp)
     bpe.initialize()
-    out = {"case": name, "gen": list(c["gen"]), "hp": _jsonable({k: (str(v) if v == INF else v) for k, v in hp.items()}),
+    out = {"case": name, "gen": c["gen"] if isinstance(c["gen"], str) else list(c["gen"]), "hp": _jsonable({k: (str(v) if v == INF else v) for k, v in hp.items()}),
            "input_sha256": hashlib.sha256(vals.tobytes() + offs.tobytes()).hexdigest(),
            "sorted_sets": bool(c.get("sorted_sets"))}
     out["post_init"] = dump_state(bpe)
@@ -98,8 +130,11 @@ def run_case(name, ref):
     out["final_trees"] = [[tree_repr(nd) for nd in bpe.tokenizers[i].bond_to_token.tree.nodes.values()] for i in range(2)]
     out["vocab_size"] = int(bpe.vocab_size)
     if "induce" in c:
-        S2, n2, seed2 = c["induce"]
-        v2, o2 = synthetic.generate(S2, n2, seed=seed2)
+        if c["induce"] == "pdb_heldout":
+            v2, o2 = pdb_heldout_inputs()
+        else:
+            S2, n2, seed2 = c["induce"]
+            v2, o2 = synthetic.generate(S2, n2, seed=seed2)
         s2 = synthetic.to_structures(v2, o2)
         ind = []
         # a training backbone first (train<->induce consistency, bpe.py:1141-1143), then held-out ones
@@ -113,7 +148,7 @@ def run_case(name, ref):
             except ValueError as e:
                 ind.append({"ok": False, "error": str(e)[:60]})
         out["induce"] = ind
-        out["induce_gen"] = list(c["induce"])
+        out["induce_gen"] = c["induce"] if isinstance(c["induce"], str) else list(c["induce"])
     out["ref_seconds"] = round(time.time() - t0, 2)
     path = os.path.join(ROOT, "tests", "golden", f"{name}.json")
     with open(path, "w") as f:

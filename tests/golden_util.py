@@ -17,9 +17,21 @@ def load_golden(name):
 
 
 def case_inputs(g):
+    if isinstance(g["gen"], str):            # frozen real-data arrays (tests/golden/<gen>_input.npz)
+        z = np.load(os.path.join(GOLDEN_DIR, f"{g['gen']}_input.npz"))
+        return z["vals"], z["offsets"]
     S, n, seed, ragged = g["gen"]
     vals, offs = synthetic.generate(S, n, seed=seed, ragged=bool(ragged))
     return vals, offs
+
+
+def induce_inputs(g):
+    """held-out backbones of a golden's induce section"""
+    if isinstance(g["induce_gen"], str):
+        z = np.load(os.path.join(GOLDEN_DIR, f"{g['induce_gen']}_input.npz"))
+        return z["vals"], z["offsets"]
+    S2, n2, seed2 = g["induce_gen"]
+    return synthetic.generate(S2, n2, seed=seed2)
 
 
 def case_hparams(g):

@@ -7,7 +7,7 @@ import pytest
 import geobpe_oracle as O
 from geobpe_b200 import synthetic
 from geobpe_b200.bpe import BPE
-from golden_util import load_golden, case_inputs, case_hparams, norm
+from golden_util import load_golden, case_inputs, case_hparams, induce_inputs, norm
 
 pytestmark = pytest.mark.gpu
 COORD_ATOL = 1e-9
@@ -40,12 +40,12 @@ def run_learn(g):
     return bpe, strucs
 
 
-@pytest.mark.parametrize("name", ["h4", "h6_ragged", "h5_uniform", "h5_cover"])
+@pytest.mark.parametrize("name", ["h4", "h6_ragged", "h5_uniform", "h5_cover", "pdb72_h"])
 def test_h_mode_vs_reference_golden(name):
     run_learn(load_golden(name))
 
 
-@pytest.mark.parametrize("name", ["m20", "m6_sub"])
+@pytest.mark.parametrize("name", ["m20", "m6_sub", "pdb72_m"])
 def test_m_mode_vs_reference_golden(name):
     run_learn(load_golden(name))
 
@@ -80,14 +80,13 @@ def test_m_mode_vs_oracle_fresh():
     assert norm(O.dump_state(bpe, max_angles=30)) == norm(O.dump_state(ora, max_angles=30))
 
 
-@pytest.mark.parametrize("name", ["m20", "m6_sub"])
+@pytest.mark.parametrize("name", ["m20", "m6_sub", "pdb72_m"])
 def test_induce_vs_reference_golden(name):
     """BPE.tokenize on training and held-out backbones: segmentation, L trace, ids and the set of backbones the
     reference rejects (glue angle outside the learned bins) must match the reference run."""
     g = load_golden(name)
     bpe, strucs = run_learn(g)
-    S2, n2, seed2 = g["induce_gen"]
-    v2, o2 = synthetic.generate(S2, n2, seed=seed2)
+    v2, o2 = induce_inputs(g)
     s2 = synthetic.to_structures(v2, o2)
     srcs = [strucs[0], strucs[1]] + s2
     from geobpe_b200.bpe import Tokenizer
@@ -127,8 +126,7 @@ def test_pickle_layout_and_induce_from_pickle(tmp_path):
     assert norm(list(b2._tokens.items())) == norm(list(bpe._tokens.items()))
     assert [list(t.bond_to_token.values()) for t in b2.tokenizers] == [list(t.bond_to_token.values()) for t in bpe.tokenizers]
     assert b2.quantize(b2.tokenizers[0]) == g["final_ids"][0]
-    S2, n2, seed2 = g["induce_gen"]
-    v2, o2 = synthetic.generate(S2, n2, seed=seed2)
+    v2, o2 = induce_inputs(g)
     toks, ok = b2.induce(synthetic.to_structures(v2, o2))
     for tk, good, want in zip(toks, ok, g["induce"][2:]):
         assert bool(good) == want["ok"]

@@ -8,10 +8,10 @@ import pytest
 
 import geobpe_oracle as O
 from geobpe_b200 import synthetic
-from golden_util import load_golden, case_inputs, case_hparams, norm
+from golden_util import load_golden, case_inputs, case_hparams, induce_inputs, norm
 
-H_CASES = ["h4", "h6_ragged", "h5_uniform", "h5_cover"]
-M_CASES = ["m20", "m6_sub", "m20_sorted", "m6_sub_sorted"]
+H_CASES = ["h4", "h6_ragged", "h5_uniform", "h5_cover", "pdb72_h"]   # pdb72_*: BASELINE configs[0] inputs (real PDBs)
+M_CASES = ["m20", "m6_sub", "m20_sorted", "m6_sub_sorted", "pdb72_m"]
 
 
 def run_oracle(g):
@@ -51,8 +51,7 @@ def test_oracle_m_mode(name):
     bpe, strucs = check_learn(g)
     if "induce" not in g:
         return
-    S2, n2, seed2 = g["induce_gen"]
-    v2, o2 = synthetic.generate(S2, n2, seed=seed2)
+    v2, o2 = induce_inputs(g)
     s2 = synthetic.to_structures(v2, o2)
     for src, want in zip([strucs[0], strucs[1]] + s2, g["induce"]):
         tk = O.Tokenizer.from_structure(src)
