@@ -347,6 +347,11 @@ def main():
     if L.hl is not None:
         loop_info = {"device_iterations": L.hl.steps, "second_rounds": L.hl.r2, "halts_by_code": {L.HALT_NAMES[k]: v for k, v in L.hl.halts.items()},
                      "max_ties": getattr(L.hl, "ntmax", 0), "kernels_per_iteration": lib.gb_h_loop_kernels_per_step()}
+        if L.hl.dist is not None:
+            loop_info["exchange"] = ("peer memory (loads over NVLink inside the loop's kernels, CUDA IPC blocks)" if L.hl.dist.peer is not None
+                                     else "NCCL (allreduce-sum slots, allgather candidates, allreduce-max tie strings)")
+            loop_info["slots_log2"] = L.sketch.log2ns
+            loop_info["kernels_per_iteration"] = 19 if L.hl.dist.peer is not None else 12
     pairs = T_end - L.bb.S
     k1_share = k1_avg_ms * args.steps / ms
     scale = None

@@ -219,6 +219,19 @@ int gb_h_loop_nargs(void);
 int gb_h_loop_part(const int64_t* args_host, int n_args, int part, int parity, void* stream);
 int64_t gb_h_loop_xbuf_elems(void);
 int64_t gb_h_loop_sbuf_bytes(int stride);
+/* peer-memory transport for the sharded run (replaces the three caller-issued collectives by loads over NVLink/NVSwitch
+ * inside the loop's own kernels; csrc/k_hloop_dist.cuh).  Every rank allocates one symmetric block with gb_peer_alloc
+ * ([slots u32 << log2ns | x u64 gb_h_loop_xbuf_elems() | sbuf gb_h_loop_sbuf_bytes() | flags u32 3 x gb_peer_max_world()],
+ * each part 256-byte aligned), sends the 64-byte CUDA IPC handle to the other ranks (any transport) and maps theirs with
+ * gb_peer_open.  args_host then carries a host table u64 [4][world] of all ranks' slots / x / sbuf / flags addresses
+ * (HA_PEERS) plus local buffers for the reduced slot counters, the reduced tie strings and u32 [4] stage counters;
+ * gb_h_loop_part then needs no collective between the parts.  A rank that sees no signal from a peer within 4 s halts
+ * with code 9 instead of spinning forever. */
+int gb_peer_alloc(int64_t bytes, void** ptr_out_host, unsigned char* handle64_out_host);
+int gb_peer_open(const unsigned char* handle64_host, void** ptr_out_host);
+int gb_peer_close(void* ptr);
+int gb_peer_free(void* ptr);
+int gb_peer_max_world(void);
 /* whole compaction periods are replayed from captured CUDA graphs (default on) */
 int gb_h_loop_use_graphs(int enable);
 /* capture the graphs of both buffer parities now (warm-up) instead of at the first whole period */

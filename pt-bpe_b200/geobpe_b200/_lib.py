@@ -54,6 +54,11 @@ SIGNATURES = {
     "gb_h_loop_part": [P, I32, I32, I32, P],
     "gb_h_loop_xbuf_elems": [],
     "gb_h_loop_sbuf_bytes": [I32],
+    "gb_peer_alloc": [I64, P, P],
+    "gb_peer_open": [P, P],
+    "gb_peer_close": [P],
+    "gb_peer_free": [P],
+    "gb_peer_max_world": [],
     "gb_h_loop_use_graphs": [I32],
     "gb_h_loop_prepare": [P, I32, P],
     "gb_h_loop_kernels_per_step": [],

@@ -13,7 +13,7 @@
 #define HL_BLK_LIST 512         // candidate pairs staged per CTA before one append to the global list
 
 enum { HALT_TIES = 1, HALT_CAND = 2, HALT_COLLISION = 3, HALT_TABLE = 4, HALT_EVLOG = 5, HALT_EMPTY = 6, HALT_STEPS = 7,
-       HALT_COUNT = 8 };
+       HALT_COUNT = 8, HALT_PEER = 9 };
 
 __device__ __forceinline__ void hl_halt(u32* hs, u32 code) {
   if (atomicCAS(&hs[HS_HALT], 0u, code) == 0u) hs[HS_HALT_STEP] = hs[HS_STEP];
@@ -504,7 +504,8 @@ enum { HA_HS = 0, HA_HS64, HA_HSH0, HA_HSH1, HA_GLUE0, HA_GLUE1, HA_POS0, HA_POS
        HA_FLAGS, HA_RMARK, HA_SCRATCH, HA_POWTAB, HA_P, HA_RBINS, HA_R, HA_SLOTS, HA_LOG2NS, HA_BMAX, HA_CAND, HA_CAP,
        HA_VARIANT, HA_CTAS, HA_TK, HA_TC, HA_TM, HA_M, HA_TIEK, HA_TIEM, HA_STRBUF, HA_STRIDE, HA_EVL, HA_EVR, HA_EVP,
        HA_LKEY, HA_LCNT, HA_LR0, HA_LNRES, HA_LEVS, HA_LNK, HA_CLKEY, HA_CLJ, HA_CLR, HA_NMAX, HA_STREAMING,
-       HA_PERIOD, HA_XBUF, HA_XALL, HA_WORLD, HA_RANK, HA_TIESK, HA_TIESM, HA_SBUF, HA_LOGSTR, HA_LOGSTRLEN, HA_N };
+       HA_PERIOD, HA_XBUF, HA_XALL, HA_WORLD, HA_RANK, HA_TIESK, HA_TIESM, HA_SBUF, HA_LOGSTR, HA_LOGSTRLEN,
+       HA_PEERS, HA_GSLOTS, HA_SRED, HA_PCTR, HA_N };
 
 // optional CUDA-event timing of the pair-count kernel inside the loop (bench.py's roofline leg)
 #include <vector>
@@ -702,6 +703,23 @@ static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t
   const u64* xall = (const u64*)a[HA_XALL];
   const int world = (int)a[HA_WORLD], rank = (int)a[HA_RANK];
   const i64 Nmax = a[HA_NMAX];
+  // peer-memory transport (k_hloop_dist.cuh): a[HA_PEERS] = host table u64 [4][world] of every rank's slots / x / sbuf /
+  // flags addresses (row entries of this rank = the local ones, which is also what HA_SLOTS / HA_XBUF / HA_SBUF hold)
+  const u64* ptab = (const u64*)a[HA_PEERS];
+  HlPeers PP;
+  u32* gslots = (u32*)a[HA_GSLOTS];
+  char* sred = (char*)a[HA_SRED];
+  u32* pctr = (u32*)a[HA_PCTR];
+  if (ptab) {
+    if (world > HLP_MAXW || !gslots || !sred || !pctr) { gb_set_error("gb_h_loop_part: bad peer arguments"); return -2; }
+    for (int r = 0; r < world; ++r) {
+      PP.slots[r] = ptab[r]; PP.x[r] = ptab[world + r]; PP.s[r] = ptab[2 * world + r]; PP.flags[r] = ptab[3 * world + r];
+    }
+    if ((u64)slots != PP.slots[rank] || (u64)x != PP.x[rank] || (u64)sbuf != PP.s[rank]) {
+      gb_set_error("gb_h_loop_part: local buffers are not the peer table's entries for this rank");
+      return -2;
+    }
+  }
   if (!x || !xall || !sbuf || world < 1 || log2ns < 12 || M <= 0 || (M & (M - 1)) || cap > KC_SET / 2 || cache > 1 || (stride & 127)) {
     gb_set_error("gb_h_loop_part: bad arguments");
     return -2;
@@ -724,21 +742,27 @@ static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t
       } else {
         k_slot_count<KeysHLT<CS>, false, 0, false><<<count_blocks, KS_THREADS, 0, st>>>(kf, Nmax, slots, shift, nullptr, hs);
       }
+      if (ptab) hl_peer_signal<<<1, 32, 0, st>>>(PP, world, rank, 0, pctr);
       break;
     }
     case 1:
-      hl_slots_scan<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs, cand, (u32)cap);
+      if (ptab) hl_peer_sum_slots<<<sms * 2, 256, 0, st>>>(PP, world, rank, pctr, hs, (uint4*)gslots, ((i64)1 << log2ns) / 4);
+      hl_slots_scan<<<scan_blocks, 256, 0, st>>>((const uint4*)(ptab ? gslots : slots), bmax, hs, cand, (u32)cap);
       hl_cand_count<CS><<<pass_blocks, KS_THREADS, 0, st>>>(kf, shift, cand, (u32)cap, tk, tc, tm, (u64)(M - 1), hs, 1, cl_key, cl_j);
       hl_table_export<<<1, 1024, 0, st>>>(tk, tc, M, hs, 1, x);
+      if (ptab) hl_peer_signal<<<1, 32, 0, st>>>(PP, world, rank, 1, pctr);
       break;
     case 2:
+      if (ptab) hl_peer_gather_x<<<world, 1024, 0, st>>>(PP, world, rank, pctr, hs, (u64*)xall);
       hl_table_import<<<1, 1024, 0, st>>>(tk, tc, tm, (u64)(M - 1), hs, 1, xall, world, rank);
       hl_decide<<<1, 1024, 0, st>>>(tk, tc, tm, M, hs, 1, tie_keys, tie_min, (u32)cap);
       GB_CK(cudaMemsetAsync(sbuf, 0, 4 * HL_TB_CAP + (size_t)HL_TB_CAP * stride, st));
       hl_tie_strings<<<1, HL_TB_CAP, 0, st>>>(hs, tie_keys, tie_min, tie_skeys, tie_smin, pos, len, rbins, R, sbuf, stride);
+      if (ptab) hl_peer_signal<<<1, 32, 0, st>>>(PP, world, rank, 2, pctr);
       break;
     case 3:
-      hl_tie_pick<<<1, HL_TB_CAP, 0, st>>>(hs, hs64, tie_skeys, tie_smin, pos, len, sbuf, stride, (char*)a[HA_LOGSTR], (u32*)a[HA_LOGSTRLEN]);
+      if (ptab) hl_peer_max_s<<<32, 256, 0, st>>>(PP, world, rank, pctr, hs, (uint4*)sred, stride);
+      hl_tie_pick<<<1, HL_TB_CAP, 0, st>>>(hs, hs64, tie_skeys, tie_smin, pos, len, ptab ? sred : sbuf, stride, (char*)a[HA_LOGSTR], (u32*)a[HA_LOGSTRLEN]);
       hl_flag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark, pos, len, rbins, R);
       hl_apply_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, flags, rmark, hsh, glue, len, tid, pos,
                                                  (u32*)a[HA_EVL], (u32*)a[HA_EVR], (u32*)a[HA_EVP]);
@@ -758,6 +782,30 @@ extern "C" int gb_h_loop_part(const int64_t* args_host, int n_args, int part, in
   return args_host[HA_STREAMING] ? h_loop_part_impl<true>(args_host, part, parity, (cudaStream_t)stream)
                                  : h_loop_part_impl<false>(args_host, part, parity, (cudaStream_t)stream);
 }
+// ---- symmetric blocks for the peer-memory transport ------------------------------------------------------------------
+// gb_peer_alloc: cudaMalloc + zero + CUDA IPC handle (64 bytes, to be sent to the other ranks by any means);
+// gb_peer_open: map another rank's block into this process (peer access is enabled lazily by the driver).
+extern "C" int gb_peer_alloc(int64_t bytes, void** ptr_out, unsigned char* handle_out) {
+  void* p = nullptr;
+  GB_CK(cudaMalloc(&p, (size_t)bytes));
+  GB_CK(cudaMemset(p, 0, (size_t)bytes));
+  cudaIpcMemHandle_t h;
+  GB_CK(cudaIpcGetMemHandle(&h, p));
+  static_assert(sizeof(h) == 64, "CUDA IPC handle size");
+  memcpy(handle_out, &h, sizeof(h));
+  *ptr_out = p;
+  return 0;
+}
+extern "C" int gb_peer_open(const unsigned char* handle, void** ptr_out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  GB_CK(cudaIpcOpenMemHandle(ptr_out, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+extern "C" int gb_peer_close(void* ptr) { GB_CK(cudaIpcCloseMemHandle(ptr)); return 0; }
+extern "C" int gb_peer_free(void* ptr) { GB_CK(cudaFree(ptr)); return 0; }
+extern "C" int gb_peer_max_world(void) { return HLP_MAXW; }
+
 extern "C" int64_t gb_h_loop_xbuf_elems(void) { return 1 + 2 * HLX_CAP; }
 extern "C" int64_t gb_h_loop_sbuf_bytes(int stride) { return 4 * HL_TB_CAP + (int64_t)HL_TB_CAP * stride; }
 

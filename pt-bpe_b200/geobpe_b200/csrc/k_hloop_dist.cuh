@@ -114,3 +114,114 @@ __global__ void __launch_bounds__(HL_TB_CAP) hl_tie_pick(u32* __restrict__ hs, u
     hs[HS_NTMAX] = max(hs[HS_NTMAX], nt);
   }
 }
+
+// ---- peer-memory transport (NVLink / NVSwitch loads instead of NCCL calls) -------------------------------------------
+// Every rank owns one cudaMalloc'd block [slots | x | sbuf | flags] that all other ranks have opened through CUDA IPC
+// (gb_peer_alloc / gb_peer_open).  An exchange is: producer kernels write the local block -> hl_peer_signal (release
+// store of the stage's sequence number into every peer's flag row) -> the consumer kernel spins (acquire loads on its OWN
+// flag row) until every rank has signalled, then PULLS what it needs straight from the peers' blocks and reduces it
+// while loading (slot sums, candidate lists, tie strings).  Three signals per iteration; because every rank waits on all
+// three, a block is never rewritten before every peer has finished reading the previous iteration's contents (the next
+// write of a region always sits behind a later wait).  Waits are bounded: a rank that sees no signal within
+// HLP_TIMEOUT_NS halts with HALT_PEER and stops waiting, so a dead peer cannot hang the GPU.
+#define HLP_MAXW 16
+#define HLP_TIMEOUT_NS 4000000000ull
+struct HlPeers { u64 slots[HLP_MAXW]; u64 x[HLP_MAXW]; u64 s[HLP_MAXW]; u64 flags[HLP_MAXW]; };
+
+__device__ __forceinline__ void hlp_st_release(u32* p, u32 v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ u32 hlp_ld_acquire(const u32* p) {
+  u32 v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 hlp_ld4(const uint4* p) {        // peer data: never from L1
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ u64 hlp_ld8(const u64* p) {
+  u64 v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ u64 hlp_now() {
+  u64 t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// flags u32 [3][HLP_MAXW] in the symmetric block: flags[stage][r] = last sequence number rank r completed for that stage;
+// ctr u32 [4] local: ctr[stage] = sequence number this rank has signalled
+__global__ void hl_peer_signal(HlPeers P, int world, int rank, int stage, u32* __restrict__ ctr) {
+  __shared__ u32 s_seq;
+  if (threadIdx.x == 0) s_seq = ++ctr[stage];
+  __syncthreads();
+  __threadfence_system();
+  if ((int)threadIdx.x < world) hlp_st_release(reinterpret_cast<u32*>(P.flags[threadIdx.x]) + stage * HLP_MAXW + rank, s_seq);
+}
+// block-wide: returns once every rank has signalled `stage` for the current sequence number (false: timed out / peer halt)
+__device__ __forceinline__ bool hl_peer_wait(const u32* __restrict__ myflags, const u32* __restrict__ ctr, int world, int stage,
+                                             u32* __restrict__ hs) {
+  __shared__ int s_ok;
+  if (threadIdx.x == 0) {
+    int ok = hs[HS_HALT] != HALT_PEER;
+    if (ok) {
+      const u32 target = ctr[stage];
+      const u64 t0 = hlp_now();
+      for (int q = 0; q < world && ok; ++q)
+        while ((int)(hlp_ld_acquire(myflags + stage * HLP_MAXW + q) - target) < 0)
+          if (hlp_now() - t0 > HLP_TIMEOUT_NS) { hl_halt(hs, HALT_PEER); hs[HS_HALT] = HALT_PEER; ok = 0; break; }
+    }
+    s_ok = ok;
+  }
+  __syncthreads();
+  return s_ok != 0;
+}
+
+// exchange 1: gslots = sum over ranks of their slot counters, reduced while the peer loads arrive
+__global__ void __launch_bounds__(256) hl_peer_sum_slots(HlPeers P, int world, int rank, const u32* __restrict__ ctr,
+                                                          u32* __restrict__ hs, uint4* __restrict__ gslots, i64 n4) {
+  if (!hl_peer_wait(reinterpret_cast<const u32*>(P.flags[rank]), ctr, world, 0, hs) || hs[HS_HALT]) return;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (i64)gridDim.x * blockDim.x) {
+    uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+    for (int p = 0; p < world; ++p) {
+      const uint4 v = hlp_ld4(reinterpret_cast<const uint4*>(P.slots[p]) + i);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    gslots[i] = acc;
+  }
+}
+// exchange 2: every rank's (key, count) candidate list -> xall (one block per peer; only the used part travels)
+__global__ void __launch_bounds__(1024) hl_peer_gather_x(HlPeers P, int world, int rank, const u32* __restrict__ ctr,
+                                                          u32* __restrict__ hs, u64* __restrict__ xall) {
+  const i64 xs = 1 + 2 * HLX_CAP;
+  const int p = blockIdx.x;
+  u64* dst = xall + (i64)p * xs;
+  if (!hl_peer_wait(reinterpret_cast<const u32*>(P.flags[rank]), ctr, world, 1, hs)) {
+    if (threadIdx.x == 0) dst[0] = (u64)HALT_PEER << 40;
+    return;
+  }
+  const u64* src = reinterpret_cast<const u64*>(P.x[p]);
+  const u64 h = hlp_ld8(src);
+  const u32 n = min((u32)(h & 0xFFFFFFFFu), (u32)HLX_CAP);
+  if (threadIdx.x == 0) dst[0] = h;
+  for (u32 i = threadIdx.x; i < n; i += blockDim.x) {
+    dst[1 + i] = hlp_ld8(src + 1 + i);
+    dst[1 + HLX_CAP + i] = hlp_ld8(src + 1 + HLX_CAP + i);
+  }
+}
+// exchange 3: bytewise max over ranks of the tied keys' strings (rows < nt) and their lengths -> sred
+__global__ void __launch_bounds__(256) hl_peer_max_s(HlPeers P, int world, int rank, const u32* __restrict__ ctr,
+                                                      u32* __restrict__ hs, uint4* __restrict__ sred, int stride) {
+  if (!hl_peer_wait(reinterpret_cast<const u32*>(P.flags[rank]), ctr, world, 2, hs) || hs[HS_HALT]) return;
+  const u32 nt = min(hs[HS_NT], (u32)HL_TB_CAP);
+  const i64 n4 = (4 * HL_TB_CAP + (i64)nt * stride) / 16;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (i64)gridDim.x * blockDim.x) {
+    uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+    for (int p = 0; p < world; ++p) {
+      const uint4 v = hlp_ld4(reinterpret_cast<const uint4*>(P.s[p]) + i);
+      acc.x = __vmaxu4(acc.x, v.x); acc.y = __vmaxu4(acc.y, v.y); acc.z = __vmaxu4(acc.z, v.z); acc.w = __vmaxu4(acc.w, v.w);
+    }
+    sred[i] = acc;
+  }
+}

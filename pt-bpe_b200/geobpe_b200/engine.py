@@ -7,6 +7,7 @@ follow Python semantics exactly: the vocabulary dicts, JSON key strings for the 
 matrix (algo.py:184-211).
 """
 import ctypes as C
+import os
 import json
 import types
 import math
@@ -277,6 +278,7 @@ class SlotSketch:
     def __init__(self, n_pairs_bound, log2ns=None, variant=2, ctas_per_sm=2):
         if log2ns is None:
             log2ns = max(16, min(24, (max(n_pairs_bound, 2) - 1).bit_length() - 1))   # NS >= pairs / 2; <= 64 MB (L2)
+            log2ns = int(os.environ.get("GEOBPE_LOG2NS", log2ns))                     # tuning knob (scripts/)
         self.log2ns = log2ns
         # the per-CTA shared-memory stage only pays when a CTA sees many more pairs than it has cache entries
         self.variant = variant if n_pairs_bound >= 296 * 32768 else (variant & ~6)
@@ -711,7 +713,7 @@ class Learner:
               WIN_R0=14, WIN_NRES=15, WIN_CNT=16, WIN_J=17, MISMATCH=18, FLAGGED=19, NEWT=20, NTOK=21, OVF=22,
               R2COUNT=23, MAXSTEPS=24, EVCAP=25, HALT_STEP=26, NTMAX=27, N=28, NCL=29, CLCAP=30, CMPT=31, DIST=32)
     HALT_NAMES = {1: "ties", 2: "candidates", 3: "collision", 4: "table", 5: "event log", 6: "empty", 7: "step log",
-                  8: "count"}
+                  8: "count", 9: "peer timeout"}
 
     def _hl_init(self):
         ts = self._ts
@@ -722,7 +724,12 @@ class Learner:
             mx = comm.all_reduce(torch.tensor([maxwin, Tb], device=_dev(), dtype=torch.int64), "max").cpu().numpy()
             maxwin, Tb = int(mx[0]), int(mx[1])
         if self.sketch is None:
-            self.sketch = SlotSketch(Tb)
+            l2 = None
+            if comm is not None and "GEOBPE_LOG2NS" not in os.environ:
+                # sharded: the slot counters cross NVLink every iteration -- a quarter of the one-GPU size (NS >= local pairs / 8);
+                # only slots holding a heavy key matter (candidates = slots >= 0.9 x previous max), see DESIGN 7
+                l2 = max(16, min(24, (max(Tb, 2) - 1).bit_length() - 3))
+            self.sketch = SlotSketch(Tb, log2ns=l2)
         sk = self.sketch
         hl = types.SimpleNamespace()
         hl.hs = _zeros(64, torch.int32)
@@ -750,6 +757,7 @@ class Learner:
             d.log_str = _zeros(cap * hl.stride, torch.uint8)
             d.log_strlen = _zeros(cap, torch.int32)
             d.graphs = {}
+            d.peer = self._peer_setup(sk.log2ns, xe, d.sbuf.numel()) if os.environ.get("GEOBPE_PEER", "1") != "0" else None
             hl.dist = d
         hl.nargs = _lib.load().gb_h_loop_nargs()
         hl.enq = 0                    # iterations enqueued since the state block was last written
@@ -769,6 +777,66 @@ class Learner:
         hl.steps = 0
         self.hl = hl
 
+    def _peer_setup(self, log2ns, xe, sbytes):
+        """symmetric block [slots | x | sbuf | flags] on every rank, mapped into every other rank through CUDA IPC, for the
+        peer-memory transport of the sharded loop (csrc/k_hloop_dist.cuh); None (on every rank) if any rank cannot set it
+        up -- the loop then keeps the three NCCL collectives per iteration"""
+        import socket
+        lib, comm = _lib.load(), self.comm
+        maxw = int(lib.gb_peer_max_world())
+        al = lambda n: (n + 255) // 256 * 256
+        o_x = al(4 << log2ns)
+        o_s = o_x + al(8 * xe)
+        o_f = o_s + al(sbytes)
+        total = o_f + al(4 * 3 * maxw)
+        pr = types.SimpleNamespace(base=None, opened=[], lib=lib)
+        handle, err = b"", None
+        if comm.world > maxw:
+            err = "world too large"
+        else:
+            base, h = C.c_void_p(), (C.c_ubyte * 64)()
+            if lib.gb_peer_alloc(total, C.byref(base), h) != 0:
+                err = lib.gb_last_error().decode()
+            else:
+                pr.base, handle = base.value, bytes(h)
+        infos = comm.all_gather_object((socket.gethostname(), handle, err))
+        ok = all(e is None for _, _, e in infos) and len({hn for hn, _, _ in infos}) == 1
+        bases = []
+        if ok:
+            for r, (_, hb, _) in enumerate(infos):
+                if r == comm.rank:
+                    bases.append(pr.base)
+                    continue
+                q = C.c_void_p()
+                if lib.gb_peer_open((C.c_ubyte * 64).from_buffer_copy(hb), C.byref(q)) != 0:
+                    err = lib.gb_last_error().decode()
+                    break
+                pr.opened.append(q.value)
+                bases.append(q.value)
+        ok = all(comm.all_gather_object(ok and err is None))
+        if not ok:
+            self._peer_release(pr)
+            return None
+        pr.table = (C.c_uint64 * (4 * comm.world))(*([b for b in bases] + [b + o_x for b in bases] + [b + o_s for b in bases] +
+                                                     [b + o_f for b in bases]))
+        pr.slots, pr.x, pr.s = pr.base, pr.base + o_x, pr.base + o_s
+        pr.gslots = _zeros(1 << log2ns, torch.int32)
+        pr.sred = _zeros(sbytes, torch.uint8)
+        pr.ctr = _zeros(4, torch.int32)
+        torch.cuda.synchronize()
+        comm.all_reduce(torch.zeros(1, device=_dev()))          # every block is zeroed and mapped before the first signal
+        torch.cuda.synchronize()
+        return pr
+
+    @staticmethod
+    def _peer_release(pr):
+        for q in pr.opened:
+            pr.lib.gb_peer_close(C.c_void_p(q))
+        pr.opened = []
+        if pr.base:
+            pr.lib.gb_peer_free(C.c_void_p(pr.base))
+            pr.base = None
+
     def _hl_args(self):
         ts, sk, hl = self._ts, self.sketch, self.hl
         a, b = ts.a, ts.b
@@ -783,6 +851,13 @@ class Learner:
         d = hl.dist
         vals += ([P(d.x), P(d.xall), self.comm.world, self.comm.rank, P(d.tie_skeys), P(d.tie_smin), P(d.sbuf), P(d.log_str),
                   P(d.log_strlen)] if d is not None else [0] * 9)
+        pr = d.peer if d is not None else None
+        if pr is not None:         # peer-memory transport: the loop's slots / x / sbuf are the symmetric block's
+            vals[19] = pr.slots
+            vals[-9], vals[-3] = pr.x, pr.s
+            vals += [C.addressof(pr.table), P(pr.gslots), P(pr.sred), P(pr.ctr)]
+        else:
+            vals += [0] * 4
         assert len(vals) == hl.nargs, (len(vals), hl.nargs)
         return (C.c_int64 * len(vals))(*[v if v < (1 << 63) else v - (1 << 64) for v in vals])
 
@@ -841,6 +916,11 @@ class Learner:
         if ev is not None:
             e1.record()
             ev.append((e0, e1, None))          # (the live-token count of that iteration is filled in by bench.py)
+        if d.peer is not None:        # exchanges happen inside the parts' own kernels (loads from the peers' blocks)
+            part(1, 5)
+            part(2, 5)
+            part(3, 6)
+            return
         comm.all_reduce(sk.slots, "sum")
         part(1, 3)
         comm.all_gather_into(d.xall, d.x)
@@ -952,8 +1032,9 @@ class Learner:
             hl.r2 += int(h[H["R2COUNT"]])
             hl.ntmax = max(getattr(hl, "ntmax", 0), int(h[H["NTMAX"]]))
             rest = want - done
-            if halt in (3, 5, 8):
-                raise RuntimeError({3: "64-bit content-hash collision detected (window bins differ); re-run with another HASH_BASE",
+            if halt in (3, 5, 8, 9):
+                raise RuntimeError({9: "a peer rank did not signal within 4 s (peer-memory transport of the sharded loop)",
+                                    3: "64-bit content-hash collision detected (window bins differ); re-run with another HASH_BASE",
                                     5: "merge-event log overflow",
                                     8: "flagged occurrences differ from the histogram count"}[halt])
             if halt == 6:

@@ -15,7 +15,9 @@ GEN = (40, 48, 31)
 STEPS = 80          # crosses one compaction period of the device-driven loop
 
 
-def worker(rank, world, port, q, async_steps):
+def worker(rank, world, port, q, mode):
+    async_steps = mode != "host"
+    os.environ["GEOBPE_PEER"] = "1" if mode == "peer" else "0"
     for p in (os.path.join(ROOT, "pt-bpe_b200"),):
         sys.path.insert(0, p)
     import torch.distributed as dist
@@ -38,20 +40,22 @@ def worker(rank, world, port, q, async_steps):
         lo, hi = np.searchsorted(pos, o[i]), np.searchsorted(pos, o[i + 1])
         segs.append([[int(3 * (pos[j] - o[i])), int(tid[j]), int(3 * ln[j] - (1 if glue[j] & E.LAST else 0))]
                      for j in range(lo, hi)])
-    q.put((rank, a, [list(p) for p in L.pop_log], [[k, v] for k, v in L.tokens.items()], segs))
+    transport = "peer" if (L.hl is not None and L.hl.dist is not None and L.hl.dist.peer is not None) else "nccl"
+    halts = dict(L.hl.halts) if L.hl is not None else {}
+    q.put((rank, a, [list(p) for p in L.pop_log], [[k, v] for k, v in L.tokens.items()], segs, transport, halts))
     dist.destroy_process_group()
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("async_steps", [True, False], ids=["device-loop", "host-driven"])
-def test_two_gpu_h_mode_matches_oracle(async_steps):
+@pytest.mark.parametrize("mode", ["peer", "nccl", "host"], ids=["device-loop-peer-memory", "device-loop-nccl", "host-driven"])
+def test_two_gpu_h_mode_matches_oracle(mode):
     import torch.multiprocessing as mp
     import geobpe_oracle as O
     from geobpe_b200 import synthetic
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = 29500 + os.getpid() % 1000
-    ps = [ctx.Process(target=worker, args=(r, 2, port + (7 if async_steps else 0), q, async_steps)) for r in range(2)]
+    ps = [ctx.Process(target=worker, args=(r, 2, port + {"peer": 0, "nccl": 7, "host": 14}[mode], q, mode)) for r in range(2)]
     [p.start() for p in ps]
     res = sorted(q.get(timeout=300) for _ in ps)
     [p.join(60) for p in ps]
@@ -62,7 +66,9 @@ def test_two_gpu_h_mode_matches_oracle(async_steps):
         ora.step()
     want_pops = [list(p) for p in ora.pop_log]
     want_tokens = [[k, v] for k, v in ora._tokens.items()]
-    for rank, a, pops, tokens, segs in res:
+    for rank, a, pops, tokens, segs, transport, halts in res:
+        if mode == "peer":           # the exchanges really went through peer memory, and no rank timed out on a signal
+            assert transport == "peer" and 9 not in halts
         assert pops == want_pops
         assert tokens == want_tokens
         for i, seg in enumerate(segs):
