@@ -292,8 +292,9 @@ def main():
     k1_ms = [a.elapsed_time(b) for a, b, _ in (L.k1_events or [])]
     k1_T = [t for _, _, t in (L.k1_events or [])]
     k1_note = "CUDA events around every K1 launch of the timed region"
-    if L.async_steps and world > 1:
-        # sharded loop: the timed region replays CUDA graphs (kernels + NCCL); K1 is timed in the iterations that follow,
+    peer = L.hl is not None and L.hl.dist is not None and L.hl.dist.peer is not None
+    if L.async_steps and world > 1 and not peer:
+        # sharded loop, NCCL exchanges: the timed region replays CUDA graphs (kernels + NCCL); K1 is timed in the iterations that follow,
         # launched part by part with CUDA events around every part-0 call (slots memset + k_slot_count)
         n_inst = min(128, args.steps)
         T_inst = L.ts.T

@@ -225,7 +225,7 @@ int64_t gb_h_loop_sbuf_bytes(int stride);
  * each part 256-byte aligned), sends the 64-byte CUDA IPC handle to the other ranks (any transport) and maps theirs with
  * gb_peer_open.  args_host then carries a host table u64 [4][world] of all ranks' slots / x / sbuf / flags addresses
  * (HA_PEERS) plus local buffers for the reduced slot counters, the reduced tie strings and u32 [4] stage counters;
- * gb_h_loop_part then needs no collective between the parts.  A rank that sees no signal from a peer within 4 s halts
+ * gb_h_loop_part then needs no collective between the parts.  A rank that sees no signal from a peer within 20 s halts
  * with code 9 instead of spinning forever. */
 int gb_peer_alloc(int64_t bytes, void** ptr_out_host, unsigned char* handle64_out_host);
 int gb_peer_open(const unsigned char* handle64_host, void** ptr_out_host);

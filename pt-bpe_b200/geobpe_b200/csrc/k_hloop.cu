@@ -518,6 +518,8 @@ static cudaEvent_t hl_event() {
   return g_ev[g_ev_used++];
 }
 
+template <bool CS> static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t st);
+
 template <bool CS>
 static int h_loop_impl(const int64_t* a, int nsteps, int parity, int step0, int compact_after, int* parity_out, cudaStream_t st) {
   u32* hs = (u32*)a[HA_HS];
@@ -580,6 +582,14 @@ static int h_loop_impl(const int64_t* a, int nsteps, int parity, int step0, int 
     return 0;
   };
   for (int s = 0; s < nsteps; ++s) {
+    if (a[HA_PEERS]) {
+      // sharded run over the peer-memory transport: the four parts back to back, no host-issued collective in between,
+      // so whole periods are captured and replayed exactly like the one-GPU loop
+      for (int part = 0; part < 4; ++part) { int rc = h_loop_part_impl<CS>(a, part, p, st); if (rc) return rc; }
+      dirty = true;
+      if ((step0 + s + 1) % period == 0) { int rc = compact(); if (rc) return rc; }
+      continue;
+    }
     KeysHLT<CS> kf{hsh[p], glue[p], len[p], powtab, P};
     GB_CK(cudaMemsetAsync(slots, 0, sizeof(u32) << log2ns, st));
     if (g_time_k1) GB_CK(cudaEventRecord(hl_event(), st));
@@ -736,12 +746,15 @@ static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t
     case 0: {
       const size_t smem = cache ? 2 * sizeof(u32) * KS_CACHE : 0;
       GB_CK(cudaMemsetAsync(slots, 0, sizeof(u32) << log2ns, st));
+      if (g_time_k1) GB_CK(cudaEventRecord(hl_event(), st));
       if (cache) {
-        GB_CK(cudaFuncSetAttribute(k_slot_count<KeysHLT<CS>, false, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (!(g_cap_stream && st == g_cap_stream))
+          GB_CK(cudaFuncSetAttribute(k_slot_count<KeysHLT<CS>, false, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_slot_count<KeysHLT<CS>, false, 1, false><<<count_blocks, KS_THREADS, smem, st>>>(kf, Nmax, slots, shift, nullptr, hs);
       } else {
         k_slot_count<KeysHLT<CS>, false, 0, false><<<count_blocks, KS_THREADS, 0, st>>>(kf, Nmax, slots, shift, nullptr, hs);
       }
+      if (g_time_k1) GB_CK(cudaEventRecord(hl_event(), st));
       if (ptab) hl_peer_signal<<<1, 32, 0, st>>>(PP, world, rank, 0, pctr);
       break;
     }

@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(HL_TB_CAP) hl_tie_pick(u32* __restrict__ hs, u
 // write of a region always sits behind a later wait).  Waits are bounded: a rank that sees no signal within
 // HLP_TIMEOUT_NS halts with HALT_PEER and stops waiting, so a dead peer cannot hang the GPU.
 #define HLP_MAXW 16
-#define HLP_TIMEOUT_NS 4000000000ull
+#define HLP_TIMEOUT_NS 20000000000ull
 struct HlPeers { u64 slots[HLP_MAXW]; u64 x[HLP_MAXW]; u64 s[HLP_MAXW]; u64 flags[HLP_MAXW]; };
 
 __device__ __forceinline__ void hlp_st_release(u32* p, u32 v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }

@@ -730,6 +730,8 @@ class Learner:
                 # only slots holding a heavy key matter (candidates = slots >= 0.9 x previous max), see DESIGN 7
                 l2 = max(16, min(24, (max(Tb, 2) - 1).bit_length() - 3))
             self.sketch = SlotSketch(Tb, log2ns=l2)
+            if comm is not None:     # the exact table also takes the other ranks' keys of the candidate slots
+                self.sketch.small.ensure(4096 * comm.world)
         sk = self.sketch
         hl = types.SimpleNamespace()
         hl.hs = _zeros(64, torch.int32)
@@ -890,7 +892,7 @@ class Learner:
             self._hl_init()
             self._hl_push_state()
         hl = self.hl
-        if hl.dist is not None:
+        if hl.dist is not None and hl.dist.peer is None:
             return self._hl_enqueue_dist(nsteps)
         hl.lazy += nsteps                   # launched in whole compaction periods (CUDA-graph replays), the rest at sync()
         self._pending += nsteps
@@ -937,7 +939,7 @@ class Learner:
             self._hl_init()
             self._hl_push_state()
         hl = self.hl
-        if hl.dist is None:
+        if hl.dist is None or hl.dist.peer is not None:     # kernels only: whole periods captured on the C side
             _lib.call_n("gb_h_loop_prepare", 0, hl.args, hl.nargs)
             return
         p0 = hl.parity
@@ -974,7 +976,7 @@ class Learner:
     def _hl_flush(self, n):
         hl = self.hl
         if n > 0:
-            if hl.dist is not None:
+            if hl.dist is not None and hl.dist.peer is None:
                 self._hl_run_dist(n)
             else:
                 self._hl_call(n, 0)
@@ -984,7 +986,8 @@ class Learner:
     def _hl_call(self, nsteps, compact_after):
         hl = self.hl
         out = C.c_int(0)
-        _lib.call_n("gb_h_loop", nsteps * 12 + 4 * (nsteps // hl.period + compact_after), hl.args, hl.nargs, nsteps, hl.parity,
+        per = 19 if (hl.dist is not None and hl.dist.peer is not None) else 12
+        _lib.call_n("gb_h_loop", nsteps * per + 4 * (nsteps // hl.period + compact_after), hl.args, hl.nargs, nsteps, hl.parity,
                     hl.enq, compact_after, C.byref(out))
         hl.parity = out.value
 
@@ -1033,7 +1036,7 @@ class Learner:
             hl.ntmax = max(getattr(hl, "ntmax", 0), int(h[H["NTMAX"]]))
             rest = want - done
             if halt in (3, 5, 8, 9):
-                raise RuntimeError({9: "a peer rank did not signal within 4 s (peer-memory transport of the sharded loop)",
+                raise RuntimeError({9: "a peer rank did not signal within 20 s (peer-memory transport of the sharded loop)",
                                     3: "64-bit content-hash collision detected (window bins differ); re-run with another HASH_BASE",
                                     5: "merge-event log overflow",
                                     8: "flagged occurrences differ from the histogram count"}[halt])
