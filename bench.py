@@ -364,6 +364,8 @@ def main():
                      pass2_achieved=pr["bytes_per_token"] * pr["tokens"] / (pr["pass2_ms"] * 1e-3) / 1e9,
                      note="K1 pass 1 (k_slot_count) alone on this workload's token arrays tiled to the per-GPU shard of "
                           "BASELINE config 5 (48 M tokens > L2); pass2_* = k_cand_count (exact resolution) on the same arrays")
+    if world > 1:
+        L.close()                                      # frees the peer-memory block (collective)
     del L
     torch.cuda.empty_cache()
 
@@ -386,6 +388,8 @@ def main():
             t = torch.tensor([dt], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.item())
+        if world > 1:
+            L2.close()
         d2h = sum(o.numel() * o.element_size() for o in out)
         e2e = {"value": args.steps / dt, "unit": "merge_iters/s", "h2d_bytes_per_step": L2.bb.h2d_bytes / args.steps,
                "d2h_bytes_per_step": d2h / args.steps, "seconds": dt,

@@ -830,6 +830,22 @@ class Learner:
         torch.cuda.synchronize()
         return pr
 
+    def close(self):
+        """release the symmetric block of the peer-memory transport (collective: every rank calls it; a barrier makes sure
+        no peer kernel still reads this rank's block).  The learner falls back to the NCCL exchanges afterwards."""
+        self.sync()
+        d = self.hl.dist if self.hl is not None else None
+        if d is None or d.peer is None:
+            return
+        torch.cuda.synchronize()
+        self.comm.all_reduce(torch.zeros(1, device=_dev()))
+        torch.cuda.synchronize()
+        self._peer_release(d.peer)
+        d.peer = None
+        d.graphs = {}
+        self.hl.args = self._hl_args()
+        self.hl._args_key = tuple(self.hl.args)
+
     @staticmethod
     def _peer_release(pr):
         for q in pr.opened:
