@@ -237,8 +237,12 @@ int gb_h_loop_use_graphs(int enable);
 /* capture the graphs of both buffer parities now (warm-up) instead of at the first whole period */
 int gb_h_loop_prepare(const int64_t* args_host, int n_args, void* stream);
 int gb_h_loop_kernels_per_step(void);
-/* CUDA-event timing of the pair-count kernel inside the loop: enable, run, synchronize, then read the per-launch ms */
-int gb_h_loop_time_k1(int enable);
+/* slot counters inside the loop: 1 (default) = exact recount (k_slot_count) at the start of every compaction period and
+ * upper bounds maintained from the merge events in between (hl_bump_list); 0 = recount every iteration */
+int gb_h_loop_incremental(int enable);
+/* CUDA-event timing inside the loop: mode 1 = around every k_slot_count launch, 2 = around every first-round
+ * hl_cand_count launch, 0 = off; run, synchronize, then read the per-launch ms */
+int gb_h_loop_time_k1(int mode);
 int gb_h_loop_k1_times(float* ms_host, int cap);
 
 /* ---- K4/K5/K6: NeRF windows, Kabsch RMSD, medoid assignment (tokenizer.py:347-363, nerf.py:84-210,

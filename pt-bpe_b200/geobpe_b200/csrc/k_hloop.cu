@@ -403,6 +403,46 @@ __global__ void __launch_bounds__(256) hl_unflag_list(const u32* __restrict__ hs
   for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
     if (cl_key[i] == win) { flags[cl_j[i]] = 0; rmark[cl_r[i]] = 0; }
 }
+// Slot counters between full recounts: UPPER BOUNDS maintained from the merge events.  A merge creates at most two new
+// pairs (left neighbour, new token) and (new token, right neighbour): their slots are incremented here, from the
+// post-merge arrays; pairs that disappear are not decremented (except the winner's own occurrences, all of which are
+// gone), so slots[s] >= true count of slot s at all times -- which is all the candidate logic needs: a key outside the
+// slots with bound >= thr has count <= its slot's count <= bound < thr.  k_slot_count makes the bounds exact again at
+// the start of every period.
+__global__ void __launch_bounds__(256) hl_bump_list(const u32* __restrict__ hs, const u64* __restrict__ hs64, const u64* __restrict__ cl_key,
+                                                     const u32* __restrict__ cl_j, const u64* __restrict__ hsh, const u32* __restrict__ glue,
+                                                     const u32* __restrict__ ls, const u32* __restrict__ tid, const u64* __restrict__ powtab,
+                                                     u64 P, u32* __restrict__ slots, int shift) {
+  if (hs[HS_HALT]) return;
+  const u32 n = hs[HS_NCL], new_tid = hs[HS_NTOK];
+  const i64 N = (i64)hs[HS_N];
+  const u64 win = hs64[0];
+  if (blockIdx.x == 0 && threadIdx.x == 0 && hs[HS_FLAGGED]) atomicSub(&slots[gb_slot_of(win, shift)], hs[HS_FLAGGED]);
+  for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    if (cl_key[i] != win) continue;
+    const u32 j = cl_j[i], l = ls[j];
+    if (l == 0u || tid[j] != new_tid) continue;        // the skipped occurrences of a run: their left token was absorbed
+    const u64 hj = hsh[j];
+    const u32 gj = glue[j];
+    if (!(gj & GB_LAST_FLAG)) {                         // (new token, right neighbour)
+      const i64 r = (i64)j + 1 + (l >> 16);
+      if (r < N) {
+        const u64 k = gb_key_h(hj, gj, hsh[r], P, __ldg(powtab + (2u * (ls[r] & 0xFFFFu) - 1u)));
+        atomicAdd(&slots[gb_slot_of(k, shift)], 1u);
+      }
+    }
+    i64 q = (i64)j - 1;                                  // (left neighbour, new token): nearest live entry to the left
+    while (q >= 0 && ls[q] == 0u) --q;
+    if (q >= 0) {
+      const u32 gq = glue[q];
+      // a freshly merged left neighbour has counted this pair as its own right pair already
+      if (!(gq & GB_LAST_FLAG) && tid[q] != new_tid) {
+        const u64 k = gb_key_h(hsh[q], gq, hj, P, __ldg(powtab + (2u * (l & 0xFFFFu) - 1u)));
+        atomicAdd(&slots[gb_slot_of(k, shift)], 1u);
+      }
+    }
+  }
+}
 // commit the iteration (step log, counters) and reset the per-iteration words for the next one
 __global__ void hl_end(u32* __restrict__ hs, const u64* __restrict__ hs64, u64* __restrict__ log_key, u32* __restrict__ log_cnt,
                        u32* __restrict__ log_r0, u32* __restrict__ log_nres, u32* __restrict__ log_evstart, u32* __restrict__ log_nk) {
@@ -509,7 +549,7 @@ enum { HA_HS = 0, HA_HS64, HA_HSH0, HA_HSH1, HA_GLUE0, HA_GLUE1, HA_POS0, HA_POS
 
 // optional CUDA-event timing of the pair-count kernel inside the loop (bench.py's roofline leg)
 #include <vector>
-static bool g_time_k1 = false;
+static int g_time_k1 = 0;        // 1: events around k_slot_count, 2: around the round-1 hl_cand_count
 static cudaStream_t g_cap_stream = nullptr;   // private stream the CUDA graphs are captured on
 static std::vector<cudaEvent_t> g_ev;
 static size_t g_ev_used = 0;
@@ -518,7 +558,9 @@ static cudaEvent_t hl_event() {
   return g_ev[g_ev_used++];
 }
 
-template <bool CS> static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t st);
+template <bool CS> static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t st, bool full);
+static bool g_incremental = true;      // slot counters: full recount once per period, upper bounds in between
+extern "C" int gb_h_loop_incremental(int enable) { g_incremental = enable != 0; return 0; }
 
 template <bool CS>
 static int h_loop_impl(const int64_t* a, int nsteps, int parity, int step0, int compact_after, int* parity_out, cudaStream_t st) {
@@ -582,30 +624,36 @@ static int h_loop_impl(const int64_t* a, int nsteps, int parity, int step0, int 
     return 0;
   };
   for (int s = 0; s < nsteps; ++s) {
+    const bool full = !g_incremental || (step0 + s) % period == 0;
     if (a[HA_PEERS]) {
       // sharded run over the peer-memory transport: the four parts back to back, no host-issued collective in between,
       // so whole periods are captured and replayed exactly like the one-GPU loop
-      for (int part = 0; part < 4; ++part) { int rc = h_loop_part_impl<CS>(a, part, p, st); if (rc) return rc; }
+      for (int part = 0; part < 4; ++part) { int rc = h_loop_part_impl<CS>(a, part, p, st, full); if (rc) return rc; }
       dirty = true;
       if ((step0 + s + 1) % period == 0) { int rc = compact(); if (rc) return rc; }
       continue;
     }
     KeysHLT<CS> kf{hsh[p], glue[p], len[p], powtab, P};
-    GB_CK(cudaMemsetAsync(slots, 0, sizeof(u32) << log2ns, st));
-    if (g_time_k1) GB_CK(cudaEventRecord(hl_event(), st));
-    if (cache) k_slot_count<KeysHLT<CS>, false, 1, false><<<count_blocks, KS_THREADS, smem, st>>>(kf, Nmax, slots, shift, nullptr, hs);
-    else k_slot_count<KeysHLT<CS>, false, 0, false><<<count_blocks, KS_THREADS, 0, st>>>(kf, Nmax, slots, shift, nullptr, hs);
-    if (g_time_k1) GB_CK(cudaEventRecord(hl_event(), st));
+    if (full) {       // exact slot counts at the start of a period; upper bounds (hl_bump_list) in between
+      GB_CK(cudaMemsetAsync(slots, 0, sizeof(u32) << log2ns, st));
+      if (g_time_k1 == 1) GB_CK(cudaEventRecord(hl_event(), st));
+      if (cache) k_slot_count<KeysHLT<CS>, false, 1, false><<<count_blocks, KS_THREADS, smem, st>>>(kf, Nmax, slots, shift, nullptr, hs);
+      else k_slot_count<KeysHLT<CS>, false, 0, false><<<count_blocks, KS_THREADS, 0, st>>>(kf, Nmax, slots, shift, nullptr, hs);
+      if (g_time_k1 == 1) GB_CK(cudaEventRecord(hl_event(), st));
+    }
     hl_slots_scan<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs, cand, (u32)cap);
     for (int round = 1; round <= 2; ++round) {
       if (round == 2) hl_slots_collect<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs, round, cand, (u32)cap);
+      if (g_time_k1 == 2 && round == 1) GB_CK(cudaEventRecord(hl_event(), st));
       hl_cand_count<CS><<<pass_blocks, KS_THREADS, 0, st>>>(kf, shift, cand, (u32)cap, tk, tc, tm, (u64)(M - 1), hs, round, cl_key, cl_j);
+      if (g_time_k1 == 2 && round == 1) GB_CK(cudaEventRecord(hl_event(), st));
       hl_decide<<<1, 1024, 0, st>>>(tk, tc, tm, M, hs, round, tie_keys, tie_min, (u32)cap);
     }
     hl_tiebreak<<<1, HL_TB_CAP, 0, st>>>(hs, hs64, tie_keys, tie_min, pos[p], len[p], rbins, R, strbuf, stride);
     hl_flag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark, pos[p], len[p], rbins, R);
     hl_apply_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, flags, rmark, hsh[p], glue[p], len[p], tid[p], pos[p],
                                                (u32*)a[HA_EVL], (u32*)a[HA_EVR], (u32*)a[HA_EVP]);
+    if (g_incremental) hl_bump_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, hsh[p], glue[p], len[p], tid[p], powtab, P, slots, shift);
     hl_unflag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark);
     hl_end<<<1, 1, 0, st>>>(hs, hs64, (u64*)a[HA_LKEY], (u32*)a[HA_LCNT], (u32*)a[HA_LR0], (u32*)a[HA_LNRES], (u32*)a[HA_LEVS],
                             (u32*)a[HA_LNK]);
@@ -682,7 +730,7 @@ extern "C" int gb_h_loop(const int64_t* args_host, int n_args, int nsteps, int p
 //   part 3: tie pick, flag, apply, unflag, end
 // (an iteration that would need a second candidate round halts and runs on the host path: ~1 in 1000)
 template <bool CS>
-static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t st) {
+static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t st, bool full) {
   u32* hs = (u32*)a[HA_HS];
   u64* hs64 = (u64*)a[HA_HS64];
   const int p = parity & 1;
@@ -745,8 +793,12 @@ static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t
   switch (part) {
     case 0: {
       const size_t smem = cache ? 2 * sizeof(u32) * KS_CACHE : 0;
+      if (!full) {        // the local counters are upper bounds kept by hl_bump_list since the last recount
+        if (ptab) hl_peer_signal<<<1, 32, 0, st>>>(PP, world, rank, 0, pctr);
+        break;
+      }
       GB_CK(cudaMemsetAsync(slots, 0, sizeof(u32) << log2ns, st));
-      if (g_time_k1) GB_CK(cudaEventRecord(hl_event(), st));
+      if (g_time_k1 == 1) GB_CK(cudaEventRecord(hl_event(), st));
       if (cache) {
         if (!(g_cap_stream && st == g_cap_stream))
           GB_CK(cudaFuncSetAttribute(k_slot_count<KeysHLT<CS>, false, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -754,14 +806,16 @@ static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t
       } else {
         k_slot_count<KeysHLT<CS>, false, 0, false><<<count_blocks, KS_THREADS, 0, st>>>(kf, Nmax, slots, shift, nullptr, hs);
       }
-      if (g_time_k1) GB_CK(cudaEventRecord(hl_event(), st));
+      if (g_time_k1 == 1) GB_CK(cudaEventRecord(hl_event(), st));
       if (ptab) hl_peer_signal<<<1, 32, 0, st>>>(PP, world, rank, 0, pctr);
       break;
     }
     case 1:
       if (ptab) hl_peer_sum_slots<<<sms * 2, 256, 0, st>>>(PP, world, rank, pctr, hs, (uint4*)gslots, ((i64)1 << log2ns) / 4);
       hl_slots_scan<<<scan_blocks, 256, 0, st>>>((const uint4*)(ptab ? gslots : slots), bmax, hs, cand, (u32)cap);
+      if (g_time_k1 == 2) GB_CK(cudaEventRecord(hl_event(), st));
       hl_cand_count<CS><<<pass_blocks, KS_THREADS, 0, st>>>(kf, shift, cand, (u32)cap, tk, tc, tm, (u64)(M - 1), hs, 1, cl_key, cl_j);
+      if (g_time_k1 == 2) GB_CK(cudaEventRecord(hl_event(), st));
       hl_table_export<<<1, 1024, 0, st>>>(tk, tc, M, hs, 1, x);
       if (ptab) hl_peer_signal<<<1, 32, 0, st>>>(PP, world, rank, 1, pctr);
       break;
@@ -779,6 +833,8 @@ static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t
       hl_flag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark, pos, len, rbins, R);
       hl_apply_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, flags, rmark, hsh, glue, len, tid, pos,
                                                  (u32*)a[HA_EVL], (u32*)a[HA_EVR], (u32*)a[HA_EVP]);
+      if (g_incremental && ptab)
+        hl_bump_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, hsh, glue, len, tid, (const u64*)a[HA_POWTAB], (u64)a[HA_P], slots, shift);
       hl_unflag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark);
       hl_end<<<1, 1, 0, st>>>(hs, hs64, (u64*)a[HA_LKEY], (u32*)a[HA_LCNT], (u32*)a[HA_LR0], (u32*)a[HA_LNRES], (u32*)a[HA_LEVS],
                               (u32*)a[HA_LNK]);
@@ -792,8 +848,8 @@ static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t
 }
 extern "C" int gb_h_loop_part(const int64_t* args_host, int n_args, int part, int parity, void* stream) {
   if (n_args != HA_N) { gb_set_error("gb_h_loop_part: expected %d arguments, got %d", (int)HA_N, n_args); return -2; }
-  return args_host[HA_STREAMING] ? h_loop_part_impl<true>(args_host, part, parity, (cudaStream_t)stream)
-                                 : h_loop_part_impl<false>(args_host, part, parity, (cudaStream_t)stream);
+  return args_host[HA_STREAMING] ? h_loop_part_impl<true>(args_host, part, parity, (cudaStream_t)stream, true)
+                                 : h_loop_part_impl<false>(args_host, part, parity, (cudaStream_t)stream, true);
 }
 // ---- symmetric blocks for the peer-memory transport ------------------------------------------------------------------
 // gb_peer_alloc: cudaMalloc + zero + CUDA IPC handle (64 bytes, to be sent to the other ranks by any means);
@@ -830,7 +886,7 @@ extern "C" int gb_h_loop_prepare(const int64_t* args_host, int n_args, void* str
   return args_host[HA_STREAMING] ? h_loop_graphs<true>(args_host, period, (cudaStream_t)stream)
                                  : h_loop_graphs<false>(args_host, period, (cudaStream_t)stream);
 }
-extern "C" int gb_h_loop_time_k1(int enable) { g_time_k1 = enable != 0; g_ev_used = 0; return 0; }
+extern "C" int gb_h_loop_time_k1(int mode) { g_time_k1 = mode; g_ev_used = 0; return 0; }
 // elapsed ms of every timed k_slot_count launch since gb_h_loop_time_k1(1) (call after a synchronize); returns the count
 extern "C" int gb_h_loop_k1_times(float* ms_host, int cap) {
   int n = 0;
