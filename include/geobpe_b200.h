@@ -240,6 +240,10 @@ int gb_h_loop_kernels_per_step(void);
 /* slot counters inside the loop: 1 (default) = exact recount (k_slot_count) at the start of every compaction period and
  * upper bounds maintained from the merge events in between (hl_bump_list); 0 = recount every iteration */
 int gb_h_loop_incremental(int enable);
+/* 1 (default) = an inconclusive first candidate round is followed by a second one inside the loop (three more launches per
+ * iteration that are no-ops ~999 times in 1000); 0 = such an iteration halts (code 2) and runs once on the host path
+ * (faster steady state, but a halt drains the queue: measured worse end to end at 2 000 merges) */
+int gb_h_loop_round2(int enable);
 /* CUDA-event timing inside the loop: mode 1 = around every k_slot_count launch, 2 = around every first-round
  * hl_cand_count launch, 0 = off; run, synchronize, then read the per-launch ms */
 int gb_h_loop_time_k1(int mode);

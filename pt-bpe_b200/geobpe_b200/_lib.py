@@ -64,6 +64,7 @@ SIGNATURES = {
     "gb_h_loop_kernels_per_step": [],
     "gb_h_loop_time_k1": [I32],
     "gb_h_loop_incremental": [I32],
+    "gb_h_loop_round2": [I32],
     "gb_h_loop_k1_times": [P, I32],
     "gb_last_error": [],
     "gb_abi_version": [],

@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(256) hl_slots_collect(const uint4* __restrict_
 // ---- exact argmax over the small table + conclusiveness test (one block) -----------------------------------------
 __global__ void __launch_bounds__(1024) hl_decide(u64* __restrict__ tk, u32* __restrict__ tc, u32* __restrict__ tm,
                                                    i64 M, u32* __restrict__ hs, int round, u64* __restrict__ tie_keys,
-                                                   u32* __restrict__ tie_min, u32 cap) {
+                                                   u32* __restrict__ tie_min, u32 cap, int allow_r2) {
   if (hs[HS_HALT] || (round == 2 && !hs[HS_ROUND2])) return;
   __shared__ u32 s_mx[32], s_nd[32], s_nt;
   u32 mx = 0, nd = 0;
@@ -124,7 +124,8 @@ __global__ void __launch_bounds__(1024) hl_decide(u64* __restrict__ tk, u32* __r
     }
   }
   // sharded run: a second round would need another exchange per iteration for a ~1-in-1000 event: hand it to the host
-  if (threadIdx.x == 0 && round == 1 && hs[HS_DIST] && hs[HS_ROUND2] && !hs[HS_HALT]) hl_halt(hs, HALT_CAND);
+  // (one GPU, default: the same -- the second-round kernels would otherwise be launched as no-ops in every iteration)
+  if (threadIdx.x == 0 && round == 1 && (hs[HS_DIST] || !allow_r2) && hs[HS_ROUND2] && !hs[HS_HALT]) hl_halt(hs, HALT_CAND);
   // the table is consumed (ties are copied out): leave it cleared for the next candidate pass
   for (i64 i = threadIdx.x; i < M; i += blockDim.x) { tk[i] = GB_EMPTY_KEY; tc[i] = 0u; tm[i] = 0xFFFFFFFFu; }
 }
@@ -412,7 +413,8 @@ __global__ void __launch_bounds__(256) hl_unflag_list(const u32* __restrict__ hs
 __global__ void __launch_bounds__(256) hl_bump_list(const u32* __restrict__ hs, const u64* __restrict__ hs64, const u64* __restrict__ cl_key,
                                                      const u32* __restrict__ cl_j, const u64* __restrict__ hsh, const u32* __restrict__ glue,
                                                      const u32* __restrict__ ls, const u32* __restrict__ tid, const u64* __restrict__ powtab,
-                                                     u64 P, u32* __restrict__ slots, int shift) {
+                                                     u64 P, u32* __restrict__ slots, int shift, const u32* __restrict__ cl_r,
+                                                     u8* __restrict__ flags, u8* __restrict__ rmark) {
   if (hs[HS_HALT]) return;
   const u32 n = hs[HS_NCL], new_tid = hs[HS_NTOK];
   const i64 N = (i64)hs[HS_N];
@@ -421,6 +423,7 @@ __global__ void __launch_bounds__(256) hl_bump_list(const u32* __restrict__ hs, 
   for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     if (cl_key[i] != win) continue;
     const u32 j = cl_j[i], l = ls[j];
+    flags[j] = 0; rmark[cl_r[i]] = 0;                   // (= hl_unflag_list: nothing here reads the marks)
     if (l == 0u || tid[j] != new_tid) continue;        // the skipped occurrences of a run: their left token was absorbed
     const u64 hj = hsh[j];
     const u32 gj = glue[j];
@@ -559,6 +562,8 @@ static cudaEvent_t hl_event() {
 }
 
 template <bool CS> static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t st, bool full);
+static bool g_round2 = true;           // in-loop second candidate round (else: such an iteration halts to the host path)
+extern "C" int gb_h_loop_round2(int enable) { g_round2 = enable != 0; return 0; }
 static bool g_incremental = true;      // slot counters: full recount once per period, upper bounds in between
 extern "C" int gb_h_loop_incremental(int enable) { g_incremental = enable != 0; return 0; }
 
@@ -642,19 +647,21 @@ static int h_loop_impl(const int64_t* a, int nsteps, int parity, int step0, int 
       if (g_time_k1 == 1) GB_CK(cudaEventRecord(hl_event(), st));
     }
     hl_slots_scan<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs, cand, (u32)cap);
-    for (int round = 1; round <= 2; ++round) {
+    for (int round = 1; round <= (g_round2 ? 2 : 1); ++round) {
       if (round == 2) hl_slots_collect<<<scan_blocks, 256, 0, st>>>((const uint4*)slots, bmax, hs, round, cand, (u32)cap);
       if (g_time_k1 == 2 && round == 1) GB_CK(cudaEventRecord(hl_event(), st));
       hl_cand_count<CS><<<pass_blocks, KS_THREADS, 0, st>>>(kf, shift, cand, (u32)cap, tk, tc, tm, (u64)(M - 1), hs, round, cl_key, cl_j);
       if (g_time_k1 == 2 && round == 1) GB_CK(cudaEventRecord(hl_event(), st));
-      hl_decide<<<1, 1024, 0, st>>>(tk, tc, tm, M, hs, round, tie_keys, tie_min, (u32)cap);
+      hl_decide<<<1, 1024, 0, st>>>(tk, tc, tm, M, hs, round, tie_keys, tie_min, (u32)cap, g_round2 ? 1 : 0);
     }
     hl_tiebreak<<<1, HL_TB_CAP, 0, st>>>(hs, hs64, tie_keys, tie_min, pos[p], len[p], rbins, R, strbuf, stride);
     hl_flag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark, pos[p], len[p], rbins, R);
     hl_apply_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, flags, rmark, hsh[p], glue[p], len[p], tid[p], pos[p],
                                                (u32*)a[HA_EVL], (u32*)a[HA_EVR], (u32*)a[HA_EVP]);
-    if (g_incremental) hl_bump_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, hsh[p], glue[p], len[p], tid[p], powtab, P, slots, shift);
-    hl_unflag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark);
+    if (g_incremental)
+      hl_bump_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, hsh[p], glue[p], len[p], tid[p], powtab, P, slots, shift, cl_r, flags, rmark);
+    else
+      hl_unflag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark);
     hl_end<<<1, 1, 0, st>>>(hs, hs64, (u64*)a[HA_LKEY], (u32*)a[HA_LCNT], (u32*)a[HA_LR0], (u32*)a[HA_LNRES], (u32*)a[HA_LEVS],
                             (u32*)a[HA_LNK]);
     GB_LAUNCH_CK();
@@ -822,7 +829,7 @@ static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t
     case 2:
       if (ptab) hl_peer_gather_x<<<world, 1024, 0, st>>>(PP, world, rank, pctr, hs, (u64*)xall);
       hl_table_import<<<1, 1024, 0, st>>>(tk, tc, tm, (u64)(M - 1), hs, 1, xall, world, rank);
-      hl_decide<<<1, 1024, 0, st>>>(tk, tc, tm, M, hs, 1, tie_keys, tie_min, (u32)cap);
+      hl_decide<<<1, 1024, 0, st>>>(tk, tc, tm, M, hs, 1, tie_keys, tie_min, (u32)cap, 0);
       GB_CK(cudaMemsetAsync(sbuf, 0, 4 * HL_TB_CAP + (size_t)HL_TB_CAP * stride, st));
       hl_tie_strings<<<1, HL_TB_CAP, 0, st>>>(hs, tie_keys, tie_min, tie_skeys, tie_smin, pos, len, rbins, R, sbuf, stride);
       if (ptab) hl_peer_signal<<<1, 32, 0, st>>>(PP, world, rank, 2, pctr);
@@ -834,8 +841,10 @@ static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t
       hl_apply_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, flags, rmark, hsh, glue, len, tid, pos,
                                                  (u32*)a[HA_EVL], (u32*)a[HA_EVR], (u32*)a[HA_EVP]);
       if (g_incremental && ptab)
-        hl_bump_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, hsh, glue, len, tid, (const u64*)a[HA_POWTAB], (u64)a[HA_P], slots, shift);
-      hl_unflag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark);
+        hl_bump_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, hsh, glue, len, tid, (const u64*)a[HA_POWTAB], (u64)a[HA_P], slots, shift,
+                                                  cl_r, flags, rmark);
+      else
+        hl_unflag_list<<<list_blocks, 256, 0, st>>>(hs, hs64, cl_key, cl_j, cl_r, flags, rmark);
       hl_end<<<1, 1, 0, st>>>(hs, hs64, (u64*)a[HA_LKEY], (u32*)a[HA_LCNT], (u32*)a[HA_LR0], (u32*)a[HA_LNRES], (u32*)a[HA_LEVS],
                               (u32*)a[HA_LNK]);
       break;
@@ -896,4 +905,5 @@ extern "C" int gb_h_loop_k1_times(float* ms_host, int cap) {
   return n;
 }
 extern "C" int gb_h_loop_nargs(void) { return (int)HA_N; }
-extern "C" int gb_h_loop_kernels_per_step(void) { return 12; }
+// kernels per one-GPU iteration: scan, candidate pass, decide, tie-break, flag, apply, bump (+ unflag), end; + the recount
+extern "C" int gb_h_loop_kernels_per_step(void) { return 8 + (g_round2 ? 3 : 0) + (g_incremental ? 0 : 1); }

@@ -857,7 +857,11 @@ class Learner:
 
     def _hl_args(self):
         ts, sk, hl = self._ts, self.sketch, self.hl
-        a, b = ts.a, ts.b
+        # the two token buffers keep their argument positions for the life of the loop (the captured graphs are keyed by the
+        # arguments); which of them is current is the `parity` passed with every call
+        if getattr(hl, "buf0", None) is None or not ((ts.a is hl.buf0 and ts.b is hl.buf1) or (ts.a is hl.buf1 and ts.b is hl.buf0)):
+            hl.buf0, hl.buf1 = ts.a, ts.b
+        a, b = hl.buf0, hl.buf1
         P = _lib.ptr
         vals = [P(hl.hs), P(hl.hs64), P(a["hsh"]), P(b["hsh"]), P(a["glue"]), P(b["glue"]), P(a["pos"]), P(b["pos"]),
                 P(a["len"]), P(b["len"]), P(a["tid"]), P(b["tid"]), P(ts.flags), P(hl.rmark), P(ts.scratch), P(self.powtab), HASH_BASE,
@@ -894,10 +898,10 @@ class Learner:
         h[H["EVCAP"]] = self.ev_left.numel()
         hl.hs.copy_(torch.from_numpy(h.astype(np.int32)))
         hl.enq = 0
-        hl.parity = 0
         _lib.call("gb_table_clear", *self.sketch.small.ptrs())     # hl_decide leaves it cleared from then on
         self._ts.flags.zero_()      # (hl.Tmax stays the initial upper bound: same arguments -> the captured graphs are reused)
         hl.args = self._hl_args()
+        hl.parity = 0 if self._ts.a is hl.buf0 else 1
         if hl.dist is not None and getattr(hl, "_args_key", None) != tuple(hl.args):
             hl.dist.graphs = {}
         hl._args_key = tuple(hl.args)
@@ -1002,8 +1006,8 @@ class Learner:
     def _hl_call(self, nsteps, compact_after):
         hl = self.hl
         out = C.c_int(0)
-        per = 19 if (hl.dist is not None and hl.dist.peer is not None) else 12
-        _lib.call_n("gb_h_loop", nsteps * per + 4 * (nsteps // hl.period + compact_after), hl.args, hl.nargs, nsteps, hl.parity,
+        per = 17 if (hl.dist is not None and hl.dist.peer is not None) else _lib.load().gb_h_loop_kernels_per_step()
+        _lib.call_n("gb_h_loop", nsteps * per + 5 * (nsteps // hl.period + compact_after), hl.args, hl.nargs, nsteps, hl.parity,
                     hl.enq, compact_after, C.byref(out))
         hl.parity = out.value
 
@@ -1043,7 +1047,7 @@ class Learner:
                 self._ts.T = int(h[H["T"]])
                 self._ev_n = e1
                 self.n_steps += done
-            if hl.parity:
+            if self._ts.a is not (hl.buf1 if hl.parity else hl.buf0):      # ts.a = the buffer the loop left current
                 self._ts.swap()
             if int(h[H["N"]]) != int(h[H["T"]]):
                 raise RuntimeError(f"compaction left {int(h[H['N']])} entries for {int(h[H['T']])} live tokens")
