@@ -314,7 +314,7 @@ def main():
         # the timed region replays CUDA graphs (no events inside); K1 is timed in an instrumented continuation of the
         # same run: the next iterations launched kernel by kernel with CUDA events around every k_slot_count launch
         import ctypes
-        n_inst = min(256, args.steps)
+        n_inst = max(L.hl.period, min(256, args.steps))       # at least one whole period: one recount launch is observed
         T_inst = L.ts.T
         lib.gb_h_loop_time_k1(1)
         for _ in range(n_inst):
@@ -326,7 +326,9 @@ def main():
         lib.gb_h_loop_time_k1(0)
         loop_ms = [float(buf[i]) for i in range(n) if buf[i] > 0]
         nk = [e[2] for e in L.step_events[-n_inst:]]
-        loop_T = (T_inst - np.concatenate([[0], np.cumsum(nk)[:-1]])).tolist()[:len(loop_ms)]
+        # (every sync leaves the loop at the start of a period: the recounts are iterations 0, period, 2 x period, ...)
+        loop_T = (T_inst - np.concatenate([[0], np.cumsum(nk)[:-1]])).tolist()[::L.hl.period][:len(loop_ms)]
+        loop_ms = loop_ms[:len(loop_T)]
         k1_ms, k1_T = loop_ms + k1_ms, loop_T + k1_T      # + the iterations that fell back to the host path
         k1_note = (f"timed region = CUDA-graph replays (no events inside a graph); timed with CUDA events around every "
                    f"launch of the kernel in the {n_inst} iterations that follow it, launched kernel by kernel")
@@ -344,7 +346,6 @@ def main():
         c2_ms = [float(buf[i]) for i in range(n) if buf[i] > 0]
         nk = [e[2] for e in L.step_events[-n2:]]
         c2_T = (T2 - np.concatenate([[0], np.cumsum(nk)[:-1]])).tolist()[:len(c2_ms)]
-        k1_T = k1_T[::L.hl.period][:len(k1_ms)] if len(k1_ms) < len(k1_T) else k1_T     # one recount per period
     bpt = 16 if args.mode == "H" else 8
     k1_avg_ms = float(np.mean(k1_ms))
     k1_bytes = bpt * float(np.mean(k1_T))
