@@ -563,9 +563,11 @@ static cudaEvent_t hl_event() {
 
 template <bool CS> static int h_loop_part_impl(const int64_t* a, int part, int parity, cudaStream_t st, bool full);
 static bool g_round2 = true;           // in-loop second candidate round (else: such an iteration halts to the host path)
-extern "C" int gb_h_loop_round2(int enable) { g_round2 = enable != 0; return 0; }
 static bool g_incremental = true;      // slot counters: full recount once per period, upper bounds in between
-extern "C" int gb_h_loop_incremental(int enable) { g_incremental = enable != 0; return 0; }
+static std::vector<int64_t> g_graph_args;      // argument set the captured period graphs belong to (h_loop_graphs)
+// (the kernel sequence of an iteration depends on these two switches: captured graphs are dropped when they change)
+extern "C" int gb_h_loop_round2(int enable) { g_round2 = enable != 0; g_graph_args.clear(); return 0; }
+extern "C" int gb_h_loop_incremental(int enable) { g_incremental = enable != 0; g_graph_args.clear(); return 0; }
 
 template <bool CS>
 static int h_loop_impl(const int64_t* a, int nsteps, int parity, int step0, int compact_after, int* parity_out, cudaStream_t st) {
@@ -675,7 +677,6 @@ static int h_loop_impl(const int64_t* a, int nsteps, int parity, int step0, int 
 
 // CUDA graphs: one graph per buffer parity holding `period` iterations + the compaction that ends the period, captured
 // once per argument set and replayed (the loop is launch-bound otherwise: ~17 launches per ~100 us iteration)
-static std::vector<int64_t> g_graph_args;
 static cudaGraphExec_t g_graph_exec[2] = {nullptr, nullptr};
 static bool g_use_graphs = true;
 extern "C" int gb_h_loop_use_graphs(int enable) { g_use_graphs = enable != 0; return 0; }

@@ -73,6 +73,28 @@ def test_halts_fall_back_to_the_host_path(monkeypatch):
     assert a.hl.halts or a.hl.r2, "the lowered cap was expected to force second rounds / halts"
 
 
+@pytest.mark.parametrize("incremental,round2", [(0, 1), (1, 0), (0, 0)])
+def test_loop_switches(incremental, round2, monkeypatch):
+    """gb_h_loop_incremental / gb_h_loop_round2: recount every iteration instead of slot bounds kept from the merge events;
+    no in-loop second round (inconclusive iterations halt to the host path).  Same results in every combination."""
+    lib = _lib.load()
+    lib.gb_h_loop_incremental(incremental)
+    lib.gb_h_loop_round2(round2)
+    try:
+        monkeypatch.setattr(E.SlotSketch, "CAP", 2)      # two candidate slots per round: second rounds are common
+        a = learner(120, 48, 5, async_steps=True)
+        b = learner(120, 48, 5, async_steps=False, use_sketch=False)
+        for _ in range(140):                              # crosses two compaction periods
+            a.step(); b.step()
+        assert state(a) == state(b)
+        assert a.hl.r2 > 0, "the lowered cap was expected to make first rounds inconclusive"
+        if not round2:
+            assert a.hl.halts.get(2, 0) > 0               # ... and each of them went to the host path
+    finally:
+        lib.gb_h_loop_incremental(1)
+        lib.gb_h_loop_round2(1)
+
+
 def test_step_log_capacity_halt(monkeypatch):
     """a full step log halts the loop (code 7); the host re-bases it and re-enqueues the rest"""
     monkeypatch.setattr(E.Learner, "HL_LOG_CAP", 16)
