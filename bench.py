@@ -375,6 +375,7 @@ def main():
     k1_share = k1_avg_ms * args.steps * k1_per_step / ms
     roof = {"bound": "hbm", "kernel": k1_name, "resolve_rounds_1_2_fallback": sk_rounds, "device_loop": loop_info,
             "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
+            "frac_of_nominal_8TBs": achieved / 8000.0,
             "traffic": (tr["in_loop"]["dram_bytes_per_token"] * float(np.mean(k1_T))) if tr else None,
             "traffic_source": tr.get("source") if tr else None, "avg_ms": k1_avg_ms, "algorithmic_bytes_per_launch": k1_bytes,
             "bytes_per_token": bpt, "launches_per_step": k1_per_step, "share_of_step": k1_share, "timing": k1_note}
@@ -386,6 +387,7 @@ def main():
         roof = {"bound": "hbm", "kernel": "hl_cand_count<KeysHL> (exact pair counts of the candidate slots: one full pass over the "
                                           "token arrays every iteration)",
                 "device_loop": loop_info, "achieved": a2, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": a2 / peak,
+                "frac_of_nominal_8TBs": a2 / 8000.0,
                 "traffic": (t2["dram_bytes_per_token"] * float(np.mean(c2_T))) if t2 else None,
                 "traffic_source": tr.get("source") if t2 else None, "avg_ms": c2_avg, "algorithmic_bytes_per_launch": c2_bytes,
                 "bytes_per_token": bpt, "launches_per_step": 1.0, "share_of_step": c2_avg * args.steps / ms, "timing": k1_note,
@@ -397,9 +399,10 @@ def main():
     if not args.no_scale_probe and rank == 0:
         pr = k1_scale_probe(L, args.mode)
         a2 = pr["bytes_per_token"] * pr["tokens"] / (pr["ms"] * 1e-3) / 1e9
-        scale = dict(pr, bound="hbm", achieved=a2, peak=peak, unit="GB/s", frac=a2 / peak,
+        scale = dict(pr, bound="hbm", achieved=a2, peak=peak, unit="GB/s", frac=a2 / peak, frac_of_nominal_8TBs=a2 / 8000.0,
                      traffic=(tr["at_scale"]["dram_bytes_per_token"] * pr["tokens"]) if tr else None,
                      pass2_achieved=pr["bytes_per_token"] * pr["tokens"] / (pr["pass2_ms"] * 1e-3) / 1e9,
+                     pass2_frac=pr["bytes_per_token"] * pr["tokens"] / (pr["pass2_ms"] * 1e-3) / 1e9 / peak,
                      note="K1 pass 1 (k_slot_count) alone on this workload's token arrays tiled to the per-GPU shard of "
                           "BASELINE config 5 (48 M tokens > L2); pass2_* = k_cand_count (exact resolution) on the same arrays")
     if world > 1:
