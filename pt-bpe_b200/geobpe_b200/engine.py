@@ -831,11 +831,17 @@ class Learner:
         return pr
 
     def close(self):
-        """release the symmetric block of the peer-memory transport (collective: every rank calls it; a barrier makes sure
-        no peer kernel still reads this rank's block).  The learner falls back to the NCCL exchanges afterwards."""
+        """sharded runs, before `destroy_process_group()`: drop the CUDA graphs that captured NCCL collectives (the process
+        group cannot be destroyed while they exist -- it blocks) and release the symmetric block of the peer-memory
+        transport (collective: every rank calls it; a barrier makes sure no peer kernel still reads this rank's block).
+        The learner stays usable: it falls back to the NCCL exchanges afterwards."""
         self.sync()
         d = self.hl.dist if self.hl is not None else None
-        if d is None or d.peer is None:
+        if d is None:
+            return
+        torch.cuda.synchronize()
+        d.graphs = {}
+        if d.peer is None:
             return
         torch.cuda.synchronize()
         self.comm.all_reduce(torch.zeros(1, device=_dev()))

@@ -43,6 +43,8 @@ def worker(rank, world, port, q, mode):
     transport = "peer" if (L.hl is not None and L.hl.dist is not None and L.hl.dist.peer is not None) else "nccl"
     halts = dict(L.hl.halts) if L.hl is not None else {}
     q.put((rank, a, [list(p) for p in L.pop_log], [[k, v] for k, v in L.tokens.items()], segs, transport, halts))
+    L.close()           # graphs holding captured NCCL collectives / the peer-memory block go before the process group
+    del L
     dist.destroy_process_group()
 
 
