@@ -145,9 +145,9 @@ def k1_scale_probe(learner, mode, reps=20, target_tokens=48_000_000):
     if mode == "H":
         h = pad(ts.a["hsh"][:T0].repeat(rep)); g = pad(ts.a["glue"][:T0].repeat(rep)); l = pad(ts.a["len"][:T0].repeat(rep))
         l[T:] = 1
-        p1 = lambda: _lib.call("gb_slot_count_h", _lib.ptr(h), _lib.ptr(g), _lib.ptr(l), T, _lib.ptr(learner.powtab), E.HASH_BASE,
+        p1 = lambda: _lib.call("gb_slot_count_h", _lib.ptr(h), _lib.ptr(g), _lib.ptr(l), T, _lib.ptr(learner.powtab), learner.hash_base,
                                _lib.ptr(sk.slots), sk.log2ns, None, sk.variant | 8, sk.ctas)
-        p2 = lambda: _lib.call("gb_cand_count_h", _lib.ptr(h), _lib.ptr(g), _lib.ptr(l), T, _lib.ptr(learner.powtab), E.HASH_BASE,
+        p2 = lambda: _lib.call("gb_cand_count_h", _lib.ptr(h), _lib.ptr(g), _lib.ptr(l), T, _lib.ptr(learner.powtab), learner.hash_base,
                                sk.log2ns, _lib.ptr(sk.cand), sk.sout.data_ptr() + 4, sk.CAP, *sk.small.ptrs(),
                                _lib.ptr(sk.small.overflow), 1)
         bpt = 16

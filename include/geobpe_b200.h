@@ -249,6 +249,29 @@ int gb_h_loop_round2(int enable);
 int gb_h_loop_time_k1(int mode);
 int gb_h_loop_k1_times(float* ms_host, int cap);
 
+/* ---- device-driven learn loop, second design (csrc/k_hloop2.cu): the same iteration (bpe.py:1792-2166, rmsd_key None)
+ *      inside ONE persistent cooperative kernel per call, with the pair counts maintained incrementally from the merge
+ *      events the way the reference maintains _geo_dict / _priority_dict (bpe.py:1924-1950 decrements, 1992-2006 and
+ *      2077-2138 increments / re-prioritisation) instead of being recounted: the slot counters of gb_slot_count_h stay
+ *      exact (a destroyed pair decrements its slot, a created pair increments it); per "period" one streaming pass counts
+ *      the keys of the candidate slots (count >= thr_num/16 of the top slot) exactly into an open-addressing table
+ *      (key, count, example window) and lists their pairs; iterations then touch only the table, the pair list and the
+ *      winner's occurrences.  A period ends on the device when the best exact count falls below the threshold, a slot
+ *      outside the candidate set reaches it, the table / list fills or a quarter of the entries is dead (compaction).
+ *      args_host: int64 [gb_h_loop2_nargs()] in the order of the HB_* enum (state block hs u32 [gb_h_loop2_state_words()]
+ *      + hs64 u64 [16], ping-pong token arrays, flags + rmark u8, scan scratch, powtab, P, rbins, R, slot counters +
+ *      chunk maxima + candidate list + cap + candidate bitmap u32 [NS/32], table tk/tc/tr0/tnres + M, pair list,
+ *      occurrence list, JSON scratch + stride, merge-event log, per-step log, thr_num, streaming flag, CTAs per SM).
+ *      Runs until hs[STEP] has advanced by nsteps or a halt code is set; final_compact != 0 leaves the arrays dense
+ *      (len = plain residue counts) for host reads. */
+int gb_h_loop2(const int64_t* args_host, int n_args, int nsteps, int final_compact, void* stream);
+int gb_h_loop2_nargs(void);
+int gb_h_loop2_state_words(void);
+/* hsh[j] = content hash under base P of token j's symbol sequence (residue symbols sym, glue symbols glue_res + 1) --
+ * the value the merges build with (H(L) P + g) P^|R| + H(R); used to re-key a run after a detected 64-bit collision */
+int gb_rehash_tokens(const uint64_t* sym, const uint32_t* glue_res, const uint32_t* pos, const uint32_t* len, int64_t T,
+                     uint64_t P, uint64_t* hsh, void* stream);
+
 /* ---- K4/K5/K6: NeRF windows, Kabsch RMSD, medoid assignment (tokenizer.py:347-363, nerf.py:84-210,
  *      angles_and_coords.py:238-317, algo.py:8-65,170-181, bpe.py:646-657) -------------------------- */
 /* coords f64 [Q][A][3] for windows starting at residue r0[q] spanning nres residues; A = atoms kept

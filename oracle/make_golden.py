@@ -25,6 +25,7 @@ from geobpe_oracle import dump_state, _jsonable
 
 INF = float("inf")
 NUM_P = {2: 2, 3: 5, 5: 1, 6: 2, 8: 1}
+NUM_P4 = {2: 100, 3: 500, 5: 20, 6: 100, 8: 5, 9: 20, 11: 1, 12: 5, 14: 1}     # README cmd 2 (configs[3])
 
 CASES = {
     # name: dict(gen=(S, n, seed, ragged), hparams, steps, [induce=(S, n, seed)], [sorted_sets])
@@ -55,6 +56,17 @@ CASES = {
     "pdb72_m": dict(gen="pdb72", steps=int(os.environ.get("PDB72_M_STEPS", 500)), induce="pdb_heldout",
                     hp=dict(bins={1: 20}, bin_strategy="histogram", std_bonds=False, rmsd_partition_min_size=0,
                             rmsd_super_res=True, num_partitions=NUM_P, max_num_strucs=100)),
+    # BASELINE configs[0] at the hyper-parameters README cmd 1 decodes to: bins {1: 50}, max_num_strucs 500
+    "pdb72_m50": dict(gen="pdb72", steps=int(os.environ.get("PDB72_M50_STEPS", 500)), induce="pdb_heldout",
+                      hp=dict(bins={1: 50}, bin_strategy="histogram", std_bonds=False, rmsd_partition_min_size=0,
+                              rmsd_super_res=True, num_partitions=NUM_P, max_num_strucs=500)),
+    # BASELINE configs[3] ("pareto") shape: bins {1: 500}, num_p 2-100:3-500:5-20:6-100:8-5:9-20:11-1:12-5:14-1; the residue
+    # initialisation takes the k == N branch of k_medoids (algo.py:163-165: all 500 sampled residues are medoids), the
+    # README cmd 2 stops there (max_iter 0: the reference cannot merge at these settings -- rmsd_partition needs at least
+    # num_p occurrences of the popped key, bpe.py:1776 -- and induces against bpe_post_init.pkl, README.md:57)
+    "cfg4_k500": dict(gen=(100, 16, 9, True), steps=0, induce=(3, 16, 10),
+                      hp=dict(bins={1: 500}, bin_strategy="histogram", std_bonds=False, rmsd_partition_min_size=0,
+                              rmsd_super_res=True, num_partitions=NUM_P4, max_num_strucs=500)),
 }
 
 

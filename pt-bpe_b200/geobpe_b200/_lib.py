@@ -51,6 +51,10 @@ SIGNATURES = {
     "gb_rmsd_matrix": [P, I32, I32, P, P],
     "gb_h_loop": [P, I32, I32, I32, I32, I32, P, P],
     "gb_h_loop_nargs": [],
+    "gb_h_loop2": [P, I32, I32, I32, P],
+    "gb_h_loop2_nargs": [],
+    "gb_rehash_tokens": [P, P, P, P, I64, U64, P, P],
+    "gb_h_loop2_state_words": [],
     "gb_h_loop_part": [P, I32, I32, I32, P],
     "gb_h_loop_xbuf_elems": [],
     "gb_h_loop_sbuf_bytes": [I32],

@@ -11,7 +11,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(PKG))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libgeobpe_b200.so")
-SOURCES = ["k_select.cu", "k3_binning.cu", "k1_paircount.cu", "k1_slots.cu", "k_hloop.cu", "k2_merge.cu", "k45_geometry.cu"]
+SOURCES = ["k_select.cu", "k3_binning.cu", "k1_paircount.cu", "k1_slots.cu", "k_hloop.cu", "k_hloop2.cu", "k2_merge.cu", "k45_geometry.cu"]
 
 
 def nvcc_path():
@@ -30,19 +30,37 @@ def needs_build():
 
 
 def build(force=False, verbose=False):
+    """one nvcc -c per source (in parallel), then one link; objects live in a git-ignored build/ directory"""
     if not force and not needs_build():
         return LIB
-    cmd = [nvcc_path(), "-shared", "-Xcompiler", "-fPIC", "-O3", "-std=c++17", "-lineinfo",
-           "-gencode", "arch=compute_100a,code=sm_100a", "-fmad=false",
-           "-I", os.path.join(ROOT, "include"), "-I", CSRC]
+    from concurrent.futures import ThreadPoolExecutor
+    objdir = os.path.join(PKG, "build")
+    os.makedirs(objdir, exist_ok=True)
+    base = [nvcc_path(), "-Xcompiler", "-fPIC", "-O3", "-std=c++17", "-lineinfo",
+            "-gencode", "arch=compute_100a,code=sm_100a", "-fmad=false",
+            "-I", os.path.join(ROOT, "include"), "-I", CSRC]
     if verbose:
-        cmd += ["-Xptxas", "-v"]
-    cmd += [os.path.join(CSRC, s) for s in SOURCES] + ["-o", LIB]
-    r = subprocess.run(cmd, capture_output=True, text=True)
+        base += ["-Xptxas", "-v"]
+    hdr_t = max(os.path.getmtime(os.path.join(CSRC, f)) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h")))
+    hdr_t = max(hdr_t, os.path.getmtime(os.path.join(ROOT, "include", "geobpe_b200.h")))
+
+    def one(src):
+        obj = os.path.join(objdir, src.replace(".cu", ".o"))
+        path = os.path.join(CSRC, src)
+        if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(os.path.getmtime(path), hdr_t):
+            return obj, ""
+        r = subprocess.run(base + ["-c", path, "-o", obj], capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"nvcc failed on {src}:\n" + r.stdout + r.stderr)
+        return obj, r.stdout + r.stderr
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
+        res = list(ex.map(one, SOURCES))
+    r = subprocess.run([nvcc_path(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a"] + [o for o, _ in res] + ["-o", LIB],
+                       capture_output=True, text=True)
     if r.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+        raise RuntimeError("link failed:\n" + r.stdout + r.stderr)
     if verbose:
-        print(r.stdout + r.stderr)
+        print("".join(t for _, t in res))
     return LIB
 
 

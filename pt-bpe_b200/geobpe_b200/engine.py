@@ -274,6 +274,7 @@ class SlotSketch:
     construction: a key outside the listed slots has count <= its slot's count < the listed threshold."""
     CAP = 4096               # candidate slots per round (k_cand_count's shared set holds 2 * CAP)
     STREAM_BYTES = 96 << 20  # token arrays above this size are read with evict-first loads (slots stay in L2)
+    STAGE_PAIRS = 296 * 32768  # the per-CTA shared-memory stage of k_slot_count pays above this many pairs
 
     def __init__(self, n_pairs_bound, log2ns=None, variant=2, ctas_per_sm=2):
         if log2ns is None:
@@ -281,7 +282,7 @@ class SlotSketch:
             log2ns = int(os.environ.get("GEOBPE_LOG2NS", log2ns))                     # tuning knob (scripts/)
         self.log2ns = log2ns
         # the per-CTA shared-memory stage only pays when a CTA sees many more pairs than it has cache entries
-        self.variant = variant if n_pairs_bound >= 296 * 32768 else (variant & ~6)
+        self.variant = variant if n_pairs_bound >= self.STAGE_PAIRS else (variant & ~6)
         self.ctas = ctas_per_sm
         self.slots = _zeros(1 << log2ns, torch.int32)
         self.bmax = _zeros(max(1, (1 << log2ns) // 4096), torch.int32)
@@ -399,6 +400,7 @@ class Learner:
         if mode == "M" and not rmsd_super_res:
             raise NotImplementedError("medoid mode is built for rmsd_super_res=True (README setting)")
         self.mode = mode
+        self.hash_base = HASH_BASE
         self.std_bonds = std_bonds
         self.bins = dict(bins)
         self.size0 = next(iter(bins))
@@ -424,6 +426,9 @@ class Learner:
         self._pending = 0           # iterations enqueued on the device and not yet read back
         self.async_steps = async_steps and mode == "H" and use_sketch
         self.use_graphs = True
+        # device-driven loop: 2 = persistent cooperative kernel with incrementally maintained pair counts (csrc/k_hloop2.cu, one GPU),
+        # 1 = per-iteration candidate pass replayed from CUDA graphs (csrc/k_hloop.cu; the sharded loop)
+        self.loop_version = int(os.environ.get("GEOBPE_LOOP", 2 if self.comm is None else 1))
         self._quantize()
         self._ts = TokenState(self.bb.R, mode)
         R = self.bb.R
@@ -570,9 +575,13 @@ class Learner:
         maxlen = int(self.bb.lens_host.max()) if self.bb.S else 1
         if self.comm is not None:
             maxlen = int(self.comm.all_reduce(torch.tensor([maxlen], device=_dev()), "max").item())
+        self._maxlen = maxlen
+        self._make_powtab()
+
+    def _make_powtab(self):
         pw = [1]
-        for _ in range(2 * maxlen + 2):
-            pw.append(pw[-1] * HASH_BASE & M64)
+        for _ in range(2 * self._maxlen + 2):
+            pw.append(pw[-1] * self.hash_base & M64)
         self.powtab = torch.from_numpy(np.array(pw, dtype=np.uint64).view(np.int64)).to(_dev())
 
     def _h_key_dicts(self, r0s, nress):
@@ -600,14 +609,14 @@ class Learner:
         if self.mode == "H":
             def launch(tab):
                 _lib.call("gb_pair_count_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab),
-                          HASH_BASE, *tab.ptrs(), _lib.ptr(tab.overflow))
+                          self.hash_base, *tab.ptrs(), _lib.ptr(tab.overflow))
         else:
             def launch(tab):
                 _lib.call("gb_pair_count_m", ts.p("cls"), ts.p("glue"), ts.T, *tab.ptrs(), _lib.ptr(tab.overflow))
         if self.mode == "H":
             def first_pos(tab):
                 _lib.call("gb_first_positions_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab),
-                          HASH_BASE, *tab.ptrs(), _lib.ptr(tab.out4), _lib.ptr(tab.tie_keys), _lib.ptr(tab.tie_min),
+                          self.hash_base, *tab.ptrs(), _lib.ptr(tab.out4), _lib.ptr(tab.tie_keys), _lib.ptr(tab.tie_min),
                           tab.TIE_CAP)
         else:
             first_pos = None                    # medoid keys decode to (class, glue, class): no example window needed
@@ -630,7 +639,7 @@ class Learner:
                 if ev is not None:
                     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                     e0.record()
-                _lib.call("gb_slot_count_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), HASH_BASE,
+                _lib.call("gb_slot_count_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), self.hash_base,
                           slots_ptr, log2ns, None, variant | (8 * cs), ctas)
                 if ev is not None:
                     e1.record()
@@ -641,7 +650,7 @@ class Learner:
                 if ev is not None:
                     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                     e0.record()
-                _lib.call("gb_cand_count_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), HASH_BASE,
+                _lib.call("gb_cand_count_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), self.hash_base,
                           log2ns, cand_ptr, ncand_ptr, cap, *tab.ptrs(), _lib.ptr(tab.overflow), cs)
                 if ev is not None:
                     e1.record()
@@ -660,7 +669,7 @@ class Learner:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
         _lib.call("gb_pair_count_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab),
-                  HASH_BASE, *tab.ptrs(), _lib.ptr(tab.overflow))
+                  self.hash_base, *tab.ptrs(), _lib.ptr(tab.overflow))
         if e is not None:
             e1.record()
             e.append((e0, e1, ts.T))
@@ -693,7 +702,7 @@ class Learner:
         self.tokens[n] = json.loads(key_str)
         self.pop_log.append((mx, key_str))
         self._ntok, self._last_count = n + 1, mx
-        _lib.call("gb_flag_pairs_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), HASH_BASE,
+        _lib.call("gb_flag_pairs_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), self.hash_base,
                   key, _lib.ptr(ts.flags))
         if self.verify:                                # checked after the merge's single read-back (u32[3], u32[4])
             _lib.call("gb_verify_flagged_h", _lib.ptr(ts.flags), ts.T, ts.p("pos"), ts.p("len"), _lib.ptr(self.rbins),
@@ -701,7 +710,7 @@ class Learner:
         r = self._merge(key, n, None, None, bound=mx)
         if self.verify:
             if int(r[3]):
-                raise RuntimeError("64-bit content-hash collision detected (window bins differ); re-run with another HASH_BASE")
+                raise RuntimeError("64-bit content-hash collision detected (window bins differ); re-run with another hash base")
             if int(r[4]) != mx:
                 raise RuntimeError(f"flagged {int(r[4])} occurrences, histogram counted {mx}")
         self.n_steps += 1
@@ -870,7 +879,7 @@ class Learner:
         a, b = hl.buf0, hl.buf1
         P = _lib.ptr
         vals = [P(hl.hs), P(hl.hs64), P(a["hsh"]), P(b["hsh"]), P(a["glue"]), P(b["glue"]), P(a["pos"]), P(b["pos"]),
-                P(a["len"]), P(b["len"]), P(a["tid"]), P(b["tid"]), P(ts.flags), P(hl.rmark), P(ts.scratch), P(self.powtab), HASH_BASE,
+                P(a["len"]), P(b["len"]), P(a["tid"]), P(b["tid"]), P(ts.flags), P(hl.rmark), P(ts.scratch), P(self.powtab), self.hash_base,
                 P(self.rbins), self.bb.R, P(sk.slots), sk.log2ns, P(sk.bmax), P(sk.cand), sk.CAP, sk.variant, sk.ctas,
                 P(sk.small.keys), P(sk.small.cnt), P(sk.small.min), sk.small.M, P(hl.tie_keys), P(hl.tie_min),
                 P(hl.strbuf), hl.stride, P(self.ev_left), P(self.ev_right), P(self.ev_p), P(hl.log_key),
@@ -914,6 +923,8 @@ class Learner:
 
     def enqueue(self, nsteps):
         """enqueue `nsteps` merge iterations on the device; nothing is read back until sync()"""
+        if self.loop_version == 2 and self.comm is None:
+            return self._h2_enqueue(nsteps)
         if self.hl is None:
             self._hl_init()
             self._hl_push_state()
@@ -961,6 +972,8 @@ class Learner:
         if not self.async_steps:
             return
         self.sync()
+        if self.loop_version == 2 and self.comm is None:
+            return                                          # one cooperative kernel per enqueue: nothing to capture
         if self.hl is None:
             self._hl_init()
             self._hl_push_state()
@@ -1020,6 +1033,8 @@ class Learner:
     def sync(self):
         """drain the device loop: read the state block and the step log, materialise vocabulary entries / pop log;
         an iteration the device could not resolve runs once on the host path, the rest is re-enqueued"""
+        if self.hl is not None and getattr(self.hl, "v2", False):
+            return self._h2_sync()
         while self._pending:
             hl, H = self.hl, self.HS
             self._hl_flush(hl.lazy)
@@ -1063,7 +1078,7 @@ class Learner:
             rest = want - done
             if halt in (3, 5, 8, 9):
                 raise RuntimeError({9: "a peer rank did not signal within 20 s (peer-memory transport of the sharded loop)",
-                                    3: "64-bit content-hash collision detected (window bins differ); re-run with another HASH_BASE",
+                                    3: "64-bit content-hash collision detected (window bins differ); re-run with another hash base",
                                     5: "merge-event log overflow",
                                     8: "flagged occurrences differ from the histogram count"}[halt])
             if halt == 6:
@@ -1079,6 +1094,210 @@ class Learner:
             self._hl_push_state()
             if rest > 0:
                 self.enqueue(rest)
+
+    # ---- device-driven loop, second design (csrc/k_hloop2.cu): one persistent cooperative kernel per enqueue --------
+    H2 = dict(T=0, STEP=1, HALT=2, EVN=3, N=4, NTOK=5, LOGCAP=6, EVCAP=7, TARGET=8, PAR=9, PERIOD_OK=10, THR=11, THR_REQ=12,
+              C1=13, NCAND=14, NCL=15, CLCAP=16, NOCC=17, M1=18, NT=19, P1=20, WIN_SLOT=21, WIN_R0=22, WIN_NRES=23, WIN_CNT=24,
+              MISMATCH=25, NEWT=26, OVF=27, ERR=28, HALT_STEP=29, NTMAX=30, CMPT=31, FRESH=32, ND=33, NZ=34, MPREV=35,
+              ST_PERIODS=36, ST_CROSS=37, ST_INCONCL=38, ST_COMPACT=39, ST_R2=40, ST_FULL=41, ST_LOOPS=42, PERIOD_LEN=43)
+    H2_TIMES = ("period_start", "decide", "flag", "deaths", "apply", "births", "compaction", "candidate_pass")
+    H2_HALT_NAMES = {**HALT_NAMES, 10: "internal", 11: "guard"}
+    H2_TABLE_LOG2 = 15
+
+    def _h2_init(self):
+        ts = self._ts
+        lib = _lib.load()
+        maxwin = int(self.bb.lens_host.max()) if self.bb.S else 2
+        if self.sketch is None:
+            self.sketch = SlotSketch(ts.T)
+        sk = self.sketch
+        hl = types.SimpleNamespace(v2=True, dist=None)
+        assert lib.gb_h_loop2_state_words() == 64
+        hl.hs = _zeros(64, torch.int32)
+        hl.hs64 = _zeros(16, torch.int64)
+        hl.stride = ((39 * maxwin + 200) + 127) // 128 * 128
+        hl.strbuf = _zeros(self.HL_TB_CAP * hl.stride, torch.uint8)
+        hl.log_cap = self.HL_LOG_CAP
+        hl.log_key = _empty(hl.log_cap, torch.int64)
+        hl.log = {k: _empty(hl.log_cap, torch.int32) for k in ("cnt", "r0", "nres", "evstart", "nk")}
+        hl.cbit = _zeros((1 << sk.log2ns) // 32, torch.int32)
+        hl.M = 1 << int(os.environ.get("GEOBPE_H2_TABLE_LOG2", self.H2_TABLE_LOG2))
+        hl.rmark = _zeros(ts.cap, torch.uint8)
+        hl.cl_key = _empty(ts.cap, torch.int64)
+        hl.cl_j = _empty(ts.cap, torch.int32)
+        hl.occ_j = _empty(ts.cap, torch.int32)
+        hl.occ_r = _empty(ts.cap, torch.int32)
+        hl.nargs = lib.gb_h_loop2_nargs()
+        hl.thr_num = int(os.environ.get("GEOBPE_H2_THR16", 14))
+        hl.ctas = int(os.environ.get("GEOBPE_H2_CTAS", 2))
+        hl.period = 64                 # (reported by bench.py; periods end on the device when the threshold is crossed)
+        hl.lazy = 0
+        hl.slots_valid = False
+        hl.buf0 = hl.buf1 = None
+        hl.halts, hl.r2, hl.steps, hl.ntmax = {}, 0, 0, 0
+        hl.stats = dict(periods=0, crossings=0, inconclusive=0, compactions=0, second_rounds=0, launches=0)
+        hl.times_ns = {k: 0 for k in self.H2_TIMES}
+        self._raw = []
+        self._ntok = len(self._tokens)
+        self._last_count = self._pop_log[-1][0] if self._pop_log else 0
+        self.hl = hl
+        self._h2_table(hl.M)
+
+    def _h2_table(self, M):
+        hl = self.hl
+        hl.M = M
+        hl.tk = _empty(M, torch.int64)
+        hl.tc = _zeros(M, torch.int32)
+        hl.tr0 = _zeros(M, torch.int32)
+        hl.tnres = _zeros(M, torch.int32)
+
+    def _h2_args(self):
+        ts, sk, hl = self._ts, self.sketch, self.hl
+        if hl.buf0 is None or not ((ts.a is hl.buf0 and ts.b is hl.buf1) or (ts.a is hl.buf1 and ts.b is hl.buf0)):
+            hl.buf0, hl.buf1 = ts.a, ts.b
+        a, b = hl.buf0, hl.buf1
+        P = _lib.ptr
+        vals = [P(hl.hs), P(hl.hs64), P(a["hsh"]), P(b["hsh"]), P(a["glue"]), P(b["glue"]), P(a["pos"]), P(b["pos"]),
+                P(a["len"]), P(b["len"]), P(a["tid"]), P(b["tid"]), P(ts.flags), P(hl.rmark), P(ts.scratch), P(self.powtab), self.hash_base,
+                P(self.rbins), self.bb.R, P(sk.slots), sk.log2ns, P(sk.bmax), P(sk.cand), sk.CAP, P(hl.cbit),
+                P(hl.tk), P(hl.tc), P(hl.tr0), P(hl.tnres), hl.M, P(hl.cl_key), P(hl.cl_j), P(hl.occ_j), P(hl.occ_r),
+                P(hl.strbuf), hl.stride, P(self.ev_left), P(self.ev_right), P(self.ev_p), P(hl.log_key),
+                P(hl.log["cnt"]), P(hl.log["r0"]), P(hl.log["nres"]), P(hl.log["evstart"]), P(hl.log["nk"]),
+                hl.thr_num, 1 if 16 * ts.cap > SlotSketch.STREAM_BYTES else 0, hl.ctas]
+        assert len(vals) == hl.nargs, (len(vals), hl.nargs)
+        return (C.c_int64 * len(vals))(*[v if v < (1 << 63) else v - (1 << 64) for v in vals])
+
+    def _h2_push_state(self):
+        """host state -> device state block (first use, after every read-back); the slot counters are recounted when a
+        host-side iteration changed the token arrays behind the loop's back"""
+        hl, H, ts = self.hl, self.H2, self._ts
+        hl.args = self._h2_args()
+        h = np.zeros(64, dtype=np.int64)
+        h[H["T"]] = h[H["N"]] = ts.T
+        h[H["EVN"]] = self._ev_n
+        h[H["NTOK"]] = self._ntok
+        h[H["LOGCAP"]] = hl.log_cap
+        h[H["EVCAP"]] = self.ev_left.numel()
+        h[H["CLCAP"]] = hl.cl_key.numel()
+        h[H["PAR"]] = 0 if ts.a is hl.buf0 else 1
+        h[H["MPREV"]] = self._last_count
+        hl.hs.copy_(torch.from_numpy(h.astype(np.int32)))
+        hl.hs64.zero_()
+        if not hl.slots_valid:
+            ts.flags.zero_()             # (the host path leaves its occurrence flags behind)
+            hl.rmark.zero_()
+            sk = self.sketch
+            cs = 1 if 16 * ts.T > SlotSketch.STREAM_BYTES else 0
+            sk.slots.zero_()
+            ev = self.k1_events
+            if ev is not None:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+            _lib.call("gb_slot_count_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), self.hash_base,
+                      _lib.ptr(sk.slots), sk.log2ns, None, sk.variant | (8 * cs), sk.ctas)
+            if ev is not None:
+                e1.record()
+                ev.append((e0, e1, ts.T))
+            hl.slots_valid = True
+
+    def _h2_enqueue(self, nsteps):
+        if self.hl is None:
+            self._h2_init()
+            self._h2_push_state()
+        hl = self.hl
+        hl.lazy += nsteps
+        self._pending += nsteps
+        self.n_steps += nsteps
+        if hl.lazy >= 256:
+            self._h2_flush(0)
+
+    def _h2_flush(self, final_compact):
+        hl = self.hl
+        if hl.lazy > 0 or final_compact:
+            _lib.call_n("gb_h_loop2", 2, hl.args, hl.nargs, hl.lazy, final_compact)
+            hl.stats["launches"] += 1
+            hl.lazy = 0
+
+    def _h2_sync(self):
+        """drain the loop: one read of the state block + step log; halts run one iteration on the host path and re-enter"""
+        while self._pending:
+            hl, H = self.hl, self.H2
+            self._h2_flush(1)
+            h = hl.hs.cpu().numpy().astype(np.int64) & 0xFFFFFFFF            # the one blocking read
+            tm = hl.hs64.cpu().numpy()
+            done, halt = int(h[H["STEP"]]), int(h[H["HALT"]])
+            want = self._pending
+            self._pending = 0
+            self.n_steps -= want
+            for k, name in enumerate(self.H2_TIMES):
+                hl.times_ns[name] += int(tm[2 + k])
+            for name, word in (("periods", "ST_PERIODS"), ("inconclusive", "ST_INCONCL"), ("compactions", "ST_COMPACT"),
+                               ("second_rounds", "ST_R2"), ("crossings", "ST_CROSS")):
+                hl.stats[name] += int(h[H[word]])
+            if done:
+                keys = hl.log_key[:done].cpu().numpy().astype(np.uint64).tolist()
+                lg = {k: _u32(v[:done]) for k, v in hl.log.items()}
+                self._raw.append((lg["cnt"], lg["r0"], lg["nres"]))      # formatted lazily (_materialise_log)
+                for s in range(done):
+                    self._step_events.append((self._ntok + s, int(lg["evstart"][s]), int(lg["nk"][s]), keys[s]))
+                self._ntok += done
+                self._last_count = int(lg["cnt"][-1])
+                e0, e1 = self._ev_n, int(h[H["EVN"]])
+                if e1 > e0:        # merge events are appended in arbitrary order: sort each iteration's range by position
+                    el, er = _u32(self.ev_left[e0:e1]), _u32(self.ev_right[e0:e1])
+                    seg = np.repeat(np.arange(done), lg["nk"])
+                    order = np.lexsort((el, seg))
+                    self.ev_left[e0:e1] = torch.from_numpy(el[order].astype(np.int32)).to(_dev())
+                    self.ev_right[e0:e1] = torch.from_numpy(er[order].astype(np.int32)).to(_dev())
+                self._ts.T = int(h[H["T"]])
+                self._ev_n = e1
+                self.n_steps += done
+            if self._ts.a is not (hl.buf1 if int(h[H["PAR"]]) else hl.buf0):      # ts.a = the buffer the loop left current
+                self._ts.swap()
+            if int(h[H["N"]]) != int(h[H["T"]]):
+                raise RuntimeError(f"compaction left {int(h[H['N']])} entries for {int(h[H['T']])} live tokens")
+            hl.steps += done
+            hl.r2 += int(h[H["ST_R2"]])
+            hl.ntmax = max(hl.ntmax, int(h[H["NTMAX"]]))
+            rest = want - done
+            if halt in (5, 8, 9, 10):
+                raise RuntimeError({5: "merge-event log overflow", 8: "flagged occurrences differ from the exact pair count",
+                                    9: "peer timeout", 10: "incremental pair counts became inconsistent"}[halt])
+            if halt == 6:
+                raise IndexError("no adjacent pairs left (the reference's peekitem(0) raises here too)")
+            if halt:
+                hl.halts[halt] = hl.halts.get(halt, 0) + 1
+                if halt == 3:          # two windows with different bins share a 64-bit content hash: re-key everything
+                    self.rehash()
+                elif halt == 4:        # the exact table was too small for this period's candidate keys
+                    self._h2_table(hl.M * 4)
+                elif halt in (1, 2):   # ties / candidates: this one iteration on the host path
+                    self._step_h_host()
+                    hl.slots_valid = False
+                    rest -= 1
+            self._h2_push_state()
+            if rest > 0:
+                self._h2_enqueue(rest)
+
+    def rehash(self, base=None):
+        """give every live token its content hash under another base (two different windows shared a 64-bit hash: the
+        popped key's occurrences did not all hold the same bins).  Dense arrays only (call after a read-back)."""
+        if self.mode != "H":
+            return
+        if self._pending:
+            self.sync()
+        if base is None:
+            base = ((self.hash_base * 0x9E3779B97F4A7C15 + 0x7F4A7C15) & M64) | 1
+        self.hash_base = base
+        self._make_powtab()
+        ts = self._ts
+        _lib.call("gb_rehash_tokens", _lib.ptr(self.sym), _lib.ptr(self.glue_res), ts.p("pos"), ts.p("len"), ts.T, base, ts.p("hsh"))
+        self.table.distinct = 0
+        if self.hl is not None and getattr(self.hl, "v2", False):
+            self.hl.slots_valid = False
+            self._h2_push_state()
+        elif self.hl is not None:
+            self._hl_push_state()
 
     NS = 1 << 20      # direct-mapped slot counters exchanged per iteration (4 MB allreduce)
 
@@ -1127,7 +1346,7 @@ class Learner:
             tab.tie_min[:len(ch)] = -1
             tab.out4.copy_(torch.tensor([mx, len(ch), 0, 0], dtype=torch.int32))
             _lib.call("gb_first_positions_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab),
-                      HASH_BASE, *tab.ptrs(), _lib.ptr(tab.out4), _lib.ptr(tab.tie_keys), _lib.ptr(tab.tie_min), tab.TIE_CAP)
+                      self.hash_base, *tab.ptrs(), _lib.ptr(tab.out4), _lib.ptr(tab.tie_keys), _lib.ptr(tab.tie_min), tab.TIE_CAP)
             mp = _u32(tab.tie_min[:len(ch)])
             have = [(k, int(m)) for k, m in zip(ch, mp.tolist()) if m != 0xFFFFFFFF]
             if have:
@@ -1145,7 +1364,7 @@ class Learner:
         self.tokens[n] = json.loads(key_str)
         self.pop_log.append((mx, key_str))
         self._ntok, self._last_count = n + 1, mx
-        _lib.call("gb_flag_pairs_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), HASH_BASE,
+        _lib.call("gb_flag_pairs_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(self.powtab), self.hash_base,
                   key, _lib.ptr(ts.flags))
         if self.verify and key in local:
             nocc = ts.select(1, ts.idx)

@@ -45,7 +45,7 @@ def test_h_mode_vs_reference_golden(name):
     run_learn(load_golden(name))
 
 
-@pytest.mark.parametrize("name", ["m20", "m6_sub", "pdb72_m"])
+@pytest.mark.parametrize("name", ["m20", "m6_sub", "pdb72_m", "pdb72_m50", "cfg4_k500"])
 def test_m_mode_vs_reference_golden(name):
     run_learn(load_golden(name))
 
@@ -80,7 +80,7 @@ def test_m_mode_vs_oracle_fresh():
     assert norm(O.dump_state(bpe, max_angles=30)) == norm(O.dump_state(ora, max_angles=30))
 
 
-@pytest.mark.parametrize("name", ["m20", "m6_sub", "pdb72_m"])
+@pytest.mark.parametrize("name", ["m20", "m6_sub", "pdb72_m", "pdb72_m50", "cfg4_k500"])
 def test_induce_vs_reference_golden(name):
     """BPE.tokenize on training and held-out backbones: segmentation, L trace, ids and the set of backbones the
     reference rejects (glue angle outside the learned bins) must match the reference run."""

@@ -11,7 +11,7 @@ from geobpe_b200 import synthetic
 from golden_util import load_golden, case_inputs, case_hparams, induce_inputs, norm
 
 H_CASES = ["h4", "h6_ragged", "h5_uniform", "h5_cover", "pdb72_h"]   # pdb72_*: BASELINE configs[0] inputs (real PDBs)
-M_CASES = ["m20", "m6_sub", "m20_sorted", "m6_sub_sorted", "pdb72_m"]
+M_CASES = ["m20", "m6_sub", "m20_sorted", "m6_sub_sorted", "pdb72_m", "pdb72_m50", "cfg4_k500"]
 
 
 def run_oracle(g):
