@@ -52,6 +52,20 @@ static __device__ int hl_json_key(char* p, const u16* __restrict__ rbins, i64 R,
   for (int k = o; k < end; ++k) p[k] = 0;
   return o;
 }
+// the same string written by lane 0 of a warp after all 32 lanes have gathered the window's bins into shared memory
+// (sb: u16 [6][cap], cap >= nres): the serial formatter then reads shared memory instead of ~6 nres dependent global loads
+__device__ __forceinline__ int hl_json_key_warp(char* p, const u16* __restrict__ rbins, i64 R, u32 r0, u32 nres, u16* sb, u32 cap) {
+  const unsigned lane = threadIdx.x & 31;
+  for (u32 e = lane; e < 6u * nres; e += 32u) {
+    const u32 slot = e / nres, k = e - slot * nres;
+    sb[slot * cap + k] = __ldg(rbins + (i64)(3u + slot) * R + r0 + k);
+  }
+  __syncwarp();
+  int o = 0;
+  if (lane == 0) o = hl_json_key(p, sb - 3 * (i64)cap, (i64)cap, 0u, nres);
+  __syncwarp();
+  return __shfl_sync(0xffffffffu, o, 0);
+}
 // warp-cooperative strcmp of two zero-padded, 128-byte aligned strings: true when a < b
 __device__ __forceinline__ bool hl_less(const char* a, const char* b, int la, int lb) {
   const unsigned lane = threadIdx.x & 31;

@@ -43,6 +43,7 @@ enum {
   H2_C1, H2_NCAND, H2_NCL, H2_CLCAP, H2_NOCC, H2_M1, H2_NT, H2_P1, H2_WIN_SLOT, H2_WIN_R0, H2_WIN_NRES, H2_WIN_CNT,
   H2_MISMATCH, H2_NEWT, H2_OVF, H2_ERR, H2_HALT_STEP, H2_NTMAX, H2_CMPT, H2_FRESH, H2_ND, H2_NZ, H2_MPREV,
   H2_ST_PERIODS, H2_ST_CROSS, H2_ST_INCONCL, H2_ST_COMPACT, H2_ST_R2, H2_ST_FULL, H2_ST_LOOPS, H2_PERIOD_LEN,
+  H2_ST_MAXNCL, H2_ST_MAXND, H2_ST_MAXNCAND, H2_ST_TIES,
   H2_WORDS = 64
 };
 // hs64: [0] popped key, [1] spare, [2..] nanoseconds accumulated per phase (block 0's view)
@@ -54,7 +55,7 @@ struct H2Args {
   u8* flags; u8* rmark; u32* scratch;
   const u64* powtab; u64 P; const u16* rbins; i64 R;
   u32* slots; int log2ns; u32* bmax; u32* cand; u32 cap; u32* cbit;
-  u64* tk; u32* tc; u32* tr0; u32* tnres; i64 M;
+  u64* tk; u32* tc; u32* tr0; u32* tnres; u32* tlist; i64 M;
   u64* cl_key; u32* cl_j;
   u32* occ_j; u32* occ_r;
   char* strbuf; int stride;
@@ -85,7 +86,9 @@ __device__ __forceinline__ i64 h2_table_add(const H2Args& a, u64 key, u32 r0, u3
       prev = atomicCAS(&a.tk[s], (u64)GB_EMPTY_KEY, key);
       if (prev == GB_EMPTY_KEY) {             // this thread inserted the key: it also provides the example window
         a.tr0[s] = r0; a.tnres[s] = nres;
-        if ((u64)atomicAdd(&a.hs[H2_ND], 1u) * 2u + 2u > (u64)a.M) a.hs[H2_OVF] = 1u;
+        const u32 id = atomicAdd(&a.hs[H2_ND], 1u);       // dense list of the occupied slots (the argmax scans it)
+        if ((i64)id < a.M) a.tlist[id] = (u32)s;
+        if ((u64)id * 2u + 2u > (u64)a.M) a.hs[H2_OVF] = 1u;
         prev = key;
       }
     }
@@ -404,6 +407,8 @@ __device__ void h2_period_start(const H2Args& a, cg::grid_group& grid, unsigned 
     else if (hs[H2_NCL] > hs[H2_CLCAP]) h2_halt(hs, H2_HALT_CAND);
     hs[H2_THR] = thr; hs[H2_THR_REQ] = 0; hs[H2_PERIOD_OK] = 1; hs[H2_FRESH] = 1; hs[H2_PERIOD_LEN] = 0;
     if (req) hs[H2_ST_R2] += 1u;
+    hs[H2_ST_MAXNCL] = max(hs[H2_ST_MAXNCL], hs[H2_NCL]); hs[H2_ST_MAXND] = max(hs[H2_ST_MAXND], hs[H2_ND]);
+    hs[H2_ST_MAXNCAND] = max(hs[H2_ST_MAXNCAND], hs[H2_NCAND]);
     const u64 t2 = h2_now();
     a.hs64[H2_TM_PS] += t2 - tm0; a.hs64[H2_TM_CAND] += t2 - tm1;
   }
@@ -411,6 +416,7 @@ __device__ void h2_period_start(const H2Args& a, cg::grid_group& grid, unsigned 
 }
 
 // ---- P1: exact argmax over the table + the reference's tie-break (block 0) -------------------------------------------
+#define H2_JS_CAP 64             // residues per window staged in shared memory for the JSON formatter (longer: global loads)
 __device__ void h2_decide(const H2Args& a, unsigned char* smem) {
   if (blockIdx.x != 0) return;
   u32* hs = a.hs;
@@ -419,21 +425,25 @@ __device__ void h2_decide(const H2Args& a, unsigned char* smem) {
   u32* s_tslot = s_red + 64;                                    // [H2_TB_CAP]
   int* s_best = reinterpret_cast<int*>(s_tslot + H2_TB_CAP);    // [H2_TB_CAP]
   int* s_len = s_best + H2_TB_CAP;                              // [H2_TB_CAP]
-  u32* s_fail = reinterpret_cast<u32*>(s_len + H2_TB_CAP);      // [1]
+  u32* s_fail = reinterpret_cast<u32*>(s_len + H2_TB_CAP);      // [1] (+ padding)
+  u16* s_bins = reinterpret_cast<u16*>(s_fail + 8);             // [H2_THREADS / 32][6][H2_JS_CAP]
   if (threadIdx.x == 0) { *s_nt = 0; *s_fail = 0; }
+  const u32 nd = min(h2_ld(hs + H2_ND), (u32)a.M);
   u32 mx = 0;
-  for (i64 i = threadIdx.x; i < a.M; i += H2_THREADS) mx = max(mx, a.tc[i]);
+  for (u32 i = threadIdx.x; i < nd; i += H2_THREADS) mx = max(mx, a.tc[a.tlist[i]]);
   for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
   if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = mx;
   __syncthreads();
   mx = 0;
   for (int w = 0; w < H2_THREADS / 32; ++w) mx = max(mx, s_red[w]);
   if (mx)
-    for (i64 i = threadIdx.x; i < a.M; i += H2_THREADS)
-      if (a.tc[i] == mx) {
+    for (u32 i = threadIdx.x; i < nd; i += H2_THREADS) {
+      const u32 sl = a.tlist[i];
+      if (a.tc[sl] == mx) {
         const u32 k = atomicAdd(s_nt, 1u);
-        if (k < H2_TB_CAP) s_tslot[k] = (u32)i;
+        if (k < H2_TB_CAP) s_tslot[k] = sl;
       }
+    }
   __syncthreads();
   const u32 nt = *s_nt, thr = hs[H2_THR];
   if (mx == 0 || mx < thr) {               // a key outside the table could reach mx: new period
@@ -449,26 +459,30 @@ __device__ void h2_decide(const H2Args& a, unsigned char* smem) {
     if (threadIdx.x == 0) { hs[H2_NTMAX] = max(hs[H2_NTMAX], nt); hs[H2_P1] = 100u + H2_HALT_TIES; }
     return;
   }
-  const u32 i = threadIdx.x;
+  const unsigned warp = threadIdx.x >> 5, nw = H2_THREADS >> 5, lane = threadIdx.x & 31;
   if (nt > 1) {
-    if (i < nt) {
+    // one warp per tied key: bins gathered into shared memory by all lanes, json.dumps(key, sort_keys=True) written by lane 0
+    for (u32 i = warp; i < nt; i += nw) {
       const u32 sl = s_tslot[i];
       const u32 nres = a.tnres[sl];
-      if (39 * (int)nres + 200 > a.stride) { *s_fail = 1u; s_len[i] = 0; }
-      else s_len[i] = hl_json_key(a.strbuf + (size_t)i * a.stride, a.rbins, a.R, a.tr0[sl], nres);
+      int len = 0;
+      if (39 * (int)nres + 200 > a.stride) { if (lane == 0) *s_fail = 1u; }
+      else if (nres <= H2_JS_CAP) len = hl_json_key_warp(a.strbuf + (size_t)i * a.stride, a.rbins, a.R, a.tr0[sl], nres, s_bins + warp * 6 * H2_JS_CAP, H2_JS_CAP);
+      else { if (lane == 0) len = hl_json_key(a.strbuf + (size_t)i * a.stride, a.rbins, a.R, a.tr0[sl], nres); len = __shfl_sync(0xffffffffu, len, 0); }
+      if (lane == 0) s_len[i] = len;
     }
-    if (i < H2_TB_CAP) s_best[i] = (int)i;
+    if (threadIdx.x < H2_TB_CAP) s_best[threadIdx.x] = (int)threadIdx.x;
     __syncthreads();
     if (*s_fail) {
       if (threadIdx.x == 0) hs[H2_P1] = 100u + H2_HALT_TIES;
       return;
     }
-    const unsigned warp = threadIdx.x >> 5, nw = H2_THREADS >> 5;
+    __threadfence_block();
     for (u32 s = 1; s < nt; s <<= 1) {
       for (u32 x = warp * 2 * s; x + s < nt; x += nw * 2 * s) {
         const int ia = s_best[x], ib = s_best[x + s];
         const bool b_less = hl_less(a.strbuf + (size_t)ib * a.stride, a.strbuf + (size_t)ia * a.stride, s_len[ib], s_len[ia]);
-        if ((threadIdx.x & 31) == 0 && b_less) s_best[x] = ib;
+        if (lane == 0 && b_less) s_best[x] = ib;
       }
       __syncthreads();
     }
@@ -478,53 +492,27 @@ __device__ void h2_decide(const H2Args& a, unsigned char* smem) {
     a.hs64[0] = a.tk[sl];
     hs[H2_WIN_SLOT] = sl; hs[H2_WIN_R0] = a.tr0[sl]; hs[H2_WIN_NRES] = a.tnres[sl]; hs[H2_WIN_CNT] = mx;
     hs[H2_M1] = mx; hs[H2_NT] = nt; hs[H2_NTMAX] = max(hs[H2_NTMAX], nt);
+    if (nt > 1) hs[H2_ST_TIES] += 1u;
     hs[H2_FRESH] = 0; hs[H2_P1] = 0;
     hs[H2_NOCC] = 0; hs[H2_MISMATCH] = 0; hs[H2_NEWT] = 0;
   }
 }
 
-// ---- P2: the winner's occurrences from the pair list (+ exact window check) -----------------------------------------
-__device__ void h2_flag(const H2Args& a, const H2Tok& t, u64 win, u32 ref_r0, u32 nres) {
+// ---- P2: the winner's occurrences from the pair list --------------------------------------------------------------
+__device__ void h2_flag(const H2Args& a, const H2Tok& t, u64 win) {
   u32* hs = a.hs;
   const u32 ncl = min(h2_ld(hs + H2_NCL), h2_ld(hs + H2_CLCAP));
-  const unsigned lane = threadIdx.x & 31;
-  for (u32 base = blockIdx.x * H2_THREADS; base < ncl; base += gridDim.x * H2_THREADS) {
-    const u32 i = base + threadIdx.x;
-    u32 j = 0, r = 0;
-    bool valid = false;
-    if (i < ncl && a.cl_key[i] == win) {
-      j = a.cl_j[i];
-      const u32 l = t.ls[j];
-      const u32 gj = t.glue[j];
-      if (l != 0u && !(gj & GB_LAST_FLAG)) {             // the entry is stale when the pair no longer exists
-        r = j + 1u + (l >> 16);
-        valid = gb_key_h(t.hsh[j], gj, t.hsh[r], a.P, __ldg(a.powtab + (2u * (t.ls[r] & 0xFFFFu) - 1u))) == win;
-      }
-    }
-    unsigned bal = __ballot_sync(0xffffffffu, valid);
-    bool mybad = false;
-    while (bal) {                                        // warp-cooperative bin-by-bin check of every occurrence's window
-      const int src = __ffs(bal) - 1;
-      bal &= bal - 1;
-      const u32 jj = __shfl_sync(0xffffffffu, j, src), rr = __shfl_sync(0xffffffffu, r, src);
-      const u32 r0 = t.pos[jj];
-      bool bad = ((t.ls[jj] & 0xFFFFu) + (t.ls[rr] & 0xFFFFu)) != nres;
-      if (!bad && r0 != ref_r0) {
-        for (u32 e = lane; e < 6u * nres; e += 32u) {
-          const u32 slot = 3u + e / nres, k = e % nres;
-          if (slot >= 6u && k == nres - 1u) continue;      // glue of the last residue lies outside the window
-          bad |= __ldg(a.rbins + (i64)slot * a.R + r0 + k) != __ldg(a.rbins + (i64)slot * a.R + ref_r0 + k);
-        }
-      }
-      bad = __any_sync(0xffffffffu, bad);
-      if ((int)lane == src) mybad = bad;
-    }
-    if (valid) {
-      const u32 q = atomicAdd(&hs[H2_NOCC], 1u);
-      a.occ_j[q] = j; a.occ_r[q] = r;
-      a.flags[j] = 1; a.rmark[r] = 1;
-      if (mybad) atomicAdd(&hs[H2_MISMATCH], 1u);
-    }
+  for (u32 i = blockIdx.x * H2_THREADS + threadIdx.x; i < ncl; i += gridDim.x * H2_THREADS) {
+    if (a.cl_key[i] != win) continue;
+    const u32 j = a.cl_j[i];
+    const u32 l = t.ls[j];
+    const u32 gj = t.glue[j];
+    if (l == 0u || (gj & GB_LAST_FLAG)) continue;           // the entry is stale when the pair no longer exists
+    const u32 r = j + 1u + (l >> 16);
+    if (gb_key_h(t.hsh[j], gj, t.hsh[r], a.P, __ldg(a.powtab + (2u * (t.ls[r] & 0xFFFFu) - 1u))) != win) continue;
+    const u32 q = atomicAdd(&hs[H2_NOCC], 1u);
+    a.occ_j[q] = j; a.occ_r[q] = r;
+    a.flags[j] = 1; a.rmark[r] = 1;
   }
 }
 __device__ void h2_unflag(const H2Args& a, u32 nocc) {
@@ -533,10 +521,25 @@ __device__ void h2_unflag(const H2Args& a, u32 nocc) {
   }
 }
 
-// ---- P3: overlap rule + the pairs the merges destroy ------------------------------------------------------------------
-__device__ void h2_deaths(const H2Args& a, const H2Tok& t, u32 nocc) {
-  for (u32 i = blockIdx.x * H2_THREADS + threadIdx.x; i < nocc; i += gridDim.x * H2_THREADS) {
-    const u32 j0 = a.occ_j[i];
+// ---- P3: exact window check, overlap rule, the pairs the merges destroy (one warp per occurrence) -------------------
+__device__ void h2_deaths(const H2Args& a, const H2Tok& t, u32 nocc, u32 ref_r0, u32 nres) {
+  const unsigned lane = threadIdx.x & 31;
+  const u32 wid = (blockIdx.x * H2_THREADS + threadIdx.x) >> 5, nw = gridDim.x * (H2_THREADS / 32);
+  for (u32 i = wid; i < nocc; i += nw) {
+    const u32 j0 = a.occ_j[i], r0tok = a.occ_r[i];
+    // every occurrence's window must hold the example window's bins (a 64-bit content-hash collision is detected here)
+    const u32 r0 = t.pos[j0];
+    bool bad = ((t.ls[j0] & 0xFFFFu) + (t.ls[r0tok] & 0xFFFFu)) != nres;
+    if (!bad && r0 != ref_r0) {
+      for (u32 e = lane; e < 6u * nres; e += 32u) {
+        const u32 slot = 3u + e / nres, k = e % nres;
+        if (slot >= 6u && k == nres - 1u) continue;        // glue of the last residue lies outside the window
+        bad |= __ldg(a.rbins + (i64)slot * a.R + r0 + k) != __ldg(a.rbins + (i64)slot * a.R + ref_r0 + k);
+      }
+    }
+    bad = __any_sync(0xffffffffu, bad);
+    if (lane != 0) continue;
+    if (bad) atomicAdd(&a.hs[H2_MISMATCH], 1u);
     if (a.rmark[j0]) continue;                 // not a run head: the pair to its left is an occurrence too
     const u32 q = h2_prev_live(t, j0);
     if (q != 0xFFFFFFFFu && !(t.glue[q] & GB_LAST_FLAG)) h2_death(a, h2_pair_key(a, t, q, j0));
@@ -648,11 +651,11 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
     const u64 win = *reinterpret_cast<volatile u64*>(&a.hs64[0]);
     const u32 ref_r0 = h2_ld(hs + H2_WIN_R0), nres = h2_ld(hs + H2_WIN_NRES), cnt = h2_ld(hs + H2_WIN_CNT);
     const u32 new_tid = h2_ld(hs + H2_NTOK), ev0 = h2_ld(hs + H2_EVN), thr = h2_ld(hs + H2_THR);
-    h2_flag(a, t, win, ref_r0, nres);
+    h2_flag(a, t, win);
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P2] += n - tm; tm = n; }
-    const u32 nocc = h2_ld(hs + H2_NOCC), mism = h2_ld(hs + H2_MISMATCH);
-    const u32 bad = mism ? H2_HALT_COLLISION : (nocc != cnt ? H2_HALT_COUNT : ((u64)ev0 + nocc > (u64)h2_ld(hs + H2_EVCAP) ? H2_HALT_EVLOG : 0u));
+    const u32 nocc = h2_ld(hs + H2_NOCC);
+    const u32 bad = nocc != cnt ? H2_HALT_COUNT : ((u64)ev0 + nocc > (u64)h2_ld(hs + H2_EVCAP) ? H2_HALT_EVLOG : 0u);
     if (bad) {                                       // nothing has been modified yet: remove the marks, stop
       h2_unflag(a, nocc);
       grid.sync();
@@ -660,20 +663,23 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
       grid.sync();
       continue;
     }
-    h2_deaths(a, t, nocc);
+    h2_deaths(a, t, nocc, ref_r0, nres);
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P3] += n - tm; tm = n; }
+    const u32 bad3 = h2_ld(hs + H2_MISMATCH) ? H2_HALT_COLLISION : (h2_ld(hs + H2_ERR) ? H2_HALT_INTERNAL : 0u);
+    if (bad3) {                                      // the token arrays are untouched (counters are rebuilt by the host)
+      h2_unflag(a, nocc);
+      grid.sync();
+      if (t0) h2_halt(hs, bad3);
+      grid.sync();
+      continue;
+    }
     h2_apply(a, t, nocc, win, new_tid, ev0);
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P4] += n - tm; tm = n; }
     h2_births_end(a, t, nocc, win, new_tid, thr, step, ev0);
     grid.sync();
-    if (t0) {
-      const u64 n = h2_now(); a.hs64[H2_TM_P5] += n - tm;
-      if (hs[H2_ERR]) h2_halt(hs, H2_HALT_INTERNAL);
-      hs[H2_ST_LOOPS] += 1u;
-    }
-    grid.sync();
+    if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P5] += n - tm; hs[H2_ST_LOOPS] += 1u; }
   }
   if (final_compact) {          // the host reads dense arrays (ls = plain residue counts)
     const u32 N = h2_ld(hs + H2_N), T = h2_ld(hs + H2_T);
@@ -688,7 +694,7 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
 // ---- host entry ------------------------------------------------------------------------------------------------------
 enum { HB_HS = 0, HB_HS64, HB_HSH0, HB_HSH1, HB_GLUE0, HB_GLUE1, HB_POS0, HB_POS1, HB_LEN0, HB_LEN1, HB_TID0, HB_TID1,
        HB_FLAGS, HB_RMARK, HB_SCRATCH, HB_POWTAB, HB_P, HB_RBINS, HB_R, HB_SLOTS, HB_LOG2NS, HB_BMAX, HB_CAND, HB_CAP, HB_CBIT,
-       HB_TK, HB_TC, HB_TR0, HB_TNRES, HB_M, HB_CLKEY, HB_CLJ, HB_OCCJ, HB_OCCR, HB_STRBUF, HB_STRIDE, HB_EVL, HB_EVR, HB_EVP,
+       HB_TK, HB_TC, HB_TR0, HB_TNRES, HB_TLIST, HB_M, HB_CLKEY, HB_CLJ, HB_OCCJ, HB_OCCR, HB_STRBUF, HB_STRIDE, HB_EVL, HB_EVR, HB_EVP,
        HB_LKEY, HB_LCNT, HB_LR0, HB_LNRES, HB_LEVS, HB_LNK, HB_THRNUM, HB_STREAMING, HB_CTAS, HB_N };
 
 __global__ void h2_set_target(u32* hs, u32 nsteps) { hs[H2_TARGET] = hs[H2_STEP] + nsteps; }
@@ -713,7 +719,7 @@ extern "C" int gb_h_loop2(const int64_t* b, int n_args, int nsteps, int final_co
   a.powtab = (const u64*)b[HB_POWTAB]; a.P = (u64)b[HB_P]; a.rbins = (const u16*)b[HB_RBINS]; a.R = b[HB_R];
   a.slots = (u32*)b[HB_SLOTS]; a.log2ns = (int)b[HB_LOG2NS]; a.bmax = (u32*)b[HB_BMAX]; a.cand = (u32*)b[HB_CAND];
   a.cap = (u32)b[HB_CAP]; a.cbit = (u32*)b[HB_CBIT];
-  a.tk = (u64*)b[HB_TK]; a.tc = (u32*)b[HB_TC]; a.tr0 = (u32*)b[HB_TR0]; a.tnres = (u32*)b[HB_TNRES]; a.M = b[HB_M];
+  a.tk = (u64*)b[HB_TK]; a.tc = (u32*)b[HB_TC]; a.tr0 = (u32*)b[HB_TR0]; a.tnres = (u32*)b[HB_TNRES]; a.tlist = (u32*)b[HB_TLIST]; a.M = b[HB_M];
   a.cl_key = (u64*)b[HB_CLKEY]; a.cl_j = (u32*)b[HB_CLJ]; a.occ_j = (u32*)b[HB_OCCJ]; a.occ_r = (u32*)b[HB_OCCR];
   a.strbuf = (char*)b[HB_STRBUF]; a.stride = (int)b[HB_STRIDE];
   a.ev_left = (u32*)b[HB_EVL]; a.ev_right = (u32*)b[HB_EVR]; a.ev_p = (u32*)b[HB_EVP];
@@ -722,7 +728,7 @@ extern "C" int gb_h_loop2(const int64_t* b, int n_args, int nsteps, int final_co
   a.thr_num = (u32)b[HB_THRNUM];
   a.max_loops = (u32)(4 * nsteps + 64);
   if (a.log2ns < 12 || a.log2ns > 30 || a.M < 1024 || (a.M & (a.M - 1)) || a.cap < 1 || a.cap > KC_SET / 2 || (a.stride & 127) ||
-      a.thr_num < 1 || a.thr_num > 16 || !a.hs || !a.hs64 || !a.cbit || !a.occ_j) {
+      a.thr_num < 1 || a.thr_num > 16 || !a.hs || !a.hs64 || !a.cbit || !a.occ_j || !a.tlist) {
     gb_set_error("gb_h_loop2: bad arguments (log2ns %d, M %lld, cap %u, stride %d, thr_num %u)", a.log2ns, (long long)a.M, a.cap,
                  a.stride, a.thr_num);
     return -2;

@@ -1099,7 +1099,8 @@ class Learner:
     H2 = dict(T=0, STEP=1, HALT=2, EVN=3, N=4, NTOK=5, LOGCAP=6, EVCAP=7, TARGET=8, PAR=9, PERIOD_OK=10, THR=11, THR_REQ=12,
               C1=13, NCAND=14, NCL=15, CLCAP=16, NOCC=17, M1=18, NT=19, P1=20, WIN_SLOT=21, WIN_R0=22, WIN_NRES=23, WIN_CNT=24,
               MISMATCH=25, NEWT=26, OVF=27, ERR=28, HALT_STEP=29, NTMAX=30, CMPT=31, FRESH=32, ND=33, NZ=34, MPREV=35,
-              ST_PERIODS=36, ST_CROSS=37, ST_INCONCL=38, ST_COMPACT=39, ST_R2=40, ST_FULL=41, ST_LOOPS=42, PERIOD_LEN=43)
+              ST_PERIODS=36, ST_CROSS=37, ST_INCONCL=38, ST_COMPACT=39, ST_R2=40, ST_FULL=41, ST_LOOPS=42, PERIOD_LEN=43,
+              ST_MAXNCL=44, ST_MAXND=45, ST_MAXNCAND=46, ST_TIES=47)
     H2_TIMES = ("period_start", "decide", "flag", "deaths", "apply", "births", "compaction", "candidate_pass")
     H2_HALT_NAMES = {**HALT_NAMES, 10: "internal", 11: "guard"}
     H2_TABLE_LOG2 = 15
@@ -1150,6 +1151,7 @@ class Learner:
         hl.tc = _zeros(M, torch.int32)
         hl.tr0 = _zeros(M, torch.int32)
         hl.tnres = _zeros(M, torch.int32)
+        hl.tlist = _zeros(M, torch.int32)
 
     def _h2_args(self):
         ts, sk, hl = self._ts, self.sketch, self.hl
@@ -1160,7 +1162,7 @@ class Learner:
         vals = [P(hl.hs), P(hl.hs64), P(a["hsh"]), P(b["hsh"]), P(a["glue"]), P(b["glue"]), P(a["pos"]), P(b["pos"]),
                 P(a["len"]), P(b["len"]), P(a["tid"]), P(b["tid"]), P(ts.flags), P(hl.rmark), P(ts.scratch), P(self.powtab), self.hash_base,
                 P(self.rbins), self.bb.R, P(sk.slots), sk.log2ns, P(sk.bmax), P(sk.cand), sk.CAP, P(hl.cbit),
-                P(hl.tk), P(hl.tc), P(hl.tr0), P(hl.tnres), hl.M, P(hl.cl_key), P(hl.cl_j), P(hl.occ_j), P(hl.occ_r),
+                P(hl.tk), P(hl.tc), P(hl.tr0), P(hl.tnres), P(hl.tlist), hl.M, P(hl.cl_key), P(hl.cl_j), P(hl.occ_j), P(hl.occ_r),
                 P(hl.strbuf), hl.stride, P(self.ev_left), P(self.ev_right), P(self.ev_p), P(hl.log_key),
                 P(hl.log["cnt"]), P(hl.log["r0"]), P(hl.log["nres"]), P(hl.log["evstart"]), P(hl.log["nk"]),
                 hl.thr_num, 1 if 16 * ts.cap > SlotSketch.STREAM_BYTES else 0, hl.ctas]
@@ -1232,8 +1234,10 @@ class Learner:
             for k, name in enumerate(self.H2_TIMES):
                 hl.times_ns[name] += int(tm[2 + k])
             for name, word in (("periods", "ST_PERIODS"), ("inconclusive", "ST_INCONCL"), ("compactions", "ST_COMPACT"),
-                               ("second_rounds", "ST_R2"), ("crossings", "ST_CROSS")):
-                hl.stats[name] += int(h[H[word]])
+                               ("second_rounds", "ST_R2"), ("crossings", "ST_CROSS"), ("tied_iterations", "ST_TIES")):
+                hl.stats[name] = hl.stats.get(name, 0) + int(h[H[word]])
+            for name, word in (("max_pair_list", "ST_MAXNCL"), ("max_table_keys", "ST_MAXND"), ("max_candidate_slots", "ST_MAXNCAND")):
+                hl.stats[name] = max(hl.stats.get(name, 0), int(h[H[word]]))
             if done:
                 keys = hl.log_key[:done].cpu().numpy().astype(np.uint64).tolist()
                 lg = {k: _u32(v[:done]) for k, v in hl.log.items()}
