@@ -13,10 +13,37 @@ from .synthetic import from_structures
 INF = float("inf")
 
 
-class Tokenizer:
-    """Per-backbone view (tokenizer.py:18-477).  State lives in HBM; Python objects are materialised on access."""
+def _window_coords(vals, init, n, index, length):
+    """Tokenizer.compute_coords (tokenizer.py:347-363) on the device: the window is rounded out to whole residues, rebuilt
+    by K4 (gb_window_coords: first residue placed from N:CA / CA:C / tau, then NeRF), and sliced back to length + 1 atoms.
+    vals: float64 [9, n] in COLUMNS order; init: (N:CA, CA:C, tau) of residue 0 (Tokenizer._init_*)."""
+    import torch
+    length = min(length, 3 * n - 1 - index)
+    start = 3 * (index // 3)
+    end = 3 * (((index + length - 1) + 1) // 3) + 1
+    off_start, off_end = index - start, end - (index + length - 1)
+    r0, nres = start // 3, (end - start + 2) // 3
+    mini = E.Backbones(np.ascontiguousarray(vals, dtype=np.float64), np.array([0, n], dtype=np.int64))
+    out = E._empty(3 * nres * 3, torch.float64)
+    r0_dev = torch.full((1,), r0, dtype=torch.int32, device=out.device)
+    E._lib.call("gb_window_coords", E._lib.ptr(mini.vals), n, n, E._lib.ptr(mini.bb), E._lib.ptr(mini.offsets),
+                E._lib.ptr(r0_dev), 1, nres, 3 * nres, None, None, float(init[0]), float(init[1]), float(init[2]), None, None, 0,
+                E._lib.ptr(out))
+    coords = out.view(3 * nres, 3).cpu().numpy()
+    return coords[off_start:len(coords) - off_end]
 
-    def __init__(self, structure=None, bpe=None, index=None):
+
+class Tokenizer:
+    """Per-backbone view (tokenizer.py:18-477).  Attached to a BPE, its state lives in HBM and Python objects are
+    materialised on access; built from a structure dict alone (Tokenizer.init_structure, BPE.recover_structure,
+    key_coords) it is a plain host object with the same accessors."""
+    BOND_TYPES = E.BOND_TYPES
+    ATOM_TYPES = ["N", "CA", "C"]
+    BOND_ANGLES = E.BOND_ANGLES
+    DIHEDRAL_ANGLES = E.DIHEDRAL_ANGLES
+    BOND_LENGTHS = E.BOND_LENGTHS
+
+    def __init__(self, structure=None, bpe=None, index=None, compute_sec_structs=False):
         self._bpe, self._i = bpe, index
         self._structure = structure
         if structure is not None:
@@ -24,13 +51,27 @@ class Tokenizer:
             self.n = len(df)
             self.fname = structure.get("fname")
             self.aa = structure.get("aa")
+            self.beta_coords = structure.get("c_beta")
         self._cache_step = None
+
+    # fixed per-backbone labels (tokenizer.py:48-51)
+    @property
+    def bond_labels(self):
+        return sum([[0, 1, 2] for _ in range(self.n - 1)] + [[0, 1]], [])
+
+    @property
+    def atom_labels(self):
+        return np.tile([0, 1, 2], self.n)
+
+    @property
+    def edges(self):
+        return [[j, j + 1, 0] for j in range(1, 3 * self.n)]
 
     # -- pickling: materialise, drop the device-backed owner (ref_tokenizers={t}.pkl, {idx}.pkl, bpe_iter={t}.pkl) ---
     def __getstate__(self):
         d = dict(self.__dict__)
         if d.get("_bpe") is not None and getattr(d["_bpe"], "_learner", None) is not None:
-            d["_mat"] = self._state()
+            d["_mat"] = dict(self._state(), orig=self._orig())      # (the reference pickles _angles_and_dists_orig too)
         d["_bpe"] = None
         d["_cache_step"] = None
         return d
@@ -38,19 +79,49 @@ class Tokenizer:
     # -- materialisation ------------------------------------------------------------------------------
     def _state(self):
         b = self._bpe
+        if getattr(self, "_local", False):
+            return self._mat                           # edited through set_token_geo / bond_to_token: a host object now
         if b is None and getattr(self, "_mat", None) is not None:
             return self._mat                           # unpickled: frozen snapshot
         if b is None or b._learner is None:
-            raise RuntimeError("Tokenizer is not attached to an initialised BPE")
+            if self._structure is None:
+                raise RuntimeError("Tokenizer is not attached to an initialised BPE")
+            df = self._structure["angles"]             # stand-alone: the structure's own DataFrame (tokenizer.py:24-31)
+            cur = {c: [float(x) for x in df[c]] for c in E.COLUMNS}
+            self._mat = {"bond_to_token": None, "cur": cur, "orig": {c: list(v) for c, v in cur.items()},
+                         "init": [E.INIT_N_CA, E.INIT_CA_C, E.INIT_TAU]}
+            self._local = True
+            return self._mat
         key = (id(b._learner), b._learner.n_steps, len(b._learner.pop_log))
         if self._cache_step != key:
             self._mat = b._materialise(self._i)
             self._cache_step = key
         return self._mat
 
+    def _detach(self):
+        """first write through the reference's setters: keep a private host copy from here on"""
+        st = self._state()
+        if not getattr(self, "_local", False):
+            self._mat = {"bond_to_token": st["bond_to_token"], "cur": {c: list(v) for c, v in st["cur"].items()},
+                         "orig": self._orig(), "init": list(st["init"])}
+            self._local = True
+        return self._mat
+
+    def _orig(self):
+        st = self._state()
+        if "orig" in st:
+            return st["orig"]
+        b = self._bpe
+        a, e = int(b._offsets[self._i]), int(b._offsets[self._i + 1])
+        return {c: [float(x) for x in b._vals[E.COL[c], a:e]] for c in E.COLUMNS}
+
     @property
     def bond_to_token(self):
         return self._state()["bond_to_token"]
+
+    @bond_to_token.setter
+    def bond_to_token(self, new_value):                # tokenizer.py:69-71: a fresh hierarchy over the given leaves
+        self._detach()["bond_to_token"] = TokenHierarchy(self, new_value)
 
     @property
     def token_pos(self):
@@ -86,13 +157,112 @@ class Tokenizer:
 
     _angles_and_dists = angles_and_dists
 
-    def _dihedral_angle(self, idx):
-        return self.cur[E.DIHEDRAL_ANGLES[idx % 3]][(idx + 1) // 3]
+    @property
+    def angles_and_dists_orig(self):
+        import pandas as pd
+        o = self._orig()
+        return pd.DataFrame({c: pd.Series(o[c], dtype=object) for c in E.COLUMNS})
 
-    def _bond_angle(self, idx):
+    _angles_and_dists_orig = angles_and_dists_orig
+
+    # -- scalar accessors (tokenizer.py:130-167) ---------------------------------------------------------------------
+    def _src(self, orig):
+        return self._orig() if orig else self.cur
+
+    def _bond_length(self, idx, orig=False):
+        if idx == 0:
+            return self._init_n_ca
+        if idx == 1:
+            return self._init_ca_c
+        return self._src(orig)[E.BOND_TYPES[idx % 3]][(idx - 2) // 3]
+
+    def _bond_angle(self, idx, orig=False):
         if idx == 0:
             return self._init_bond_angle
-        return self.cur[E.BOND_ANGLES[idx % 3]][(idx - 1) // 3]
+        return self._src(orig)[E.BOND_ANGLES[idx % 3]][(idx - 1) // 3]
+
+    def _dihedral_angle(self, idx, orig=False):
+        return self._src(orig)[E.DIHEDRAL_ANGLES[idx % 3]][(idx + 1) // 3]
+
+    def _set_bond_length(self, idx, value):
+        st = self._detach()
+        if idx < 2:
+            st["init"][idx] = value
+        else:
+            st["cur"][E.BOND_TYPES[idx % 3]][(idx - 2) // 3] = value
+
+    def _set_bond_angle(self, idx, value):
+        st = self._detach()
+        if idx == 0:
+            st["init"][2] = value
+        else:
+            st["cur"][E.BOND_ANGLES[idx % 3]][(idx - 1) // 3] = value
+
+    def _set_dihedral_angle(self, idx, value):
+        self._detach()["cur"][E.DIHEDRAL_ANGLES[idx % 3]][(idx + 1) // 3] = value
+
+    # -- window geometry (tokenizer.py:169-202, 253-286) ---------------------------------------------------------------
+    def token_geo(self, idx, l, orig=False):
+        """geometry of bonds idx .. idx+l-1: l bond lengths, l-1 bond angles, l-2 dihedrals, keyed by type"""
+        if idx + l - 1 > 3 * self.n - 1:
+            raise ValueError(f"idx+l cannot exceed {3 * self.n - 1}")
+        ans = {}
+        for j in range(idx, idx + l):
+            ans.setdefault(E.BOND_TYPES[j % 3], []).append(self._bond_length(j, orig=orig))
+        for j in range(idx, idx + l - 1):
+            ans.setdefault(E.BOND_ANGLES[j % 3], []).append(self._bond_angle(j, orig=orig))
+        for j in range(idx, idx + l - 2):
+            ans.setdefault(E.DIHEDRAL_ANGLES[j % 3], []).append(self._dihedral_angle(j, orig=orig))
+        return ans
+
+    def set_token_geo(self, idx, l, vals):
+        """inverse of token_geo: every list of `vals` must be consumed exactly"""
+        it = {k: iter(v) for k, v in vals.items()}
+        used = {k: 0 for k in vals}
+
+        def take(k):
+            used[k] += 1
+            return next(it[k])
+        for j in range(idx, idx + l):
+            self._set_bond_length(j, take(E.BOND_TYPES[j % 3]))
+        for j in range(idx, idx + l - 1):
+            self._set_bond_angle(j, take(E.BOND_ANGLES[j % 3]))
+        for j in range(idx, idx + l - 2):
+            self._set_dihedral_angle(j, take(E.DIHEDRAL_ANGLES[j % 3]))
+        assert all(used[k] == len(vals[k]) for k in vals)
+
+    @staticmethod
+    def num_bonds(geo):                                # tokenizer.py:303-305
+        return len(geo.get("N:CA", [])) + len(geo.get("CA:C", [])) + len(geo.get("0C:1N", []))
+
+    @staticmethod
+    def init_structure(n):                             # tokenizer.py:394-417: a blank n-residue structure
+        import pandas as pd
+        cols = {c: [0.0 if c in E.BOND_TYPES else np.nan for _ in range(n)] for c in E.COLUMNS}
+        return {"angles": pd.DataFrame(cols), "coords": None, "c_beta": None,
+                "full_idxes": sum([[i, i, i] for i in range(1, n + 1)], []), "full_coords": None, "side_chain": None,
+                "aa": None, "fname": None}
+
+    @staticmethod
+    def key_coords(key):
+        """tokenizer.py:204-230: coordinates of a vocabulary geometry placed in a blank backbone (length + 1 atoms)"""
+        length = Tokenizer.num_bonds(key)
+        cnt = lambda names: sorted((len(key.get(x, [])), x) for x in names)
+        bt, ba, da = cnt(E.BOND_TYPES), cnt(E.BOND_ANGLES), cnt(E.DIHEDRAL_ANGLES)
+        if bt[2][0] > bt[1][0]:
+            index = E.BOND_TYPES.index(bt[2][1])
+        elif ba[2][0] > ba[1][0]:
+            index = E.BOND_ANGLES.index(ba[2][1])
+        elif da[2][0] > da[1][0]:
+            index = E.DIHEDRAL_ANGLES.index(da[2][1])
+        else:
+            raise AssertionError("key does not determine its starting bond type (tokenizer.py:218-219)")
+        start = 3 * (index // 3)
+        end = 3 * (((index + length - 1) + 1) // 3) + 1
+        off_start = index - start
+        t = Tokenizer(Tokenizer.init_structure((end - start + 2) // 3))
+        t.set_token_geo(off_start, length, key)
+        return t.compute_coords()[off_start:off_start + length + 1]
 
     def tokenize(self):                               # tokenizer.py:379-392
         out = []
@@ -105,8 +275,11 @@ class Tokenizer:
                 out.append(("BOND_ANGLE", E.BOND_ANGLES[(b - 1) % 3], self._bond_angle(b - 1)))
         return out
 
-    def compute_coords(self, index=0, length=INF, orig=False):   # tokenizer.py:347-363 (whole-residue windows)
-        return self._bpe._compute_coords(self._i, index, length, orig)
+    def compute_coords(self, index=0, length=INF, orig=False):   # tokenizer.py:347-363
+        st = self._state()
+        src = self._orig() if orig else st["cur"]
+        vals = np.array([src[c] for c in E.COLUMNS], dtype=np.float64)
+        return _window_coords(vals, st["init"], self.n, index, length)
 
     def visualize(self, *a, **k):
         return None
@@ -221,26 +394,6 @@ class _View:
             self._ev_cache = (n, E._u32(L.ev_left[:n]), E._u32(L.ev_right[:n]), E._u32(L.ev_p[:n]))
         return self._ev_cache[1:]
 
-    def _compute_coords(self, i, index, length, orig):
-        if index != 0 or length != INF:
-            raise NotImplementedError("host-side compute_coords mirrors the whole-chain call only")
-        L = self._learner
-        t = self.tokenizers[i]
-        st = t._state()
-        n = t.n
-        vals = np.array([st["cur"][c] for c in E.COLUMNS], dtype=np.float64)
-        if orig:
-            vals = self._vals[:, int(L.bb.offsets_host[i]):int(L.bb.offsets_host[i + 1])].copy()
-        import torch
-        mini = E.Backbones(vals, np.array([0, n], dtype=np.int64))
-        out = E._empty(3 * n * 3, torch.float64)
-        r0 = torch.zeros(1, dtype=torch.int32, device=out.device)
-        f3 = st["init"]
-        E._lib.call("gb_window_coords", E._lib.ptr(mini.vals), n, n, E._lib.ptr(mini.bb), E._lib.ptr(mini.offsets),
-                    E._lib.ptr(r0), 1, n, 3 * n, None, None, float(f3[0]), float(f3[1]), float(f3[2]), None, None, 0,
-                    E._lib.ptr(out))
-        return out.view(3 * n, 3).cpu().numpy()
-
 
 class BPE(_View):
     def __init__(self, structures, bins, bin_strategy="histogram", save_dir=None, compute_sec_structs=False,
@@ -330,6 +483,11 @@ class BPE(_View):
         if self.std_bonds:
             for i in range(3):
                 self._thresholds[E.BOND_TYPES[i]] = [(E.BOND_LENGTHS[i], E.BOND_LENGTHS[i])]
+        import torch
+        self._bin_centers, self._bin_weights = ThresholdDict(), ThresholdDict()       # bpe.py:871-872
+        for size in L.th.thresholds:
+            self._bin_centers[size] = {k: torch.tensor(v, dtype=torch.float32).mean(axis=-1) for k, v in L.th.thresholds[size].items()}
+            self._bin_weights[size] = {k: torch.tensor(v, dtype=torch.float32) / sum(v) for k, v in L.th.bin_counts[size].items()}
         self._tokens = L.tokens
         if self._mode == "M":
             self._sphere_dict = L.sphere_dict
@@ -378,6 +536,91 @@ class BPE(_View):
     @property
     def vocab_size(self):
         return len(self._tokens) + self.cum_bin_count()
+
+    def capacity(self, tokenizer=False):
+        """bpe.py:885-902: bits to store the vocabulary geometries (4-byte floats) + with `tokenizer` the token streams at
+        uniform entropy (log2 |V| per motif, log2 bins per glue angle)"""
+        total = 0
+        for token in self._tokens.values():
+            n = Tokenizer.num_bonds(token)
+            total += 4 * (n + n - 1 + n - 2) * 8
+        if tokenizer:
+            mbits, bbits = np.log2(len(self._tokens)), np.log2(self.bins[1])
+            for m in self._motif_counts():
+                total += mbits * m
+                total += 3 * (m - 1) * bbits
+        return total
+
+    def _motif_counts(self):
+        """motifs per backbone ((len(t.tokenize()) + 3) // 4 in the reference): from the device token arrays when attached"""
+        if self._learner is not None and len(self.tokenizers) == self._learner.bb.S:
+            pos = self._token_arrays()[0]
+            return np.diff(np.searchsorted(pos, self._learner.bb.offsets_host)).tolist()
+        return [len(t.bond_to_token) for t in self.tokenizers]
+
+    def dequantize(self, quantized):
+        """bpe.py:959-983: ids -> ("MOTIF", token id) / ("DIHEDRAL" | "BOND_ANGLE", type, bin centre)"""
+        cum, num_vocab = self.cum_bin_count(), self.vocab_size
+        keys = list(self._tokens)
+        out = []
+        for i, q in enumerate(quantized):
+            if q < num_vocab - cum:
+                if q > len(keys):
+                    raise ValueError(f"pos {i} > vocab range=(0, {len(keys)})")
+                out.append(("MOTIF", keys[q]))
+                continue
+            c, token = q - (num_vocab - cum), None
+            for k, v in self._thresholds[1].items():
+                if self.res_init and k not in ["omega", "phi", "C:1N:1CA"]:
+                    continue
+                if c < len(v):
+                    s0, e0 = v[c]
+                    token = ("DIHEDRAL" if k in E.DIHEDRAL_ANGLES else "BOND_ANGLE", k, (s0 + e0) / 2)
+                    break
+                c -= len(v)
+            if token is None:
+                raise ValueError(f"pos {i} > vocab_size={num_vocab}")
+            out.append(token)
+        return out
+
+    def recover(self, tokenized):
+        """bpe.py:986-1002: token stream -> per-type value lists (motif geometries concatenated with the glue values)"""
+        repl = {}
+        for token in tokenized:
+            if token[0] == "MOTIF":
+                key_dict = self._tokens[token[1]]
+                while isinstance(key_dict, str):
+                    key_dict = json.loads(key_dict)
+                for k in key_dict:
+                    repl.setdefault(k, []).extend(key_dict[k])
+            else:
+                repl.setdefault(token[1], []).append(token[2])
+        return repl
+
+    init_structure = staticmethod(Tokenizer.init_structure)
+
+    def recover_structure(self, repl, tokenized):
+        """bpe.py:1029-1051: a stand-alone Tokenizer rebuilt from recovered value lists + the motif sequence"""
+        n = len(repl["N:CA"])
+        t_new = Tokenizer(self.init_structure(n))
+        cur = t_new._detach()["cur"]
+        cur["N:CA"][:n - 1] = repl["N:CA"][1:]
+        cur["CA:C"][:n - 1] = repl["CA:C"][1:]
+        cur["0C:1N"][:n - 1] = repl["0C:1N"]
+        cur["phi"][1:] = repl["phi"]
+        cur["psi"][:n - 1] = repl["psi"]
+        cur["omega"][:n - 1] = repl["omega"]
+        cur["tau"][:n - 1] = repl["tau"][1:]
+        cur["CA:C:1N"][:n - 1] = repl["CA:C:1N"]
+        cur["C:1N:1CA"][:n - 1] = repl["C:1N:1CA"]
+        t_new.bond_to_token = {}
+        at = 0
+        for key, *rest in tokenized:
+            if key == "MOTIF":
+                nb = Tokenizer.num_bonds(self._tokens[rest[0]])
+                t_new.bond_to_token[at] = (at, rest[0], nb)
+                at += nb
+        return t_new
 
     def quantize(self, tokenized):
         if isinstance(tokenized, Tokenizer):

@@ -47,7 +47,8 @@ enum {
   H2_WORDS = 64
 };
 // hs64: [0] popped key, [1] spare, [2..] nanoseconds accumulated per phase (block 0's view)
-enum { H2_TM_PS = 2, H2_TM_P1, H2_TM_P2, H2_TM_P3, H2_TM_P4, H2_TM_P5, H2_TM_CMP, H2_TM_CAND, H2_W64 = 16 };
+enum { H2_TM_PS = 2, H2_TM_P1, H2_TM_P2, H2_TM_P3, H2_TM_P4, H2_TM_P5, H2_TM_CMP, H2_TM_CAND,
+       H2_TW_P2 /* block 0's own work (before the barrier) */, H2_TW_P3, H2_TW_P4, H2_TW_P5, H2_W64 = 16 };
 
 struct H2Args {
   u32* hs; u64* hs64;
@@ -58,7 +59,7 @@ struct H2Args {
   u64* tk; u32* tc; u32* tr0; u32* tnres; u32* tlist; i64 M;
   u64* cl_key; u32* cl_j;
   u32* occ_j; u32* occ_r;
-  char* strbuf; int stride;
+  char* strbuf; int stride; const u16* rank;      // rank u16 [2][1024]: order of the element strings "<v>," / "<v>]"
   u32* ev_left; u32* ev_right; u32* ev_p;
   u64* log_key; u32* log_cnt; u32* log_r0; u32* log_nres; u32* log_evs; u32* log_nk;
   u32 thr_num;                    // candidate threshold = thr_num / 16 of the top slot count
@@ -416,7 +417,7 @@ __device__ void h2_period_start(const H2Args& a, cg::grid_group& grid, unsigned 
 }
 
 // ---- P1: exact argmax over the table + the reference's tie-break (block 0) -------------------------------------------
-#define H2_JS_CAP 64             // residues per window staged in shared memory for the JSON formatter (longer: global loads)
+#define H2_CODE_BYTES 32768      // shared memory for the tied keys' rank sequences (larger sets go through global memory)
 __device__ void h2_decide(const H2Args& a, unsigned char* smem) {
   if (blockIdx.x != 0) return;
   u32* hs = a.hs;
@@ -426,7 +427,7 @@ __device__ void h2_decide(const H2Args& a, unsigned char* smem) {
   int* s_best = reinterpret_cast<int*>(s_tslot + H2_TB_CAP);    // [H2_TB_CAP]
   int* s_len = s_best + H2_TB_CAP;                              // [H2_TB_CAP]
   u32* s_fail = reinterpret_cast<u32*>(s_len + H2_TB_CAP);      // [1] (+ padding)
-  u16* s_bins = reinterpret_cast<u16*>(s_fail + 8);             // [H2_THREADS / 32][6][H2_JS_CAP]
+  u16* s_codes = reinterpret_cast<u16*>(s_fail + 8);            // [H2_CODE_BYTES / 2] rank sequences of the tied keys
   if (threadIdx.x == 0) { *s_nt = 0; *s_fail = 0; }
   const u32 nd = min(h2_ld(hs + H2_ND), (u32)a.M);
   u32 mx = 0;
@@ -461,27 +462,71 @@ __device__ void h2_decide(const H2Args& a, unsigned char* smem) {
   }
   const unsigned warp = threadIdx.x >> 5, nw = H2_THREADS >> 5, lane = threadIdx.x & 31;
   if (nt > 1) {
-    // one warp per tied key: bins gathered into shared memory by all lanes, json.dumps(key, sort_keys=True) written by lane 0
+    // The reference pops min((-count, json.dumps(key, sort_keys=True))).  For pair windows (nres >= 2) that string is
+    //   {"0C:1N": [0 x m], "C:1N:1CA": [..nres-1], "CA:C": [0 x nres], "CA:C:1N": [..m], "N:CA": [0 x nres], "omega": [..nres-1],
+    //    "phi": [..nres-1], "psi": [..m], "tau": [..nres]}           (m = nres - 1 when the window ends its backbone)
+    // i.e. nine lists with fixed headers.  Each list element prints as "<v>, " or "<v>]": these element strings form a
+    // prefix-free set, so the byte order of two key strings equals the lexicographic order of their sequences of element
+    // ranks (a.rank: position of "<v>," / "<v>]" among all element strings in byte order).  One warp writes a key's rank
+    // sequence in parallel; the tournament compares 32 ranks per step.
+    int my_len = 0;
+    for (u32 i = threadIdx.x; i < nt; i += H2_THREADS) {
+      const u32 sl = s_tslot[i];
+      const u32 nres = a.tnres[sl], r0 = a.tr0[sl];
+      const u32 m = (__ldg(a.rbins + 4 * a.R + r0 + nres - 1) == GB_NOBIN) ? nres - 1 : nres;
+      s_len[i] = (int)(3u * m + 6u * nres - 3u);
+      s_best[i] = (int)m;                             // (borrowed until the tournament starts)
+      my_len = max(my_len, s_len[i]);
+    }
+    for (int o = 16; o; o >>= 1) my_len = max(my_len, __shfl_xor_sync(0xffffffffu, my_len, o));
+    __syncthreads();
+    if (lane == 0) s_red[warp] = (u32)my_len;
+    __syncthreads();
+    u32 lmax = 0;
+    for (int w = 0; w < (int)nw; ++w) lmax = max(lmax, s_red[w]);
+    const u32 cstride = (lmax + 31u) & ~31u;          // ranks per key, padded to whole warp steps
+    u16* cb = s_codes;
+    if ((size_t)nt * cstride * sizeof(u16) > H2_CODE_BYTES) {
+      cb = reinterpret_cast<u16*>(a.strbuf);
+      if ((size_t)nt * cstride * sizeof(u16) > (size_t)H2_TB_CAP * a.stride) {
+        if (threadIdx.x == 0) hs[H2_P1] = 100u + H2_HALT_TIES;
+        return;
+      }
+    }
     for (u32 i = warp; i < nt; i += nw) {
       const u32 sl = s_tslot[i];
-      const u32 nres = a.tnres[sl];
-      int len = 0;
-      if (39 * (int)nres + 200 > a.stride) { if (lane == 0) *s_fail = 1u; }
-      else if (nres <= H2_JS_CAP) len = hl_json_key_warp(a.strbuf + (size_t)i * a.stride, a.rbins, a.R, a.tr0[sl], nres, s_bins + warp * 6 * H2_JS_CAP, H2_JS_CAP);
-      else { if (lane == 0) len = hl_json_key(a.strbuf + (size_t)i * a.stride, a.rbins, a.R, a.tr0[sl], nres); len = __shfl_sync(0xffffffffu, len, 0); }
-      if (lane == 0) s_len[i] = len;
+      const u32 nres = a.tnres[sl], r0 = a.tr0[sl], m = (u32)s_best[i], len = (u32)s_len[i];
+      // list lengths and sources (0 = the std-bonds zero list, else the residue-major rbins slot)
+      const u32 seg_n[9] = {m, nres - 1, nres, m, nres, nres - 1, nres - 1, m, nres};
+      const u32 seg_s[9] = {0, 7, 0, 4, 0, 6, 8, 5, 3};
+      for (u32 p = lane; p < cstride; p += 32) {
+        u16 code = 0;
+        if (p < len) {
+          u32 k = p, g = 0;
+#pragma unroll
+          for (int q = 0; q < 8; ++q) if (g == (u32)q && k >= seg_n[q]) { k -= seg_n[q]; g = q + 1; }
+          const u32 v = seg_s[g] ? (u32)__ldg(a.rbins + (i64)seg_s[g] * a.R + r0 + k) : 0u;
+          code = __ldg(a.rank + ((k == seg_n[g] - 1u) ? 1024u : 0u) + min(v, 1023u));
+        }
+        cb[(size_t)i * cstride + p] = code;
+      }
     }
+    __syncthreads();
     if (threadIdx.x < H2_TB_CAP) s_best[threadIdx.x] = (int)threadIdx.x;
     __syncthreads();
-    if (*s_fail) {
-      if (threadIdx.x == 0) hs[H2_P1] = 100u + H2_HALT_TIES;
-      return;
-    }
-    __threadfence_block();
     for (u32 s = 1; s < nt; s <<= 1) {
       for (u32 x = warp * 2 * s; x + s < nt; x += nw * 2 * s) {
         const int ia = s_best[x], ib = s_best[x + s];
-        const bool b_less = hl_less(a.strbuf + (size_t)ib * a.stride, a.strbuf + (size_t)ia * a.stride, s_len[ib], s_len[ia]);
+        bool b_less = false;
+        for (u32 off = 0; off < cstride; off += 32) {
+          const u16 ca = cb[(size_t)ia * cstride + off + lane], cbv = cb[(size_t)ib * cstride + off + lane];
+          const unsigned diff = __ballot_sync(0xffffffffu, ca != cbv);
+          if (diff) {
+            const int l = __ffs(diff) - 1;
+            b_less = __shfl_sync(0xffffffffu, (int)(cbv < ca), l) != 0;
+            break;
+          }
+        }
         if (lane == 0 && b_less) s_best[x] = ib;
       }
       __syncthreads();
@@ -652,6 +697,7 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
     const u32 ref_r0 = h2_ld(hs + H2_WIN_R0), nres = h2_ld(hs + H2_WIN_NRES), cnt = h2_ld(hs + H2_WIN_CNT);
     const u32 new_tid = h2_ld(hs + H2_NTOK), ev0 = h2_ld(hs + H2_EVN), thr = h2_ld(hs + H2_THR);
     h2_flag(a, t, win);
+    if (t0) a.hs64[H2_TW_P2] += h2_now() - tm;
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P2] += n - tm; tm = n; }
     const u32 nocc = h2_ld(hs + H2_NOCC);
@@ -664,6 +710,7 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
       continue;
     }
     h2_deaths(a, t, nocc, ref_r0, nres);
+    if (t0) a.hs64[H2_TW_P3] += h2_now() - tm;
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P3] += n - tm; tm = n; }
     const u32 bad3 = h2_ld(hs + H2_MISMATCH) ? H2_HALT_COLLISION : (h2_ld(hs + H2_ERR) ? H2_HALT_INTERNAL : 0u);
@@ -675,9 +722,11 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
       continue;
     }
     h2_apply(a, t, nocc, win, new_tid, ev0);
+    if (t0) a.hs64[H2_TW_P4] += h2_now() - tm;
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P4] += n - tm; tm = n; }
     h2_births_end(a, t, nocc, win, new_tid, thr, step, ev0);
+    if (t0) a.hs64[H2_TW_P5] += h2_now() - tm;
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P5] += n - tm; hs[H2_ST_LOOPS] += 1u; }
   }
@@ -694,7 +743,7 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
 // ---- host entry ------------------------------------------------------------------------------------------------------
 enum { HB_HS = 0, HB_HS64, HB_HSH0, HB_HSH1, HB_GLUE0, HB_GLUE1, HB_POS0, HB_POS1, HB_LEN0, HB_LEN1, HB_TID0, HB_TID1,
        HB_FLAGS, HB_RMARK, HB_SCRATCH, HB_POWTAB, HB_P, HB_RBINS, HB_R, HB_SLOTS, HB_LOG2NS, HB_BMAX, HB_CAND, HB_CAP, HB_CBIT,
-       HB_TK, HB_TC, HB_TR0, HB_TNRES, HB_TLIST, HB_M, HB_CLKEY, HB_CLJ, HB_OCCJ, HB_OCCR, HB_STRBUF, HB_STRIDE, HB_EVL, HB_EVR, HB_EVP,
+       HB_TK, HB_TC, HB_TR0, HB_TNRES, HB_TLIST, HB_M, HB_CLKEY, HB_CLJ, HB_OCCJ, HB_OCCR, HB_STRBUF, HB_STRIDE, HB_RANK, HB_EVL, HB_EVR, HB_EVP,
        HB_LKEY, HB_LCNT, HB_LR0, HB_LNRES, HB_LEVS, HB_LNK, HB_THRNUM, HB_STREAMING, HB_CTAS, HB_N };
 
 __global__ void h2_set_target(u32* hs, u32 nsteps) { hs[H2_TARGET] = hs[H2_STEP] + nsteps; }
@@ -721,14 +770,14 @@ extern "C" int gb_h_loop2(const int64_t* b, int n_args, int nsteps, int final_co
   a.cap = (u32)b[HB_CAP]; a.cbit = (u32*)b[HB_CBIT];
   a.tk = (u64*)b[HB_TK]; a.tc = (u32*)b[HB_TC]; a.tr0 = (u32*)b[HB_TR0]; a.tnres = (u32*)b[HB_TNRES]; a.tlist = (u32*)b[HB_TLIST]; a.M = b[HB_M];
   a.cl_key = (u64*)b[HB_CLKEY]; a.cl_j = (u32*)b[HB_CLJ]; a.occ_j = (u32*)b[HB_OCCJ]; a.occ_r = (u32*)b[HB_OCCR];
-  a.strbuf = (char*)b[HB_STRBUF]; a.stride = (int)b[HB_STRIDE];
+  a.strbuf = (char*)b[HB_STRBUF]; a.stride = (int)b[HB_STRIDE]; a.rank = (const u16*)b[HB_RANK];
   a.ev_left = (u32*)b[HB_EVL]; a.ev_right = (u32*)b[HB_EVR]; a.ev_p = (u32*)b[HB_EVP];
   a.log_key = (u64*)b[HB_LKEY]; a.log_cnt = (u32*)b[HB_LCNT]; a.log_r0 = (u32*)b[HB_LR0]; a.log_nres = (u32*)b[HB_LNRES];
   a.log_evs = (u32*)b[HB_LEVS]; a.log_nk = (u32*)b[HB_LNK];
   a.thr_num = (u32)b[HB_THRNUM];
   a.max_loops = (u32)(4 * nsteps + 64);
   if (a.log2ns < 12 || a.log2ns > 30 || a.M < 1024 || (a.M & (a.M - 1)) || a.cap < 1 || a.cap > KC_SET / 2 || (a.stride & 127) ||
-      a.thr_num < 1 || a.thr_num > 16 || !a.hs || !a.hs64 || !a.cbit || !a.occ_j || !a.tlist) {
+      a.thr_num < 1 || a.thr_num > 16 || !a.hs || !a.hs64 || !a.cbit || !a.occ_j || !a.tlist || !a.rank) {
     gb_set_error("gb_h_loop2: bad arguments (log2ns %d, M %lld, cap %u, stride %d, thr_num %u)", a.log2ns, (long long)a.M, a.cap,
                  a.stride, a.thr_num);
     return -2;

@@ -63,6 +63,29 @@ def get_ind(v, values):
     raise ValueError(f"value {v} does not fall into any bin")
 
 
+def tie_rank_table():
+    """u16 [2][1024]: rank of the element strings "<v>," (row 0) and "<v>]" (row 1) in byte order.  A list element of the
+    reference's key string json.dumps(key, sort_keys=True) prints as "<v>, " or "<v>]"; these strings are prefix-free, so
+    the order of two key strings (bpe.py:1149,1469: the tie-break) is the lexicographic order of their element-rank
+    sequences (csrc/k_hloop2.cu h2_decide)."""
+    strs = sorted([(f"{v},".encode(), 0, v) for v in range(1024)] + [(f"{v}]".encode(), 1, v) for v in range(1024)])
+    tab = np.zeros((2, 1024), dtype=np.uint16)
+    for rank, (_, last, v) in enumerate(strs):
+        tab[last, v] = rank
+    return tab
+
+
+def tie_rank_sequence(key_dict, tab=None):
+    """the rank sequence h2_decide builds for a histogram-mode pair key (nine lists in sort_keys order); host mirror used
+    by the tests to pin the device tie-break order against python's string order"""
+    tab = tie_rank_table() if tab is None else tab
+    seq = []
+    for name in sorted(key_dict):
+        vals = key_dict[name]
+        seq += [int(tab[1 if k == len(vals) - 1 else 0, v]) for k, v in enumerate(vals)]
+    return seq
+
+
 def _dev():
     return torch.device("cuda", torch.cuda.current_device())
 
@@ -432,9 +455,9 @@ class Learner:
         self._quantize()
         self._ts = TokenState(self.bb.R, mode)
         R = self.bb.R
-        self.ev_left = _empty(R, torch.int32)
-        self.ev_right = _empty(R, torch.int32)
-        self.ev_p = _empty(R, torch.int32)
+        self._evl = _empty(R, torch.int32)
+        self._evr = _empty(R, torch.int32)
+        self._evp = _empty(R, torch.int32)
         self._ev_n = 0
         if mode == "H":
             self._init_tokens_h()
@@ -480,6 +503,25 @@ class Learner:
     @property
     def ev_n(self):
         self._drain(); return self._ev_n
+
+    # merge-event log: the device loops append an iteration's events in arbitrary order; they are put into (iteration,
+    # position) order on the device the first time somebody reads them
+    @property
+    def ev_left(self):
+        self._drain(); self._sort_pending(); return self._evl
+
+    @property
+    def ev_right(self):
+        self._drain(); self._sort_pending(); return self._evr
+
+    @property
+    def ev_p(self):
+        self._drain(); return self._evp
+
+    def _sort_pending(self):
+        todo, self._unsorted = getattr(self, "_unsorted", []), []
+        for e0, e1, nk in todo:
+            self._sort_events(e0, e1, nk)
 
     @ev_n.setter
     def ev_n(self, v):
@@ -882,7 +924,7 @@ class Learner:
                 P(a["len"]), P(b["len"]), P(a["tid"]), P(b["tid"]), P(ts.flags), P(hl.rmark), P(ts.scratch), P(self.powtab), self.hash_base,
                 P(self.rbins), self.bb.R, P(sk.slots), sk.log2ns, P(sk.bmax), P(sk.cand), sk.CAP, sk.variant, sk.ctas,
                 P(sk.small.keys), P(sk.small.cnt), P(sk.small.min), sk.small.M, P(hl.tie_keys), P(hl.tie_min),
-                P(hl.strbuf), hl.stride, P(self.ev_left), P(self.ev_right), P(self.ev_p), P(hl.log_key),
+                P(hl.strbuf), hl.stride, P(self._evl), P(self._evr), P(self._evp), P(hl.log_key),
                 P(hl.log["cnt"]), P(hl.log["r0"]), P(hl.log["nres"]), P(hl.log["evstart"]), P(hl.log["nk"]),
                 P(hl.cl_key), P(hl.cl_j), P(hl.cl_r), hl.Tmax, 1 if 16 * hl.Tmax > SlotSketch.STREAM_BYTES else 0, hl.period]
         d = hl.dist
@@ -910,7 +952,7 @@ class Learner:
         h[H["MPREV"]] = self._last_count
         h[H["NTOK"]] = self._ntok
         h[H["MAXSTEPS"]] = hl.log_cap
-        h[H["EVCAP"]] = self.ev_left.numel()
+        h[H["EVCAP"]] = self._evl.numel()
         hl.hs.copy_(torch.from_numpy(h.astype(np.int32)))
         hl.enq = 0
         _lib.call("gb_table_clear", *self.sketch.small.ptrs())     # hl_decide leaves it cleared from then on
@@ -1060,11 +1102,7 @@ class Learner:
                 # the device appends an iteration's merge events in arbitrary order: sort each iteration's range by position
                 e0, e1 = self._ev_n, int(h[H["EVN"]])
                 if e1 > e0:
-                    el, er = _u32(self.ev_left[e0:e1]), _u32(self.ev_right[e0:e1])
-                    seg = np.repeat(np.arange(done), lg["nk"])
-                    order = np.lexsort((el, seg))
-                    self.ev_left[e0:e1] = torch.from_numpy(el[order].astype(np.int32)).to(_dev())
-                    self.ev_right[e0:e1] = torch.from_numpy(er[order].astype(np.int32)).to(_dev())
+                    self._unsorted = getattr(self, "_unsorted", []) + [(e0, e1, hl.log["nk"][:done].clone())]
                 self._ts.T = int(h[H["T"]])
                 self._ev_n = e1
                 self.n_steps += done
@@ -1101,7 +1139,8 @@ class Learner:
               MISMATCH=25, NEWT=26, OVF=27, ERR=28, HALT_STEP=29, NTMAX=30, CMPT=31, FRESH=32, ND=33, NZ=34, MPREV=35,
               ST_PERIODS=36, ST_CROSS=37, ST_INCONCL=38, ST_COMPACT=39, ST_R2=40, ST_FULL=41, ST_LOOPS=42, PERIOD_LEN=43,
               ST_MAXNCL=44, ST_MAXND=45, ST_MAXNCAND=46, ST_TIES=47)
-    H2_TIMES = ("period_start", "decide", "flag", "deaths", "apply", "births", "compaction", "candidate_pass")
+    H2_TIMES = ("period_start", "decide", "flag", "deaths", "apply", "births", "compaction", "candidate_pass",
+                "flag_block0_work", "deaths_block0_work", "apply_block0_work", "births_block0_work")
     H2_HALT_NAMES = {**HALT_NAMES, 10: "internal", 11: "guard"}
     H2_TABLE_LOG2 = 15
 
@@ -1122,6 +1161,7 @@ class Learner:
         hl.log_key = _empty(hl.log_cap, torch.int64)
         hl.log = {k: _empty(hl.log_cap, torch.int32) for k in ("cnt", "r0", "nres", "evstart", "nk")}
         hl.cbit = _zeros((1 << sk.log2ns) // 32, torch.int32)
+        hl.rank = torch.from_numpy(tie_rank_table().view(np.int16).copy()).to(_dev())
         hl.M = 1 << int(os.environ.get("GEOBPE_H2_TABLE_LOG2", self.H2_TABLE_LOG2))
         hl.rmark = _zeros(ts.cap, torch.uint8)
         hl.cl_key = _empty(ts.cap, torch.int64)
@@ -1163,7 +1203,7 @@ class Learner:
                 P(a["len"]), P(b["len"]), P(a["tid"]), P(b["tid"]), P(ts.flags), P(hl.rmark), P(ts.scratch), P(self.powtab), self.hash_base,
                 P(self.rbins), self.bb.R, P(sk.slots), sk.log2ns, P(sk.bmax), P(sk.cand), sk.CAP, P(hl.cbit),
                 P(hl.tk), P(hl.tc), P(hl.tr0), P(hl.tnres), P(hl.tlist), hl.M, P(hl.cl_key), P(hl.cl_j), P(hl.occ_j), P(hl.occ_r),
-                P(hl.strbuf), hl.stride, P(self.ev_left), P(self.ev_right), P(self.ev_p), P(hl.log_key),
+                P(hl.strbuf), hl.stride, P(hl.rank), P(self._evl), P(self._evr), P(self._evp), P(hl.log_key),
                 P(hl.log["cnt"]), P(hl.log["r0"]), P(hl.log["nres"]), P(hl.log["evstart"]), P(hl.log["nk"]),
                 hl.thr_num, 1 if 16 * ts.cap > SlotSketch.STREAM_BYTES else 0, hl.ctas]
         assert len(vals) == hl.nargs, (len(vals), hl.nargs)
@@ -1179,7 +1219,7 @@ class Learner:
         h[H["EVN"]] = self._ev_n
         h[H["NTOK"]] = self._ntok
         h[H["LOGCAP"]] = hl.log_cap
-        h[H["EVCAP"]] = self.ev_left.numel()
+        h[H["EVCAP"]] = self._evl.numel()
         h[H["CLCAP"]] = hl.cl_key.numel()
         h[H["PAR"]] = 0 if ts.a is hl.buf0 else 1
         h[H["MPREV"]] = self._last_count
@@ -1248,11 +1288,7 @@ class Learner:
                 self._last_count = int(lg["cnt"][-1])
                 e0, e1 = self._ev_n, int(h[H["EVN"]])
                 if e1 > e0:        # merge events are appended in arbitrary order: sort each iteration's range by position
-                    el, er = _u32(self.ev_left[e0:e1]), _u32(self.ev_right[e0:e1])
-                    seg = np.repeat(np.arange(done), lg["nk"])
-                    order = np.lexsort((el, seg))
-                    self.ev_left[e0:e1] = torch.from_numpy(el[order].astype(np.int32)).to(_dev())
-                    self.ev_right[e0:e1] = torch.from_numpy(er[order].astype(np.int32)).to(_dev())
+                    self._unsorted = getattr(self, "_unsorted", []) + [(e0, e1, hl.log["nk"][:done].clone())]
                 self._ts.T = int(h[H["T"]])
                 self._ev_n = e1
                 self.n_steps += done
@@ -1282,6 +1318,17 @@ class Learner:
             self._h2_push_state()
             if rest > 0:
                 self._h2_enqueue(rest)
+
+    def _sort_events(self, e0, e1, nk_dev):
+        """order the merge events [e0, e1) by (iteration, left position) on the device (nk_dev: events per iteration)"""
+        if e1 - e0 < 2:
+            return
+        el = self._evl[e0:e1].to(torch.int64) & 0xFFFFFFFF
+        seg = torch.repeat_interleave(torch.arange(nk_dev.numel(), device=_dev()), nk_dev.to(torch.int64) & 0xFFFFFFFF,
+                                      output_size=e1 - e0)
+        order = torch.argsort((seg << 32) | el)
+        self._evl[e0:e1] = self._evl[e0:e1][order]
+        self._evr[e0:e1] = self._evr[e0:e1][order]
 
     def rehash(self, base=None):
         """give every live token its content hash under another base (two different windows shared a 64-bit hash: the
@@ -1393,10 +1440,10 @@ class Learner:
             q, cnt_dev = nk, None
         else:
             q, cnt_dev = min(bound, ts.T), u + 4
-        if self.ev_n + q > self.ev_left.numel():
+        if self.ev_n + q > self._evl.numel():
             raise RuntimeError("merge-event log overflow")
-        _lib.call("gb_write_events", _lib.ptr(ts.kept), q, cnt_dev, ts.p("pos"), aux, self.ev_left.data_ptr() + off,
-                  self.ev_right.data_ptr() + off, self.ev_p.data_ptr() + off)
+        _lib.call("gb_write_events", _lib.ptr(ts.kept), q, cnt_dev, ts.p("pos"), aux, self._evl.data_ptr() + off,
+                  self._evr.data_ptr() + off, self._evp.data_ptr() + off)
         if self.mode == "M":
             self._oplog(nk, p2cls)
         _lib.call("gb_merge_compact", _lib.ptr(ts.flags), ts.T,
@@ -1832,7 +1879,7 @@ class Inducer(Learner):
         R, S = self.bb.R, self.bb.S
         self.failed = (self.status_host & 3) != 0          # glue angle outside the training range -> ValueError
         self._ts = TokenState(R, "M")
-        self.ev_left = _empty(R, torch.int32); self.ev_right = _empty(R, torch.int32); self.ev_p = _empty(R, torch.int32)
+        self._evl = _empty(R, torch.int32); self._evr = _empty(R, torch.int32); self._evp = _empty(R, torch.int32)
         self._ev_n = 0
         th1 = thresholds[1]
         B = max(len(th1[k]) for k in BOND_TYPES)

@@ -41,4 +41,5 @@ if getattr(hl, "v2", False):
     out["device_steps"] = hl.steps
     out["phase_us_per_it"] = {k: v / 1e3 / max(hl.steps, 1) for k, v in hl.times_ns.items()}
     out["table_M"] = hl.M
+    out["device_us_per_it"] = sum(v for k, v in hl.times_ns.items() if k in ("period_start", "decide", "flag", "deaths", "apply", "births", "compaction")) / 1e3 / max(hl.steps, 1)
 print(json.dumps(out))
