@@ -1,12 +1,23 @@
 #!/usr/bin/env python
-"""bench.py -- GeoBPE learn hot path on B200 (BASELINE.json metric: BPE merge iterations / s).
+"""bench.py -- GeoBPE learn / induce hot path on B200 (BASELINE.json metric: BPE merge iterations / s, residues / s encoded).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--mode H|M] [--impl reference]
 
-A "step" is one merge iteration (K1 pair count + argmax, tie-break, K2 merge [+K4/K5/K6 in medoid mode]) over
-the resident shard of synthetic backbones.  N=1 workload = BASELINE.json configs[1]: 10k backbones x 256
-residues, histogram quantisation, 2,000 merges.  N>1: every rank holds its own 10k x 256 shard (weak scaling),
-pair counts combined by an NCCL allreduce.  Prints ONE JSON line on rank 0.
+A "step" is one merge iteration (BPE.step, bpe.py:1792-2166: pick the most frequent adjacent motif pair with the
+reference's tie-break, merge its occurrences left to right, update the pair counts) over the resident shard of synthetic
+backbones.  N=1 workload = BASELINE.json configs[1]: 10k backbones x 256 residues, histogram quantisation, 2,000 merges.
+N>1: every rank holds its own 10k x 256 shard (weak scaling); the sharded loop exchanges over peer memory / NCCL.
+Prints ONE JSON line on rank 0.
+
+  value        merge iterations / s, token arrays resident in HBM, W warm-up + K timed iterations ending with a drain of the
+               device loop (state block + step log read back)
+  e2e          the same through the public API from HOST arrays: H2D, thresholds + binning, residue tokens, K merges, D2H of
+               step log / segmentation / merge events; median of --reps repetitions, setup and steps reported separately
+  full_config  the configs[1] run itself (2,000 merges) whatever --steps says: device-resident rate and e2e
+  roofline     the pair-count kernel (k_slot_count), CUDA events around live launches on this workload's token arrays
+  loop_kernel  the persistent learn-loop kernel: device timers per phase, periods, candidate-pass bandwidth
+  roofline_at_scale  pair-count + exact-candidate kernels on 46 M tokens (per-GPU shard of configs[4], larger than L2)
+  medoid / induce / k5 / cpu_baseline / parity_check (N>1)   see DESIGN.md 6
 """
 import argparse
 import json
@@ -35,12 +46,15 @@ def parse():
     ap.add_argument("--backbones", type=int, default=10000)
     ap.add_argument("--residues", type=int, default=256)
     ap.add_argument("--bins", type=int, default=None)
+    ap.add_argument("--reps", type=int, default=3, help="repetitions of the e2e / full_config legs (median reported)")
     ap.add_argument("--cpu-backbones", type=int, default=None,
-                    help="backbones of the CPU sample (default: 2500 for --impl reference, 320 for the cpu_baseline leg)")
+                    help="backbones of the CPU sample (default: the whole workload for --impl reference, 320 for the cpu_baseline leg)")
     ap.add_argument("--induce-backbones", type=int, default=100000, help="held-out backbones x 512 residues (BASELINE configs[2])")
     ap.add_argument("--induce-residues", type=int, default=512)
     ap.add_argument("--induce-merges", type=int, default=2000)
+    ap.add_argument("--medoid-steps", type=int, default=300)
     ap.add_argument("--no-induce", action="store_true")
+    ap.add_argument("--no-medoid", action="store_true")
     ap.add_argument("--cpu-steps", type=int, default=2000)
     ap.add_argument("--no-scale-probe", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -101,32 +115,33 @@ class ClockSampler:
                 "samples": len(self.rows)}
 
 
-def reference_arm(args):
-    """--impl reference / cpu_baseline: the CPU oracle (port of the reference's algorithm; the reference itself is
-    Python and cannot travel to the GPU box) on a BOUNDED sample of the same workload, host cores."""
+def reference_arm(args, S, mode=None, steps=None):
+    """the CPU oracle (kind "port": restatement of the reference's algorithm; the reference itself is Python with absent
+    dependencies and cannot travel to the GPU box) on S backbones of the same synthetic workload, one host core.
+    value = steps-only rate (like the GPU arm's `value`), e2e_value = steps / (initialize + bin + steps)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import geobpe_oracle as O
     from geobpe_b200 import synthetic
-    S, n = args.cpu_backbones or (2500 if args.impl == "reference" else 320), args.residues
+    mode = mode or args.mode
+    n = args.residues
     vals, offs = synthetic.generate(S, n, seed=0)
     strucs = synthetic.to_structures(vals, offs)
     t0 = time.perf_counter()
-    bpe = O.BPE(strucs, res_init=True, seed=0, **oracle_hparams(args.mode, args.bins))
+    bpe = O.BPE(strucs, res_init=True, seed=0, **oracle_hparams(mode, args.bins))
     bpe.initialize()
     t1 = time.perf_counter()
     bpe.bin()
     t2 = time.perf_counter()
     k = 0
-    nsteps = min(args.steps + args.warmup, args.cpu_steps)
+    nsteps = min(steps if steps is not None else args.steps + args.warmup, args.cpu_steps)
     while k < nsteps:
         bpe.step()
         k += 1
     t3 = time.perf_counter()
-    return {"value": k / (t3 - t0), "steps_only_value": k / (t3 - t2), "unit": "merge_iters/s", "cores": 1, "kind": "port",
-            "sample": f"{S} backbones x {n} residues ({S * n} residues), mode {args.mode}, value = steps/(initialize+bin+steps): initialize {t1 - t0:.2f}s, "
-                      f"bin {t2 - t1:.2f}s, {k} steps {t3 - t2:.3f}s (incremental; cost grows with occurrences/merge; "
-                      f"bin() alone extrapolates linearly to {(t2 - t1) * args.backbones / S:.0f}s at {args.backbones} backbones)",
-            "init_s": t1 - t0, "bin_s": t2 - t1, "steps_s": t3 - t2}
+    return {"value": k / (t3 - t2), "e2e_value": k / (t3 - t0), "unit": "merge_iters/s", "cores": 1, "kind": "port",
+            "sample": f"{S} backbones x {n} residues ({S * n} residues), mode {mode}: initialize {t1 - t0:.2f}s, bin {t2 - t1:.2f}s, "
+                      f"{k} steps {t3 - t2:.3f}s; value = steps-only rate, e2e_value = steps / (initialize + bin + steps)",
+            "backbones": S, "same_config": S == args.backbones, "init_s": t1 - t0, "bin_s": t2 - t1, "steps_s": t3 - t2, "steps": k}
 
 
 def k1_scale_probe(learner, mode, reps=20, target_tokens=48_000_000):
@@ -178,6 +193,85 @@ def k1_scale_probe(learner, mode, reps=20, target_tokens=48_000_000):
             "slots": 1 << sk.log2ns, "nonzero_slots": int(so[2]), "top_slot_count": int(so[0])}
 
 
+def k1_live(L, reps=10):
+    """the pair-count kernel on the learner's CURRENT token arrays: CUDA events around `reps` launches (the slot counters
+    are restored afterwards: the loop keeps them exact incrementally)"""
+    import torch
+    from geobpe_b200 import _lib, engine as E
+    ts, sk = L.ts, L.sketch
+    keep = sk.slots.clone()
+    cs = 1 if 16 * ts.T > E.SlotSketch.STREAM_BYTES else 0
+    ms = []
+    for i in range(reps + 2):
+        sk.slots.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        if L.mode == "H":
+            _lib.call("gb_slot_count_h", ts.p("hsh"), ts.p("glue"), ts.p("len"), ts.T, _lib.ptr(L.powtab), L.hash_base,
+                      _lib.ptr(sk.slots), sk.log2ns, None, sk.variant | (8 * cs), sk.ctas)
+        else:
+            _lib.call("gb_slot_count_m", ts.p("cls"), ts.p("glue"), ts.T, _lib.ptr(sk.slots), sk.log2ns, None, sk.variant | (8 * cs), sk.ctas)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 2:
+            ms.append(e0.elapsed_time(e1))
+    nz = int((sk.slots != 0).sum().item())
+    sk.slots.copy_(keep)
+    return float(np.mean(ms)), int(ts.T), nz
+
+
+def k5_probe(Q=1 << 20, K=500, A=4, reps=5):
+    """K5 medoid assignment at the BASELINE configs[3] shape (500 medoids, 4-atom residue windows): achieved FLOP/s with the
+    per-RMSD flop count of SURVEY 8(d) (centroids 6m + covariance 18m + 3x3 singular values ~400 + residual 30m, m = A atoms)"""
+    import torch
+    from geobpe_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(0)
+    P = torch.randn(Q, A * 3, dtype=torch.float64, device="cuda", generator=g)
+    M = torch.randn(K, A * 3, dtype=torch.float64, device="cuda", generator=g)
+    out = torch.empty(Q, dtype=torch.int32, device="cuda")
+    ms = []
+    for i in range(reps + 1):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.call("gb_kabsch_assign", _lib.ptr(P), Q, A, _lib.ptr(M), K, _lib.ptr(out), None)
+        e1.record()
+        torch.cuda.synchronize()
+        if i:
+            ms.append(e0.elapsed_time(e1))
+    flop = 6 * A + 18 * A + 400 + 30 * A
+    t = float(np.mean(ms)) * 1e-3
+    return {"kernel": "k_kabsch_assign (float64, one thread per window, medoids in shared memory)", "windows": Q, "medoids": K, "atoms": A,
+            "rmsds": Q * K, "ms": t * 1e3, "flop_per_rmsd": flop, "flop_formula": "6m + 18m + 400 + 30m, m = atoms per window",
+            "achieved_tflops": Q * K * flop / t / 1e12, "rmsds_per_s": Q * K / t, "bound": "fp64 CUDA cores",
+            "peak_fp64_tflops_nominal": 40.0, "frac_of_nominal_fp64": Q * K * flop / t / 1e12 / 40.0}
+
+
+def medoid_arm(args):
+    """BASELINE configs[1] in medoid mode (README setting: bins 50, num_p 2-2:3-5:5-1:6-2:8-1, max_num_strucs 500)"""
+    import torch
+    from geobpe_b200 import engine as E, synthetic
+    hp = hparams("M", None)
+    vals, offs = synthetic.generate(args.backbones, args.residues, seed=0)
+    t0 = time.perf_counter()
+    L = E.Learner(vals, offs, rng=np.random.default_rng(0), verify=True, **hp)
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    for _ in range(5):
+        L.step()
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    k0 = L.n_steps
+    while L.n_steps - k0 < args.medoid_steps:
+        L.step()
+    torch.cuda.synchronize()
+    t3 = time.perf_counter()
+    k = L.n_steps - k0
+    return {"value": k / (t3 - t2), "unit": "merge_iters/s", "steps": k, "initialize_s": t1 - t0, "steps_s": t3 - t2,
+            "config": f"{args.backbones} x {args.residues}, medoid quantisation, bins 50, num_p {NUM_P}, max_num_strucs 500",
+            "vocabulary_tokens": len(L.tokens), "live_tokens_end": int(L.ts.T),
+            "note": "host-driven step: K1 on the device, tie-break / occurrence-set order / k-medoids iterations on the host (numpy RNG stream)"}
+
+
 def induce_arm(args, rank, world, barrier):
     """BASELINE configs[2]: frozen-vocabulary encode (K7, BPE.tokenize / bin/induce.py) of held-out synthetic backbones
     against a medoid-mode vocabulary learned here on the configs[1] training set.  Host arrays in, token arrays out;
@@ -210,15 +304,80 @@ def induce_arm(args, rank, world, barrier):
         t = torch.tensor([dt], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dt = float(t.item())
-    return {"metric": "residues_per_s_encoded", "value": R * world / dt, "unit": "residues/s", "seconds": dt,
-            "backbones": S * world, "residues": R * world, "residues_per_backbone": args.induce_residues,
-            "vocabulary_merges": args.induce_merges, "vocabulary_tokens": len(tokens), "tokens_out_per_rank": int(ts.T),
-            "rejected_backbones_rank0": int(ind.failed.sum()), "merges_fired_rank0": int(ind.n_steps),
-            "h2d_bytes": int(hv.nbytes + ho.nbytes), "d2h_bytes": int(sum(o.numel() * o.element_size() for o in out)),
-            "vocabulary_learn_seconds": t_learn,
-            "note": "host arrays -> H2D -> K3 binning -> residue medoid assignment (K4/K5) -> merge replay (K2 + K4/K5 per vocabulary "
-                    "merge) -> D2H of the segmentation; backbones whose glue angles leave the training range are rejected like the "
-                    "reference's ValueError (bpe.py:1105-1108)"}
+    res = {"metric": "residues_per_s_encoded", "value": R * world / dt, "unit": "residues/s", "seconds": dt,
+           "backbones": S * world, "residues": R * world, "residues_per_backbone": args.induce_residues,
+           "vocabulary_merges": args.induce_merges, "vocabulary_tokens": len(tokens), "tokens_out_per_rank": int(ts.T),
+           "rejected_backbones_rank0": int(ind.failed.sum()), "merges_fired_rank0": int(ind.n_steps),
+           "h2d_bytes": int(hv.nbytes + ho.nbytes), "d2h_bytes": int(sum(o.numel() * o.element_size() for o in out)),
+           "vocabulary_learn_seconds": t_learn,
+           "note": "host arrays -> H2D -> K3 binning -> residue medoid assignment (K4/K5) -> merge replay (K2 + K4/K5 per vocabulary "
+                   "merge) -> D2H of the segmentation; backbones whose glue angles leave the training range are rejected like the "
+                   "reference's ValueError (bpe.py:1105-1108)"}
+    if rank == 0 and world == 1 and not args.no_cpu:
+        res["cpu_baseline"] = induce_cpu(args, tokens, sphere, th, hv, ho)
+    return res
+
+
+def induce_cpu(args, tokens, sphere, thresholds, hv, ho, nb=3):
+    """BPE.tokenize of the first `nb` held-out backbones by the CPU oracle against the SAME vocabulary (one core)"""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import geobpe_oracle as O
+    from geobpe_b200 import synthetic
+    try:
+        tv, to = synthetic.generate(2, 16, seed=3)
+        ob = O.BPE(synthetic.to_structures(tv, to), res_init=True, seed=0, **oracle_hparams("M", None))
+        ob.initialize()
+        ob._tokens, ob._sphere_dict = tokens, sphere
+        for size, th in thresholds.items():
+            ob._thresholds[size] = th
+        strucs = synthetic.to_structures(hv[:, :int(ho[nb])], ho[:nb + 1])
+        t0 = time.perf_counter()
+        done = res = 0
+        for s in strucs:
+            tk = O.Tokenizer.from_structure(s)
+            try:
+                ob.tokenize(tk)
+            except ValueError:
+                pass
+            done += 1
+            res += len(s["angles"])
+            if time.perf_counter() - t0 > 25:
+                break
+        dt = time.perf_counter() - t0
+        return {"value": res / dt, "unit": "residues/s", "cores": 1, "kind": "port",
+                "sample": f"{done} held-out backbones x {args.induce_residues} residues against the same {len(sphere)}-key vocabulary, {dt:.1f}s"}
+    except Exception as ex:
+        return {"error": f"{type(ex).__name__}: {ex}"}
+
+
+def parity_check(comm, rank, world, steps=128, per_rank=48, n=64):
+    """N>1 self-check (the driver's GPU tests run on one GPU): a small set sharded over the ranks through the SAME sharded
+    loop the timed region used, against a one-GPU learner on the union, run on every rank: pop log + this rank's segmentation"""
+    import hashlib
+    from geobpe_b200 import engine as E, synthetic
+    vals, offs = synthetic.generate(per_rank * world, n, seed=77, ragged=True)
+    a, b = rank * per_rank, (rank + 1) * per_rank
+    lo, hi = int(offs[a]), int(offs[b])
+    hp = dict(bins={1: 6}, bin_strategy="histogram", std_bonds=True, mode="H")
+    Ls = E.Learner(np.ascontiguousarray(vals[:, lo:hi]), offs[a:b + 1] - offs[a], rng=np.random.default_rng(0), verify=True, comm=comm, **hp)
+    Lu = E.Learner(vals, offs, rng=np.random.default_rng(0), verify=True, **hp)
+    for _ in range(steps):
+        Ls.step(); Lu.step()
+    ok = [list(p) for p in Ls.pop_log] == [list(p) for p in Lu.pop_log]
+    ts, tu = Ls.ts, Lu.ts
+    pu, lu, tu_ = E._u32(tu.a["pos"][:tu.T]), E._u32(tu.a["len"][:tu.T]), E._u32(tu.a["tid"][:tu.T])
+    sel = (pu >= lo) & (pu < hi)
+    seg_u = np.stack([pu[sel] - lo, lu[sel], tu_[sel]])
+    seg_s = np.stack([E._u32(ts.a["pos"][:ts.T]), E._u32(ts.a["len"][:ts.T]), E._u32(ts.a["tid"][:ts.T])])
+    ok = ok and seg_u.shape == seg_s.shape and bool((seg_u == seg_s).all())
+    digest = hashlib.sha256(json.dumps([list(p) for p in Lu.pop_log]).encode()).hexdigest()[:16]
+    flags = comm.all_gather_object((bool(ok), digest))
+    dev_steps = Ls.hl.steps if Ls.hl is not None else 0
+    Ls.close()
+    return {"ranks": world, "steps": steps, "ok": all(f for f, _ in flags) and len({d for _, d in flags}) == 1,
+            "per_rank_ok": [f for f, _ in flags], "pop_log_sha256_16": digest, "device_iterations_sharded": dev_steps,
+            "what": f"{per_rank * world} ragged backbones x <= {n} residues sharded over {world} ranks vs one-GPU learner on the union: "
+                    f"pop log (count, key string) and this rank's segmentation (pos, len, token id) bit-exact"}
 
 
 def main():
@@ -229,21 +388,22 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        r = reference_arm(args)
+        r = reference_arm(args, args.cpu_backbones or args.backbones)
         line = {"impl": "reference", "metric": "bpe_merge_iters_per_s", "value": r["value"], "unit": "merge_iters/s",
                 "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": 1e3 / r["value"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "u64" if args.mode == "H" else "f64", "data": "synthetic",
-                "config": {"workload": f"BASELINE configs[1] bounded sample on host cores: {r['sample']}"},
-                "cpu_baseline": r, "e2e": {"value": r["value"], "unit": "merge_iters/s", "h2d_bytes_per_step": 0,
-                                           "d2h_bytes_per_step": 0}}
+                "config": {"workload": f"BASELINE configs[1] on host cores: {r['sample']}", "same_config": r["same_config"]},
+                "cpu_baseline": r, "e2e": {"value": r["e2e_value"], "unit": "merge_iters/s", "h2d_bytes_per_step": 0,
+                                           "d2h_bytes_per_step": 0, "setup_s": r["init_s"] + r["bin_s"], "steps_s": r["steps_s"]}}
         print(json.dumps(line))
         return
     import torch
     import torch.distributed as dist
     torch.cuda.set_device(local)
     if world > 1:
-        os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line (NCCL prints its version at VERSION)
+        os.environ.setdefault("NCCL_DEBUG", "WARN")   # a driver-set level is kept (NCCL's own lines go to stderr below)
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from geobpe_b200 import _lib, engine as E, synthetic
     from geobpe_b200 import build as B
@@ -261,162 +421,33 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    # ---- device-resident arm: inputs already in HBM, W warm-up + K timed merge iterations ----------------
-    L = mk()
-    for _ in range(args.warmup):
-        L.step()
-    L.sync()
-    L.prepare()                                      # warm-up also captures the loop's CUDA graphs
-    L.k1_events = None if L.async_steps else []      # device loop: K1 is timed in an instrumented continuation (below)
-    T_start = L.ts.T
-    lib = _lib.load()
-    barrier()
-    launches0 = _lib.launches
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clk:
+    def max_over_ranks(x):
+        if world > 1:
+            t = torch.tensor([x], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return x
+
+    def resident_run(L, nsteps):
+        """nsteps iterations + drain, CUDA events on the launching stream, barrier + synchronize on both sides"""
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        done = 0
-        while done < args.steps:
+        for _ in range(nsteps):
             L.step()
-            done += 1
-        L.sync()            # device-driven loop: drain it (one D2H of the state block + step log) inside the timed region
+        L.sync()            # drain the device loop (one D2H of the state block + step log) inside the timed region
         e1.record()
         barrier()
-    ms = e0.elapsed_time(e1)
-    T_end, top = L.ts.T, L.pop_log[-1][0]
-    if world > 1:
-        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    launches = _lib.launches - launches0
-    k1_ms = [a.elapsed_time(b) for a, b, _ in (L.k1_events or [])]
-    k1_T = [t for _, _, t in (L.k1_events or [])]
-    c2_ms, c2_T = [], []
-    k1_note = "CUDA events around every K1 launch of the timed region"
-    peer = L.hl is not None and L.hl.dist is not None and L.hl.dist.peer is not None
-    if L.async_steps and world > 1 and not peer:
-        # sharded loop, NCCL exchanges: the timed region replays CUDA graphs (kernels + NCCL); K1 is timed in the iterations that follow,
-        # launched part by part with CUDA events around every part-0 call (slots memset + k_slot_count)
-        n_inst = min(128, args.steps)
-        T_inst = L.ts.T
-        L.k1_events = []
-        for _ in range(n_inst):
-            L.step()
-        L.sync()
-        torch.cuda.synchronize()
-        k1_ms = [a.elapsed_time(b) for a, b, _ in L.k1_events]
-        nk = [e[2] for e in L.step_events[-n_inst:]]
-        k1_T = (T_inst - np.concatenate([[0], np.cumsum(nk)[:-1]])).tolist()[:len(k1_ms)]
-        L.k1_events = None
-        k1_note = (f"timed region = CUDA-graph replays; K1 (slots memset + k_slot_count) timed with CUDA events in the {n_inst} "
-                   f"iterations that follow it, launched part by part")
-    elif L.async_steps:
-        # the timed region replays CUDA graphs (no events inside); K1 is timed in an instrumented continuation of the
-        # same run: the next iterations launched kernel by kernel with CUDA events around every k_slot_count launch
-        import ctypes
-        n_inst = max(L.hl.period, min(256, args.steps))       # at least one whole period: one recount launch is observed
-        T_inst = L.ts.T
-        lib.gb_h_loop_time_k1(1)
-        for _ in range(n_inst):
-            L.step()
-        L.sync()
-        torch.cuda.synchronize()
-        buf = (ctypes.c_float * (n_inst + 64))()
-        n = lib.gb_h_loop_k1_times(buf, len(buf))
-        lib.gb_h_loop_time_k1(0)
-        loop_ms = [float(buf[i]) for i in range(n) if buf[i] > 0]
-        nk = [e[2] for e in L.step_events[-n_inst:]]
-        # (every sync leaves the loop at the start of a period: the recounts are iterations 0, period, 2 x period, ...)
-        loop_T = (T_inst - np.concatenate([[0], np.cumsum(nk)[:-1]])).tolist()[::L.hl.period][:len(loop_ms)]
-        loop_ms = loop_ms[:len(loop_T)]
-        k1_ms, k1_T = loop_ms + k1_ms, loop_T + k1_T      # + the iterations that fell back to the host path
-        k1_note = (f"timed region = CUDA-graph replays (no events inside a graph); timed with CUDA events around every "
-                   f"launch of the kernel in the {n_inst} iterations that follow it, launched kernel by kernel")
-        # second continuation: the exact candidate pass (hl_cand_count), the counting kernel that runs EVERY iteration
-        # (k_slot_count recounts the slot bounds once per compaction period)
-        n2 = min(128, args.steps)
-        T2 = L.ts.T
-        lib.gb_h_loop_time_k1(2)
-        for _ in range(n2):
-            L.step()
-        L.sync()
-        torch.cuda.synchronize()
-        n = lib.gb_h_loop_k1_times(buf, len(buf))
-        lib.gb_h_loop_time_k1(0)
-        c2_ms = [float(buf[i]) for i in range(n) if buf[i] > 0]
-        nk = [e[2] for e in L.step_events[-n2:]]
-        c2_T = (T2 - np.concatenate([[0], np.cumsum(nk)[:-1]])).tolist()[:len(c2_ms)]
-    bpt = 16 if args.mode == "H" else 8
-    k1_avg_ms = float(np.mean(k1_ms))
-    k1_bytes = bpt * float(np.mean(k1_T))
-    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
-    peak = float(peaks.get("hbm_gbs", 6650.0))
-    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s"
-    achieved = k1_bytes / (k1_avg_ms * 1e-3) / 1e9
-    tr = {}
-    tp = os.path.join(ROOT, "profiles", "r1_k1_traffic.json")
-    if os.path.exists(tp) and args.mode == "H":      # dram__bytes_read + write per launch from the committed ncu --set full capture
-        tr = json.load(open(tp))
-    sk = getattr(L, "sketch", None)
-    distinct = (int(L.hl.hs.cpu()[8]) if L.hl is not None else int(sk.sout.cpu()[2])) if sk is not None else L.table.distinct   # sketch: non-zero slots (lower bound)
-    k1_name = ("k_slot_count" if sk is not None else "k_pair_count") + ("<KeysH>" if args.mode == "H" else "<KeysM>")
-    sk_rounds = list(sk.rounds) if sk is not None else None
-    loop_info = None
-    if L.hl is not None:
-        loop_info = {"device_iterations": L.hl.steps, "second_rounds": L.hl.r2, "halts_by_code": {L.HALT_NAMES[k]: v for k, v in L.hl.halts.items()},
-                     "max_ties": getattr(L.hl, "ntmax", 0), "kernels_per_iteration": lib.gb_h_loop_kernels_per_step()}
-        if L.hl.dist is not None:
-            loop_info["exchange"] = ("peer memory (loads over NVLink inside the loop's kernels, CUDA IPC blocks)" if L.hl.dist.peer is not None
-                                     else "NCCL (allreduce-sum slots, allgather candidates, allreduce-max tie strings)")
-            loop_info["slots_log2"] = L.sketch.log2ns
-            loop_info["kernels_per_iteration"] = 17 if L.hl.dist.peer is not None else 12
-    pairs = T_end - L.bb.S
-    k1_per_step = 1.0 / L.hl.period if (c2_ms and L.hl is not None) else 1.0
-    k1_share = k1_avg_ms * args.steps * k1_per_step / ms
-    roof = {"bound": "hbm", "kernel": k1_name, "resolve_rounds_1_2_fallback": sk_rounds, "device_loop": loop_info,
-            "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
-            "frac_of_nominal_8TBs": achieved / 8000.0,
-            "traffic": (tr["in_loop"]["dram_bytes_per_token"] * float(np.mean(k1_T))) if tr else None,
-            "traffic_source": tr.get("source") if tr else None, "avg_ms": k1_avg_ms, "algorithmic_bytes_per_launch": k1_bytes,
-            "bytes_per_token": bpt, "launches_per_step": k1_per_step, "share_of_step": k1_share, "timing": k1_note}
-    if c2_ms:
-        # the dominant counting kernel of the step is the exact candidate pass; the recount kernel is reported beside it
-        c2_avg, c2_bytes = float(np.mean(c2_ms)), bpt * float(np.mean(c2_T))
-        a2 = c2_bytes / (c2_avg * 1e-3) / 1e9
-        t2 = tr.get("in_loop_pass2") if tr else None
-        roof = {"bound": "hbm", "kernel": "hl_cand_count<KeysHL> (exact pair counts of the candidate slots: one full pass over the "
-                                          "token arrays every iteration)",
-                "device_loop": loop_info, "achieved": a2, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": a2 / peak,
-                "frac_of_nominal_8TBs": a2 / 8000.0,
-                "traffic": (t2["dram_bytes_per_token"] * float(np.mean(c2_T))) if t2 else None,
-                "traffic_source": tr.get("source") if t2 else None, "avg_ms": c2_avg, "algorithmic_bytes_per_launch": c2_bytes,
-                "bytes_per_token": bpt, "launches_per_step": 1.0, "share_of_step": c2_avg * args.steps / ms, "timing": k1_note,
-                "note": "token arrays of this config (41 MB) are L2-resident, so the rate is not DRAM-limited here; "
-                        "roofline_at_scale times the same two kernels on 48 M tokens (> L2)",
-                "recount": {k: roof[k] for k in ("kernel", "achieved", "frac", "traffic", "avg_ms", "algorithmic_bytes_per_launch",
-                                                 "launches_per_step", "share_of_step")}}
-    scale = None
-    if not args.no_scale_probe and rank == 0:
-        pr = k1_scale_probe(L, args.mode)
-        a2 = pr["bytes_per_token"] * pr["tokens"] / (pr["ms"] * 1e-3) / 1e9
-        scale = dict(pr, bound="hbm", achieved=a2, peak=peak, unit="GB/s", frac=a2 / peak, frac_of_nominal_8TBs=a2 / 8000.0,
-                     traffic=(tr["at_scale"]["dram_bytes_per_token"] * pr["tokens"]) if tr else None,
-                     pass2_achieved=pr["bytes_per_token"] * pr["tokens"] / (pr["pass2_ms"] * 1e-3) / 1e9,
-                     pass2_frac=pr["bytes_per_token"] * pr["tokens"] / (pr["pass2_ms"] * 1e-3) / 1e9 / peak,
-                     note="K1 pass 1 (k_slot_count) alone on this workload's token arrays tiled to the per-GPU shard of "
-                          "BASELINE config 5 (48 M tokens > L2); pass2_* = k_cand_count (exact resolution) on the same arrays")
-    if world > 1:
-        L.close()                                      # frees the peer-memory block (collective)
-    del L
-    torch.cuda.empty_cache()
+        return max_over_ranks(e0.elapsed_time(e1))
 
-    # ---- e2e arm: host buffers -> H2D -> initialize (K3, residue tokens) -> K merges -> D2H token arrays ----
-    e2e = None
-    if not args.no_e2e:
+    def e2e_run(nsteps):
+        """host arrays -> Learner -> nsteps merges -> D2H of step log, vocabulary, segmentation, merge events"""
         barrier()
         t0 = time.perf_counter()
         L2 = mk()
-        for _ in range(args.steps):
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        for _ in range(nsteps):
             L2.step()
         ts = L2.ts
         n_vocab = len(L2.tokens)                       # formats the vocabulary entries / pop log of every iteration
@@ -424,19 +455,155 @@ def main():
         n_ev = L2.ev_n
         out += [L2.ev_left[:n_ev].cpu(), L2.ev_right[:n_ev].cpu()]
         torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        if world > 1:
-            t = torch.tensor([dt], device="cuda", dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            dt = float(t.item())
+        t2 = time.perf_counter()
+        d2h = sum(o.numel() * o.element_size() for o in out)
+        h2d = L2.bb.h2d_bytes
         if world > 1:
             L2.close()
-        d2h = sum(o.numel() * o.element_size() for o in out)
-        e2e = {"value": args.steps / dt, "unit": "merge_iters/s", "h2d_bytes_per_step": L2.bb.h2d_bytes / args.steps,
-               "d2h_bytes_per_step": d2h / args.steps, "seconds": dt,
-               "note": "Learner(host arrays): H2D of 72 B/residue, K3 thresholds+binning, residue tokens, K merges, D2H of the step log + vocabulary entries formatted on the host, D2H of segmentation + merge events"}
         del L2
-    induce = None
+        return max_over_ranks(t1 - t0), max_over_ranks(t2 - t1), h2d, d2h, n_vocab
+
+    def e2e_median(nsteps, reps):
+        e2e_run(min(nsteps, 64))                       # untimed: allocator growth, lazily loaded kernels
+        rows = [e2e_run(nsteps) for _ in range(reps)]
+        tot = sorted(r[0] + r[1] for r in rows)
+        med = tot[len(tot) // 2]
+        row = min(rows, key=lambda r: abs(r[0] + r[1] - med))
+        return {"value": nsteps / med, "unit": "merge_iters/s", "h2d_bytes_per_step": row[2] / nsteps, "d2h_bytes_per_step": row[3] / nsteps,
+                "seconds": med, "setup_s": row[0], "steps_s": row[1], "reps": reps, "values_all_reps": [nsteps / t for t in tot],
+                "spread": (tot[-1] - tot[0]) / med,
+                "note": "Learner(host arrays): H2D of 72 B/residue, K3 thresholds + binning, residue tokens (setup_s); K merges, D2H of the "
+                        "step log, vocabulary entries formatted on the host, D2H of segmentation + merge events (steps_s); median repetition"}
+
+    # ---- device-resident arm: inputs already in HBM, W warm-up + K timed merge iterations ----------------
+    L = mk()
+    for _ in range(args.warmup):
+        L.step()
+    L.sync()
+    L.prepare()                                      # (v1 loop: captures the CUDA graphs)
+    T_start = L.ts.T
+    launches0 = _lib.launches
+    with ClockSampler(local) as clk:
+        ms = resident_run(L, args.steps)
+        T_end = L.ts.T
+        launches = _lib.launches - launches0
+        hl = L.hl
+        snap = None
+        if hl is not None and getattr(hl, "v2", False):     # loop statistics of warm-up + timed region (before the filler below)
+            snap = (hl.steps, dict(hl.stats), dict(hl.times_ns), dict(hl.halts), hl.ntmax, hl.M)
+        if ms < 600:                                 # keep the GPU busy until nvidia-smi has sampled the clocks a few times
+            t_end = time.time() + 0.9
+            Lb = mk() if world == 1 else None
+            while Lb is not None and time.time() < t_end and Lb.n_steps < 1500:
+                for _ in range(64):
+                    Lb.step()
+                Lb.sync()
+            del Lb
+    top = L.pop_log[-1][0]
+    v2 = hl is not None and getattr(hl, "v2", False)
+    loop_info = None
+    if hl is not None:
+        loop_info = {"design": "persistent cooperative kernel, incremental pair counts (k_hloop2.cu)" if v2 else
+                     "per-iteration candidate pass, CUDA-graph replays (k_hloop.cu)",
+                     "device_iterations": hl.steps, "halts_by_code": {L.H2_HALT_NAMES.get(k, k): v for k, v in hl.halts.items()},
+                     "max_ties": getattr(hl, "ntmax", 0)}
+        if v2:
+            steps_, stats_, times_, halts_, ntmax_, M_ = snap
+            n_it = max(steps_, 1)
+            loop_info.update(device_iterations=steps_, halts_by_code={L.H2_HALT_NAMES.get(k, k): v for k, v in halts_.items()}, max_ties=ntmax_,
+                             stats=stats_, phase_us_per_iteration={k: v / 1e3 / n_it for k, v in times_.items()},
+                             table_slots=M_, slots_log2=L.sketch.log2ns, ctas_per_sm=hl.ctas)
+            cp_ns, periods = times_["candidate_pass"], max(stats_["periods"], 1)
+            if cp_ns:
+                loop_info["candidate_pass"] = {"avg_us": cp_ns / 1e3 / periods, "per_iteration": periods / n_it,
+                                               "achieved_gbs": 16.0 * L.ts.T / (cp_ns / periods), "bytes_per_token": 16}
+            loop_info["equivalent_recount_gbs"] = 16.0 * 0.5 * (T_start + T_end) * args.steps / (ms * 1e6)
+            loop_info["equivalent_note"] = ("what a design that re-reads 16 B per live token every iteration would have to stream to run "
+                                            "these iterations in this time; the incremental design reads only the pair list and the occurrences")
+        elif hl.dist is not None:
+            loop_info["exchange"] = ("peer memory (loads over NVLink inside the loop's kernels, CUDA IPC blocks)" if hl.dist.peer is not None
+                                     else "NCCL (allreduce-sum slots, allgather candidates, allreduce-max tie strings)")
+            loop_info["slots_log2"] = L.sketch.log2ns
+
+    # ---- roofline: the pair-count kernel on this workload's live token arrays ---------------------------------------
+    bpt = 16 if args.mode == "H" else 8
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s"
+    tr = {}
+    tp = os.path.join(ROOT, "profiles", "r1_k1_traffic.json")
+    if os.path.exists(tp) and args.mode == "H":      # dram__bytes_read + write per launch from the committed ncu --set full capture
+        tr = json.load(open(tp))
+    roof = None
+    distinct = 0
+    if L.sketch is not None:
+        k1_ms, k1_T, distinct = k1_live(L)
+        ach = bpt * k1_T / (k1_ms * 1e-3) / 1e9
+        launches_per_step = (1.0 / max(snap[0], 1)) if v2 else (1.0 / hl.period if hl is not None else 1.0)
+        roof = {"bound": "hbm", "kernel": "k_slot_count<KeysH> (pair-count kernel: every adjacent pair hashed into the slot counters)",
+                "achieved": ach, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": ach / peak, "frac_of_nominal_8TBs": ach / 8000.0,
+                "bytes_per_token": bpt, "survey_bytes_per_token": 8, "frac_at_survey_bytes": ach / peak * 8 / bpt,
+                "traffic": (tr["in_loop"]["dram_bytes_per_token"] * k1_T) if tr else None, "traffic_source": tr.get("source") if tr else None,
+                "avg_ms": k1_ms, "algorithmic_bytes_per_launch": bpt * k1_T, "launches_per_step": launches_per_step,
+                "share_of_step": k1_ms * launches_per_step / (ms / args.steps),
+                "timing": ("CUDA events around 10 launches on the live token arrays after the timed region (the loop runs it once, at bin(); "
+                           "the pair counts are then maintained incrementally)") if v2 else "CUDA events around 10 launches on the live token arrays",
+                "note": f"token arrays of this config ({bpt * k1_T / 1e6:.0f} MB) are L2-resident: not a DRAM number; see roofline_at_scale",
+                "loop_kernel": loop_info}
+    scale = None
+    if not args.no_scale_probe and rank == 0 and L.sketch is not None:
+        pr = k1_scale_probe(L, args.mode)
+        a2 = pr["bytes_per_token"] * pr["tokens"] / (pr["ms"] * 1e-3) / 1e9
+        p2 = pr["bytes_per_token"] * pr["tokens"] / (pr["pass2_ms"] * 1e-3) / 1e9
+        scale = dict(pr, bound="hbm", achieved=a2, peak=peak, unit="GB/s", frac=a2 / peak, frac_of_nominal_8TBs=a2 / 8000.0,
+                     survey_bytes_per_token=8, frac_at_survey_bytes=a2 / peak * 8 / pr["bytes_per_token"],
+                     traffic=(tr["at_scale"]["dram_bytes_per_token"] * pr["tokens"]) if tr else None,
+                     pass2_achieved=p2, pass2_frac=p2 / peak,
+                     note="K1 pass 1 (k_slot_count) alone on this workload's token arrays tiled to the per-GPU shard of "
+                          "BASELINE config 5 (48 M tokens > L2); pass2_* = k_cand_count (exact resolution) on the same arrays")
+    pairs = T_end - L.bb.S
+    par = None
+    if world > 1:
+        L.close()                                      # frees the peer-memory block (collective)
+    del L
+    torch.cuda.empty_cache()
+    if world > 1:
+        try:
+            par = parity_check(comm, rank, world)
+        except Exception as ex:
+            par = {"ranks": world, "ok": False, "error": f"{type(ex).__name__}: {ex}"}
+
+    # ---- e2e + the full configs[1] run -------------------------------------------------------------------------------
+    e2e = full = None
+    if not args.no_e2e:
+        e2e = e2e_median(args.steps, args.reps)
+        if args.mode == "H":
+            if args.steps == 2000:
+                full = {"steps": 2000, "value": args.steps / (ms * 1e-3), "ms_per_step": ms / args.steps, "e2e": e2e, "same_run_as_value": True}
+            else:
+                Lf = mk()
+                for _ in range(args.warmup):
+                    Lf.step()
+                Lf.sync()
+                msf = resident_run(Lf, 2000)
+                if world > 1:
+                    Lf.close()
+                del Lf
+                full = {"steps": 2000, "value": 2000 / (msf * 1e-3), "ms_per_step": msf / 2000, "e2e": e2e_median(2000, args.reps),
+                        "same_run_as_value": False}
+            full["config"] = f"BASELINE configs[1] in full: {args.backbones} x {args.residues}, histogram quantisation, 2,000 merges"
+    medoid = induce = k5 = None
+    if rank == 0 and world == 1 and not args.no_medoid and args.mode == "H":
+        try:
+            medoid = medoid_arm(args)
+            if not args.no_cpu:
+                medoid["cpu_baseline"] = reference_arm(args, 100, mode="M", steps=40)
+        except Exception as ex:
+            medoid = {"error": f"{type(ex).__name__}: {ex}"}
+        try:
+            k5 = k5_probe()
+        except Exception as ex:
+            k5 = {"error": f"{type(ex).__name__}: {ex}"}
     if not args.no_induce:
         try:
             induce = induce_arm(args, rank, world, barrier)
@@ -444,8 +611,10 @@ def main():
             induce = {"error": f"{type(ex).__name__}: {ex}"}
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cpu = reference_arm(args)
+        cpu = reference_arm(args, args.cpu_backbones or 320)
     if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
         return
     line = {
         "metric": "bpe_merge_iters_per_s", "value": args.steps / (ms * 1e-3), "unit": "merge_iters/s",
@@ -458,12 +627,16 @@ def main():
                    "mode": args.mode, "l2": "inputs (token arrays 41 MB + table) smaller than L2 at this config; "
                                             "the at-scale probe uses 48 M tokens (768 MB) > L2",
                    "live_tokens_start": T_start, "live_tokens_end": T_end, "distinct_keys": distinct,
+                   "distinct_keys_note": "non-zero slot counters after the timed region (lower bound of the distinct pair keys)",
                    "pairs": pairs, "distinct_over_pairs": distinct / max(pairs, 1), "last_top_count": top,
                    "residues_total": R * world},
-        "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
-        "roofline": roof,
-        "roofline_at_scale": scale, "induce": induce, "cpu_baseline": cpu,
+        "clocks": clk.summary(), "e2e": e2e, "full_config": full, "gpu_launches": launches,
+        "gpu_launches_note": "kernel launches issued through the C ABI inside the timed region (the persistent loop kernel runs hundreds of "
+                             "iterations per launch)",
+        "roofline": roof, "roofline_at_scale": scale, "medoid": medoid, "induce": induce, "k5": k5, "cpu_baseline": cpu,
     }
+    if par is not None:
+        line["parity_check"] = par
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

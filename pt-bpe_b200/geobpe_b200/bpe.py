@@ -454,9 +454,11 @@ class BPE(_View):
     def __getstate__(self):
         """pickle layout of encode.py:403-427: vocabulary + hyper-parameters + materialised tokenizers; the device
         state (HBM buffers) is not part of the pickle"""
+        d = dict(self.__dict__)
         if self._learner is not None:
             self._learner.tokens
-        d = dict(self.__dict__)
+            if not isinstance(self._learner, E.Inducer):
+                d["_resume"] = self._learner.export_state()       # lets step() continue after pickle.load (encode.py:239-260)
         for k in ("_learner", "_export", "_ev_cache"):
             d[k] = None
         d["_tokens"] = d.pop("_tokens_", None)
@@ -501,8 +503,7 @@ class BPE(_View):
         t0 = time.perf_counter()
         L = self._learner
         if L is None:
-            raise RuntimeError("this BPE was unpickled: the device state is gone; resume by re-running initialize() "
-                               "(learning is seconds on the GPU) -- induce/tokenize/quantize work on the pickle as is")
+            L = self._resume_learner()
         L.step()
         if self._mode == "M":                          # bpe.py:2164-2166: recurse while the top key is recurring
             while L.ts.T > L.bb.S and L.peek_m()[2] is not None:
@@ -510,8 +511,30 @@ class BPE(_View):
         self._step = self._learner.n_steps
         self._times.append(time.perf_counter() - t0)
 
+    def _resume_learner(self):
+        """bin/encode.py:239-260 reloads the newest bpe_iter={t}.pkl and keeps stepping: the inputs are re-uploaded and
+        re-binned (deterministic), segmentation / merge events / vocabulary come from the pickle"""
+        st = self.__dict__.get("_resume")
+        if st is None:
+            raise RuntimeError("this BPE was unpickled without learn state (initialize() was never run): call initialize() first")
+        self._learner = E.Learner(self._vals, self._offsets, self.bins, self.bin_strategy, self.std_bonds, mode=self._mode,
+                                  rmsd_super_res=self.rmsd_super_res, num_partitions=self.num_partitions,
+                                  max_num_strucs=self.max_num_strucs, rng=self.rng, resume=st)
+        L = self._learner
+        self._tokens = L.tokens
+        if self._mode == "M":
+            self._sphere_dict = L.sphere_dict
+        self._export = self._ev_cache = None
+        if isinstance(self.n, int) and len(self.tokenizers) == L.bb.S:     # (not after an induce --append)
+            for i, t in enumerate(self.tokenizers):
+                if not getattr(t, "_local", False):
+                    t._bpe, t._i, t._mat, t._cache_step = self, i, None, None
+        return L
+
     @property
     def pop_log(self):
+        if self._learner is None and self.__dict__.get("_resume") is not None:
+            return self._resume["pop_log"]
         return self._learner.pop_log
 
     def glue_opt_all(self):

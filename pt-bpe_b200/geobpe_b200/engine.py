@@ -409,7 +409,7 @@ class Learner:
 
     def __init__(self, vals, offsets, bins, bin_strategy="histogram", std_bonds=True, mode="H",
                  rmsd_super_res=True, num_partitions=3, max_num_strucs=500, rng=None, verify=True, comm=None,
-                 use_sketch=True, async_steps=True):
+                 use_sketch=True, async_steps=True, resume=None):
         self.comm = comm if (comm is not None and comm.world > 1) else None
         if self.comm is not None and mode != "H":
             raise NotImplementedError("multi-GPU medoid mode needs the sampled windows gathered in set order "
@@ -459,10 +459,14 @@ class Learner:
         self._evr = _empty(R, torch.int32)
         self._evp = _empty(R, torch.int32)
         self._ev_n = 0
+        if resume is not None:
+            self.hash_base = resume.get("hash_base", self.hash_base)
         if mode == "H":
             self._init_tokens_h()
-        else:
+        elif resume is None:
             self._init_tokens_m()
+        if resume is not None:
+            self._load_state(resume)
 
 
     # ---- state that the device-driven loop advances: reading it first drains the loop -------------------------
@@ -488,8 +492,12 @@ class Learner:
         for cnt, r0, nres in raw:
             dicts = self._h_key_dicts(r0.tolist(), nres.tolist()) if nres is not None else None
             for s in range(len(cnt)):
-                key_str = json.dumps(dicts[s], sort_keys=True) if dicts is not None else r0[s]
-                self._tokens[len(self._tokens)] = json.loads(key_str)
+                if dicts is not None:                  # (same dict json.loads(key_str) would build: keys in sorted order)
+                    key_str = json.dumps(dicts[s], sort_keys=True)
+                    self._tokens[len(self._tokens)] = {k: dicts[s][k] for k in sorted(dicts[s])}
+                else:
+                    key_str = r0[s]
+                    self._tokens[len(self._tokens)] = json.loads(key_str)
                 self._pop_log.append((int(cnt[s]), key_str))
 
     @property
@@ -1564,18 +1572,7 @@ class Learner:
         """bpe.py:263-391: residue tokens = nearest of K medoids (size 3 = inner residues, size 2 = last)."""
         bb = self.bb
         R, S = bb.R, bb.S
-        self.class_of, self.class_geo, self.class_f3, self._f3_dirty = {}, [], [], True
-        self.sphere_dict = {}
-        self.sphere_packed = {}        # packed key -> key string, for keys popped in step()
-        self.token_keys = []           # list(_tokens)
-        th1 = self.th.thresholds[self.size0]
-        if self.std_bonds:
-            self.d_f3 = (BOND_LENGTHS[0], BOND_LENGTHS[1], INIT_TAU)
-        else:
-            self.d_f3 = (self.centre("N:CA", get_ind(INIT_N_CA, th1["N:CA"])),
-                         self.centre("CA:C", get_ind(INIT_CA_C, th1["CA:C"])), INIT_TAU)
-        if self.std_bonds:
-            raise NotImplementedError("medoid mode with std_bonds needs quantised-bond coordinates; free_bonds only")
+        self._m_setup()
         is_last = torch.zeros(R, dtype=torch.bool, device=_dev())
         is_last[(bb.offsets[1:] - 1)] = True
         lists = {3: torch.nonzero(~is_last).flatten().to(torch.int32), 2: torch.nonzero(is_last).flatten().to(torch.int32)}
@@ -1627,15 +1624,78 @@ class Learner:
         ts.a["tid"][:R] = tid_res
         self.init_tid = tid_res.clone()
         # op log of the occurrence sets: initial segment = every adjacent pair in order (bpe.py:1441-1453)
+        _lib.call("gb_pair_keys_m", ts.p("cls"), ts.p("glue"), ts.p("pos"), R, _lib.ptr(self.log_key), _lib.ptr(self.log_pos))
+        self.log_n = R
+        self.log_bounds = [R]          # end offsets of: initial segment, step 1, step 2, ...
+        self.key_reset_at = {}         # packed key -> log offset after which its set is fresh
+
+    def _m_setup(self):
+        """medoid-mode tables that do not consume the RNG stream (also the starting point of a resumed run)"""
+        R = self.bb.R
+        self.class_of, self.class_geo, self.class_f3, self._f3_dirty = {}, [], [], True
+        self.sphere_dict = {}
+        self.sphere_packed = {}        # packed key -> key string, for keys popped in step()
+        self.token_keys = []           # list(_tokens)
+        th1 = self.th.thresholds[self.size0]
+        if self.std_bonds:
+            raise NotImplementedError("medoid mode with std_bonds needs quantised-bond coordinates; free_bonds only")
+        self.d_f3 = (self.centre("N:CA", get_ind(INIT_N_CA, th1["N:CA"])),
+                     self.centre("CA:C", get_ind(INIT_CA_C, th1["CA:C"])), INIT_TAU)
         self.log_cap = 5 * R + 16
         self.log_key = _empty(self.log_cap, torch.int64)
         self.log_pos = _empty(self.log_cap, torch.int32)
         self.log_scratch = _empty(_lib.load().gb_select_scratch_elems(self.log_cap), torch.int32)
         self.log_sel = _empty(self.log_cap, torch.int32)
-        _lib.call("gb_pair_keys_m", ts.p("cls"), ts.p("glue"), ts.p("pos"), R, _lib.ptr(self.log_key), _lib.ptr(self.log_pos))
-        self.log_n = R
-        self.log_bounds = [R]          # end offsets of: initial segment, step 1, step 2, ...
-        self.key_reset_at = {}         # packed key -> log offset after which its set is fresh
+
+    # ---- checkpoint / resume (bpe_iter={t}.pkl is reloaded by bin/encode.py:239-260 and stepping continues) ---------------
+    def export_state(self):
+        """host copy of everything a later Learner(resume=...) needs beyond the inputs: segmentation, merge events, step
+        bookkeeping; medoid mode also its geometry classes and the occurrence-set op log (CPython set order emulation)"""
+        self._drain()
+        self._sort_pending()
+        ts, T, n = self._ts, self._ts.T, self._ev_n
+        u = lambda t: _u32(t).astype(np.uint32)
+        st = dict(mode=self.mode, T=T, n_steps=self.n_steps, hash_base=self.hash_base, pos=u(ts.a["pos"][:T]), len=u(ts.a["len"][:T]),
+                  tid=u(ts.a["tid"][:T]), ev_left=u(self._evl[:n]), ev_right=u(self._evr[:n]), ev_p=u(self._evp[:n]),
+                  step_events=list(self._step_events), pop_log=list(self.pop_log), tokens=self.tokens)
+        if self.mode == "M":
+            st.update(cls=u(ts.a["cls"][:T]), class_geo=self.class_geo, sphere_dict=self.sphere_dict, sphere_packed=self.sphere_packed,
+                      sphere_n=self.sphere_n, token_keys=self.token_keys, init_tid=u(self.init_tid),
+                      log_key=self.log_key[:self.log_n].cpu().numpy(), log_pos=u(self.log_pos[:self.log_n]),
+                      log_bounds=list(self.log_bounds), key_reset_at=dict(self.key_reset_at))
+        return st
+
+    def _load_state(self, st):
+        if st["mode"] != self.mode:
+            raise ValueError("checkpoint was written in the other quantisation mode")
+        ts, T, dev = self._ts, int(st["T"]), _dev()
+        up = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.int32)).to(dev)
+        ts.T = T
+        ts.a["pos"][:T] = up(st["pos"]); ts.a["len"][:T] = up(st["len"]); ts.a["tid"][:T] = up(st["tid"])
+        last = (ts.a["pos"][:T].to(torch.int64) & 0xFFFFFFFF) + (ts.a["len"][:T].to(torch.int64) & 0xFFFF) - 1
+        ts.a["glue"][:T] = self.glue_res[last]
+        n = len(st["ev_left"])
+        self._evl[:n] = up(st["ev_left"]); self._evr[:n] = up(st["ev_right"]); self._evp[:n] = up(st["ev_p"])
+        self._ev_n = n
+        self._step_events = list(st["step_events"])
+        self._pop_log = list(st["pop_log"])
+        self._tokens = st["tokens"]
+        self.n_steps = int(st["n_steps"])
+        if self.mode == "H":
+            _lib.call("gb_rehash_tokens", _lib.ptr(self.sym), _lib.ptr(self.glue_res), ts.p("pos"), ts.p("len"), T, self.hash_base, ts.p("hsh"))
+            return
+        self._m_setup()
+        self.class_geo = st["class_geo"]
+        self.class_of = {json.dumps(g): c for c, g in enumerate(self.class_geo)}
+        self.class_f3 = [[g["N:CA"][0], g["CA:C"][0], g["tau"][0]] for g in self.class_geo]
+        self.sphere_dict, self.sphere_packed, self.sphere_n = st["sphere_dict"], st["sphere_packed"], st["sphere_n"]
+        self.token_keys = st["token_keys"]
+        ts.a["cls"][:T] = up(st["cls"])
+        self.init_tid = up(st["init_tid"])
+        m = len(st["log_key"])
+        self.log_key[:m] = torch.from_numpy(np.ascontiguousarray(st["log_key"])).to(dev)
+        self.log_pos[:m] = up(st["log_pos"])
+        self.log_n, self.log_bounds, self.key_reset_at = m, list(st["log_bounds"]), dict(st["key_reset_at"])
 
     def _oplog(self, nk, p2cls):
         ts = self.ts
