@@ -267,10 +267,39 @@ int gb_h_loop_k1_times(float* ms_host, int cap);
 int gb_h_loop2(const int64_t* args_host, int n_args, int nsteps, int final_compact, void* stream);
 int gb_h_loop2_nargs(void);
 int gb_h_loop2_state_words(void);
+/* sharded run of the same loop (args: rbase = global index of the shard's first residue -- rbins then holds the rows of ALL
+ * ranks --, world, rank, host table u64 [3][world] of every rank's delta / export / flag block inside its gb_peer_alloc'ed
+ * symmetric block, dcap, xcap): slot counters, candidate bitmap and exact table are replicated; per iteration every rank
+ * publishes the keys of the pairs its merges destroyed / created (bpe.py:1924-1950, 1992-2006) and replays the other
+ * ranks' over NVLink / NVSwitch loads inside the kernel; per period the exact (key, count, example window) lists.  This
+ * replaces the reference's single-process _geo_dict with one replicated priority structure -- "pair counts combined ...
+ * merges applied locally" (north_star). */
+int64_t gb_h_loop2_delta_bytes(int64_t dcap);
+int64_t gb_h_loop2_export_bytes(int64_t xcap);
+int64_t gb_h_loop2_flag_bytes(void);
+int gb_h_loop2_max_world(void);
 /* hsh[j] = content hash under base P of token j's symbol sequence (residue symbols sym, glue symbols glue_res + 1) --
  * the value the merges build with (H(L) P + g) P^|R| + H(R); used to re-key a run after a detected 64-bit collision */
 int gb_rehash_tokens(const uint64_t* sym, const uint32_t* glue_res, const uint32_t* pos, const uint32_t* len, int64_t T,
                      uint64_t P, uint64_t* hsh, void* stream);
+
+/* ---- K7: induce merge replay on the device (bpe.py:1116-1139 BPE.tokenize's loop over the learned merges + step_helper
+ *      1316-1425, for a whole batch of held-out backbones at once).  Token arrays are the medoid-mode SoA in the lazily
+ *      compacted layout (ls = len | extra << 16, 0 = dead entry; dense on entry).  Merge m (host arrays, launch order =
+ *      vocabulary order, merges that cannot occur left out): packed pair key, K medoids with A = bonds + 1 atoms each
+ *      (coordinates f64 at med + mmed_off[m]), class / token id of medoid p at p2cls / p2tid [mp2_off[m] + p].  Per merge:
+ *      occurrences flagged in one pass, each assigned to its nearest medoid (NeRF from the pristine coordinates `vals`,
+ *      Kabsch RMSD, first minimum), overlap rule, in-place merge, (left, right, medoid) appended to the event log.
+ *      st u32 [8] zeroed by the caller except st[2] = first free event slot; rep_start u32 [n_merges + 1] with
+ *      rep_start[0] = st[2]; rep_cnt u32 [n_merges] receives the events of every merge.  Nothing is read back. */
+int gb_induce_replay(uint32_t* cls, uint32_t* glue, const uint32_t* pos, uint32_t* ls, uint32_t* tid, uint8_t* flags,
+                     uint8_t* rmark, uint32_t* aux, int64_t N, const double* vals, int64_t ld, const uint32_t* bb,
+                     const int64_t* offsets, const double* f3tab, int n_merges, const uint64_t* mkey_host,
+                     const int* mK_host, const int* mA_host, const int* mnres_host, const int64_t* mmed_off_host,
+                     const int64_t* mp2_off_host, const double* med, const uint32_t* p2cls, const uint32_t* p2tid,
+                     uint32_t* occ_j, uint32_t* occ_r, uint32_t* ev_left, uint32_t* ev_right, uint32_t* ev_p,
+                     int64_t evcap, uint32_t* st, uint32_t* rep_start, uint32_t* rep_cnt, void* stream);
+int gb_induce_max_atoms(void);
 
 /* ---- K4/K5/K6: NeRF windows, Kabsch RMSD, medoid assignment (tokenizer.py:347-363, nerf.py:84-210,
  *      angles_and_coords.py:238-317, algo.py:8-65,170-181, bpe.py:646-657) -------------------------- */

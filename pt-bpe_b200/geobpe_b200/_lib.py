@@ -53,8 +53,14 @@ SIGNATURES = {
     "gb_h_loop_nargs": [],
     "gb_h_loop2": [P, I32, I32, I32, P],
     "gb_h_loop2_nargs": [],
+    "gb_induce_replay": [P] * 8 + [I64, P, I64, P, P, P, I32] + [P] * 6 + [P, P, P] + [P] * 5 + [I64, P, P, P, P],
+    "gb_induce_max_atoms": [],
     "gb_rehash_tokens": [P, P, P, P, I64, U64, P, P],
     "gb_h_loop2_state_words": [],
+    "gb_h_loop2_delta_bytes": [I64],
+    "gb_h_loop2_export_bytes": [I64],
+    "gb_h_loop2_flag_bytes": [],
+    "gb_h_loop2_max_world": [],
     "gb_h_loop_part": [P, I32, I32, I32, P],
     "gb_h_loop_xbuf_elems": [],
     "gb_h_loop_sbuf_bytes": [I32],
@@ -75,7 +81,8 @@ SIGNATURES = {
     "gb_sm_count": [],
     "gb_select_scratch_elems": [I64],
 }
-_RESTYPES = {"gb_last_error": C.c_char_p, "gb_select_scratch_elems": I64, "gb_h_loop_xbuf_elems": I64, "gb_h_loop_sbuf_bytes": I64}
+_RESTYPES = {"gb_last_error": C.c_char_p, "gb_select_scratch_elems": I64, "gb_h_loop2_delta_bytes": I64,
+             "gb_h_loop2_export_bytes": I64, "gb_h_loop2_flag_bytes": I64, "gb_h_loop_xbuf_elems": I64, "gb_h_loop_sbuf_bytes": I64}
 
 _lib = None
 launches = 0  # kernels launched through the C ABI (bench.py reports it)

@@ -20,6 +20,13 @@
 //   The period ends (and the next one starts on the device, no host round trip) when the best exact count falls below
 //   thr, a non-candidate slot reaches thr, the table / list fills up or a quarter of the entries is dead (compaction).
 //
+// Sharded run (world > 1, one process per GPU, backbones split by contiguous ranges): slot counters, candidate bitmap and
+// the exact table are REPLICATED -- every rank holds the global counts -- and kept identical by exchanging, per iteration,
+// only the keys of the pairs each rank's merges destroyed / created (a few per merge) through peer memory (CUDA IPC
+// blocks; release / acquire flags; loads over NVLink inside this kernel); per period the ranks' exact (key, count,
+// example window) lists.  Every rank therefore takes the same decision from its own copy: no exchange for the argmax or
+// the tie-break (rbins of all ranks are replicated once at start so that any rank can order any key).
+//
 // Phases are separated by grid-wide barriers; every branch that decides whether a barrier is executed depends only on
 // state words that were written before the previous barrier and are not written again before the next one.
 #include <cooperative_groups.h>
@@ -28,6 +35,8 @@
 #include "k_hl_json.cuh"
 namespace cg = cooperative_groups;
 
+#define H2_MAXW 16               // ranks of a sharded run
+#define H2_TIMEOUT_NS 20000000000ull
 #define H2_THREADS 512
 #define H2_TB_CAP 128            // ties resolved on the device
 #define H2_BLK_LIST 512          // candidate pairs staged per CTA before one append to the global list
@@ -44,11 +53,12 @@ enum {
   H2_MISMATCH, H2_NEWT, H2_OVF, H2_ERR, H2_HALT_STEP, H2_NTMAX, H2_CMPT, H2_FRESH, H2_ND, H2_NZ, H2_MPREV,
   H2_ST_PERIODS, H2_ST_CROSS, H2_ST_INCONCL, H2_ST_COMPACT, H2_ST_R2, H2_ST_FULL, H2_ST_LOOPS, H2_PERIOD_LEN,
   H2_ST_MAXNCL, H2_ST_MAXND, H2_ST_MAXNCAND, H2_ST_TIES,
+  H2_HALT_REQ, H2_PERIOD_REQ, H2_NDEATH, H2_NBIRTH, H2_DSEQ, H2_XSEQ, H2_ST_WAIT_US,
   H2_WORDS = 64
 };
 // hs64: [0] popped key, [1] spare, [2..] nanoseconds accumulated per phase (block 0's view)
 enum { H2_TM_PS = 2, H2_TM_P1, H2_TM_P2, H2_TM_P3, H2_TM_P4, H2_TM_P5, H2_TM_CMP, H2_TM_CAND,
-       H2_TW_P2 /* block 0's own work (before the barrier) */, H2_TW_P3, H2_TW_P4, H2_TW_P5, H2_W64 = 16 };
+       H2_TW_P2 /* block 0's own work (before the barrier) */, H2_TW_P3, H2_TW_P4, H2_TW_P5, H2_TM_XCH, H2_W64 = 16 };
 
 struct H2Args {
   u32* hs; u64* hs64;
@@ -59,12 +69,64 @@ struct H2Args {
   u64* tk; u32* tc; u32* tr0; u32* tnres; u32* tlist; i64 M;
   u64* cl_key; u32* cl_j;
   u32* occ_j; u32* occ_r;
-  char* strbuf; int stride; const u16* rank;      // rank u16 [2][1024]: order of the element strings "<v>," / "<v>]"
+  char* strbuf; int stride; const u16* erank;     // erank u16 [2][1024]: order of the element strings "<v>," / "<v>]"
   u32* ev_left; u32* ev_right; u32* ev_p;
   u64* log_key; u32* log_cnt; u32* log_r0; u32* log_nres; u32* log_evs; u32* log_nk;
   u32 thr_num;                    // candidate threshold = thr_num / 16 of the top slot count
   u32 max_loops;
+  // sharded run
+  u32 rbase;                      // global residue index of this shard's residue 0 (rbins holds every rank's rows)
+  int world, rank;
+  u64 peer_d[H2_MAXW];            // every rank's delta blocks   [2 parities][H2D header | deaths | births]
+  u64 peer_x[H2_MAXW];            // every rank's export blocks  [2 parities][header | key, count, r0, nres]
+  u64 peer_f[H2_MAXW];            // every rank's flag rows      u32 [2 stages][H2_MAXW]
+  u32 dcap, xcap;
 };
+
+// ---- peer memory: release / acquire flags and loads that bypass L1 (another GPU writes these addresses) ------------------
+__device__ __forceinline__ void h2p_st_release(u32* p, u32 v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ u32 h2p_ld_acquire(const u32* p) {
+  u32 v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ u32 h2p_ld32(const u32* p) {
+  u32 v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ u64 h2p_ld64(const u64* p) {
+  u64 v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+// delta block of one parity: u32 hdr[8] = {nocc, halt_req, period_req, n_deaths, n_births}, u64 dkey[dcap], u64 bkey[dcap],
+// u32 br0[dcap], u32 bnres[dcap]
+struct H2D { u32* hdr; u64* dkey; u64* bkey; u32* br0; u32* bnres; };
+__device__ __forceinline__ size_t h2d_bytes(u32 dcap) { return 32 + (size_t)dcap * 24; }
+__device__ __forceinline__ H2D h2d_at(u64 base, u32 dcap, u32 par) {
+  unsigned char* p = reinterpret_cast<unsigned char*>(base) + (size_t)par * h2d_bytes(dcap);
+  H2D d;
+  d.hdr = reinterpret_cast<u32*>(p);
+  d.dkey = reinterpret_cast<u64*>(p + 32);
+  d.bkey = d.dkey + dcap;
+  d.br0 = reinterpret_cast<u32*>(d.bkey + dcap);
+  d.bnres = d.br0 + dcap;
+  return d;
+}
+// export block of one parity: u32 hdr[8] = {n, halt_req}, u64 key[xcap], u32 cnt[xcap], u32 r0[xcap], u32 nres[xcap]
+struct H2X { u32* hdr; u64* key; u32* cnt; u32* r0; u32* nres; };
+__device__ __forceinline__ size_t h2x_bytes(u32 xcap) { return 32 + (size_t)xcap * 20; }
+__device__ __forceinline__ H2X h2x_at(u64 base, u32 xcap, u32 par) {
+  unsigned char* p = reinterpret_cast<unsigned char*>(base) + (size_t)par * h2x_bytes(xcap);
+  H2X x;
+  x.hdr = reinterpret_cast<u32*>(p);
+  x.key = reinterpret_cast<u64*>(p + 32);
+  x.cnt = reinterpret_cast<u32*>(x.key + xcap);
+  x.r0 = x.cnt + xcap;
+  x.nres = x.r0 + xcap;
+  return x;
+}
 
 __device__ __forceinline__ u32 h2_ld(const u32* p) { return *reinterpret_cast<const volatile u32*>(p); }
 __device__ __forceinline__ u64 h2_now() {
@@ -99,6 +161,27 @@ __device__ __forceinline__ i64 h2_table_add(const H2Args& a, u64 key, u32 r0, u3
   a.hs[H2_OVF] = 1u;
   return -1;
 }
+// add c occurrences of a key counted by another rank (its example window is a global residue range: valid everywhere)
+__device__ __forceinline__ void h2_table_addc(const H2Args& a, u64 key, u32 c, u32 r0, u32 nres) {
+  const u64 mask = (u64)(a.M - 1);
+  u64 s = gb_mix64(key) & mask;
+  for (int probe = 0; probe < H2_PROBES; ++probe) {
+    u64 prev = *reinterpret_cast<volatile u64*>(&a.tk[s]);
+    if (prev == GB_EMPTY_KEY) {
+      prev = atomicCAS(&a.tk[s], (u64)GB_EMPTY_KEY, key);
+      if (prev == GB_EMPTY_KEY) {
+        a.tr0[s] = r0; a.tnres[s] = nres;
+        const u32 id = atomicAdd(&a.hs[H2_ND], 1u);
+        if ((i64)id < a.M) a.tlist[id] = (u32)s;
+        if ((u64)id * 2u + 2u > (u64)a.M) a.hs[H2_OVF] = 1u;
+        prev = key;
+      }
+    }
+    if (prev == key) { atomicAdd(&a.tc[s], c); return; }
+    s = (s + 1) & mask;
+  }
+  a.hs[H2_OVF] = 1u;
+}
 __device__ __forceinline__ i64 h2_table_find(const H2Args& a, u64 key) {
   const u64 mask = (u64)(a.M - 1);
   u64 s = gb_mix64(key) & mask;
@@ -129,6 +212,11 @@ __device__ __forceinline__ u64 h2_pair_key(const H2Args& a, const H2Tok& t, u32 
 __device__ __forceinline__ void h2_death(const H2Args& a, u64 key) {
   const u32 s = gb_slot_of(key, 64 - a.log2ns);
   atomicSub(&a.slots[s], 1u);
+  if (a.world > 1) {                               // the other ranks replay it on their copies
+    const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, a.hs[H2_DSEQ] & 1u);
+    const u32 g = atomicAdd(&a.hs[H2_NDEATH], 1u);
+    if (g < a.dcap) d.dkey[g] = key; else a.hs[H2_HALT_REQ] = H2_HALT_TABLE;
+  }
   if (h2_cbit(a.cbit, s)) {
     const i64 t = h2_table_find(a, key);
     if (t < 0) a.hs[H2_ERR] = 1u; else atomicSub(&a.tc[t], 1u);
@@ -137,14 +225,125 @@ __device__ __forceinline__ void h2_death(const H2Args& a, u64 key) {
 __device__ __forceinline__ void h2_birth(const H2Args& a, u64 key, u32 left, u32 r0, u32 nres, u32 thr) {
   const u32 s = gb_slot_of(key, 64 - a.log2ns);
   const u32 old = atomicAdd(&a.slots[s], 1u);
+  const bool dist = a.world > 1;
+  // (sharded: whatever ends a period must end it on every rank -- requests travel with the deltas, the threshold test runs on
+  //  the final global counters in the next iteration's first phase)
+  if (dist) {
+    const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, a.hs[H2_DSEQ] & 1u);
+    const u32 g = atomicAdd(&a.hs[H2_NBIRTH], 1u);
+    if (g < a.dcap) { d.bkey[g] = key; d.br0[g] = r0; d.bnres[g] = nres; } else a.hs[H2_HALT_REQ] = H2_HALT_TABLE;
+  }
   if (h2_cbit(a.cbit, s)) {
-    if (h2_table_add(a, key, r0, nres) < 0) a.hs[H2_PERIOD_OK] = 0u;
+    if (h2_table_add(a, key, r0, nres) < 0) { if (dist) a.hs[H2_HALT_REQ] = H2_HALT_TABLE; else a.hs[H2_PERIOD_OK] = 0u; }
     const u32 g = atomicAdd(&a.hs[H2_NCL], 1u);
     if (g < a.hs[H2_CLCAP]) { a.cl_key[g] = key; a.cl_j[g] = left; }
-    else { a.hs[H2_PERIOD_OK] = 0u; a.hs[H2_ST_FULL] = 1u; }
-  } else if (old + 1u >= thr) {
+    else { if (dist) a.hs[H2_PERIOD_REQ] = 1u; else a.hs[H2_PERIOD_OK] = 0u; a.hs[H2_ST_FULL] = 1u; }
+  } else if (!dist && old + 1u >= thr) {
     a.hs[H2_PERIOD_OK] = 0u;             // a key outside the table may have reached the threshold: new period
     a.hs[H2_ST_CROSS] = 1u;
+  }
+}
+
+// ---- sharded run: signal / wait, the per-iteration delta exchange, the per-period table exchange --------------------------
+// stage 0 = deltas, 1 = exports; seq = this use's sequence number (its low bit selects the buffer parity)
+__device__ void h2_signal_wait(const H2Args& a, int stage, u32 seq) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    __threadfence_system();
+    for (int q = 0; q < a.world; ++q)
+      h2p_st_release(reinterpret_cast<u32*>(a.peer_f[q]) + stage * H2_MAXW + a.rank, seq);
+    const u32* mine = reinterpret_cast<const u32*>(a.peer_f[a.rank]) + stage * H2_MAXW;
+    const u64 t0 = h2_now();
+    bool ok = a.hs[H2_HALT] != H2_HALT_PEER;
+    for (int q = 0; q < a.world && ok; ++q)
+      while ((int)(h2p_ld_acquire(mine + q) - seq) < 0)
+        if (h2_now() - t0 > H2_TIMEOUT_NS) { h2_halt(a.hs, H2_HALT_PEER); ok = false; break; }
+    a.hs[H2_ST_WAIT_US] += (u32)((h2_now() - t0) / 1000ull);
+  }
+}
+// replay the other ranks' deltas of this iteration on the local copies; block 0 thread 0 folds the headers
+__device__ void h2_apply_remote(const H2Args& a, u32 par, u32 cnt) {
+  u32* hs = a.hs;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    u32 tot = 0, halt = 0, per = 0;
+    for (int r = 0; r < a.world; ++r) {
+      const H2D d = h2d_at(a.peer_d[r], a.dcap, par);
+      tot += h2p_ld32(d.hdr + 0);
+      const u32 h = h2p_ld32(d.hdr + 1);
+      if (!halt) halt = h;
+      per |= h2p_ld32(d.hdr + 2);
+    }
+    if (halt) h2_halt(hs, halt);
+    else if (tot != cnt) h2_halt(hs, H2_HALT_COUNT);
+    if (per) hs[H2_PERIOD_OK] = 0u;
+  }
+  const i64 gtid = (i64)blockIdx.x * H2_THREADS + threadIdx.x, gsz = (i64)gridDim.x * H2_THREADS;
+  for (int r = 0; r < a.world; ++r) {
+    if (r == a.rank) continue;
+    const H2D d = h2d_at(a.peer_d[r], a.dcap, par);
+    const u32 nd = min(h2p_ld32(d.hdr + 3), a.dcap), nb = min(h2p_ld32(d.hdr + 4), a.dcap);
+    for (i64 i = gtid; i < nd; i += gsz) {
+      const u64 key = h2p_ld64(d.dkey + i);
+      const u32 s = gb_slot_of(key, 64 - a.log2ns);
+      atomicSub(&a.slots[s], 1u);
+      if (h2_cbit(a.cbit, s)) {
+        const i64 t = h2_table_find(a, key);
+        if (t < 0) hs[H2_ERR] = 1u; else atomicSub(&a.tc[t], 1u);
+      }
+    }
+    for (i64 i = gtid; i < nb; i += gsz) {
+      const u64 key = h2p_ld64(d.bkey + i);
+      const u32 s = gb_slot_of(key, 64 - a.log2ns);
+      atomicAdd(&a.slots[s], 1u);
+      if (h2_cbit(a.cbit, s)) h2_table_addc(a, key, 1u, h2p_ld32(d.br0 + i), h2p_ld32(d.bnres + i));
+    }
+  }
+}
+// threshold test on the FINAL global counters: did a pair created in the previous iteration (on any rank) lift a slot
+// outside the candidate set to the threshold?  (runs beside the argmax of the next iteration; blocks 1..)
+__device__ void h2_cross_check(const H2Args& a, u32 par, u32 thr) {
+  if (blockIdx.x == 0 || gridDim.x < 2) return;
+  const i64 gtid = (i64)(blockIdx.x - 1) * H2_THREADS + threadIdx.x, gsz = (i64)(gridDim.x - 1) * H2_THREADS;
+  for (int r = 0; r < a.world; ++r) {
+    const H2D d = h2d_at(a.peer_d[r], a.dcap, par);
+    const u32 nb = min(h2p_ld32(d.hdr + 4), a.dcap);
+    for (i64 i = gtid; i < nb; i += gsz) {
+      const u32 s = gb_slot_of(h2p_ld64(d.bkey + i), 64 - a.log2ns);
+      if (!h2_cbit(a.cbit, s) && a.slots[s] >= thr) { a.hs[H2_PERIOD_OK] = 0u; a.hs[H2_ST_CROSS] = 1u; }
+    }
+  }
+}
+// period start: every rank publishes the exact (key, count, example window) entries of its shard; all ranks add the others'
+__device__ void h2_export_table(const H2Args& a, u32 par) {
+  const H2X x = h2x_at(a.peer_x[a.rank], a.xcap, par);
+  const u32 nd = min(h2_ld(a.hs + H2_ND), (u32)a.M);
+  const i64 gtid = (i64)blockIdx.x * H2_THREADS + threadIdx.x, gsz = (i64)gridDim.x * H2_THREADS;
+  for (i64 i = gtid; i < nd && i < a.xcap; i += gsz) {
+    const u32 sl = a.tlist[i];
+    x.key[i] = a.tk[sl]; x.cnt[i] = a.tc[sl]; x.r0[i] = a.tr0[sl]; x.nres[i] = a.tnres[sl];
+  }
+  if (gtid == 0) {
+    x.hdr[0] = min(nd, a.xcap);
+    x.hdr[1] = (nd > a.xcap || a.hs[H2_OVF]) ? (u32)H2_HALT_TABLE : (a.hs[H2_NCL] > a.hs[H2_CLCAP] ? (u32)H2_HALT_CAND : 0u);
+  }
+}
+__device__ void h2_import_tables(const H2Args& a, u32 par) {
+  const i64 gtid = (i64)blockIdx.x * H2_THREADS + threadIdx.x, gsz = (i64)gridDim.x * H2_THREADS;
+  if (gtid == 0) {
+    u32 halt = 0;
+    for (int r = 0; r < a.world; ++r) {
+      const u32 h = h2p_ld32(h2x_at(a.peer_x[r], a.xcap, par).hdr + 1);
+      if (!halt) halt = h;
+    }
+    if (halt) h2_halt(a.hs, halt);
+  }
+  for (int r = 0; r < a.world; ++r) {
+    if (r == a.rank) continue;
+    const H2X x = h2x_at(a.peer_x[r], a.xcap, par);
+    const u32 n = min(h2p_ld32(x.hdr + 0), a.xcap);
+    for (i64 i = gtid; i < n; i += gsz) {
+      const u32 c = h2p_ld32(x.cnt + i);
+      if (c) h2_table_addc(a, h2p_ld64(x.key + i), c, h2p_ld32(x.r0 + i), h2p_ld32(x.nres + i));
+    }
   }
 }
 
@@ -298,7 +497,7 @@ __device__ void h2_cand_pass(const H2Args& a, int par, u32 n, u32* s_set, u64* s
         const u32 j = (u32)(j0 + e);
         const u32 l = t.ls[j];
         const u32 r = j + 1u + (l >> 16);
-        h2_table_add(a, key[e], t.pos[j], (l & 0xFFFFu) + (t.ls[r] & 0xFFFFu));
+        h2_table_add(a, key[e], a.rbase + t.pos[j], (l & 0xFFFFu) + (t.ls[r] & 0xFFFFu));
         const u32 q = atomicAdd(&s_misc[0], 1u);           // block-local list first: one global atomic per CTA at the end
         if (q < H2_BLK_LIST) { s_key[q] = key[e]; s_j[q] = j; }
         else {
@@ -403,9 +602,19 @@ __device__ void h2_period_start(const H2Args& a, cg::grid_group& grid, unsigned 
     h2_cand_pass<CS>(a, par, ncand, s_set, s_key, s_j, s_misc);
   }
   grid.sync();
+  if (a.world > 1) {       // the table becomes global: every rank adds the other ranks' exact counts of the same candidate slots
+    const u32 xseq = h2_ld(hs + H2_XSEQ) + 1u;
+    h2_export_table(a, xseq & 1u);
+    grid.sync();
+    h2_signal_wait(a, 1, xseq);
+    grid.sync();
+    h2_import_tables(a, xseq & 1u);
+    if (t0) hs[H2_XSEQ] = xseq;
+    grid.sync();
+  }
   if (t0) {
     if (hs[H2_OVF]) h2_halt(hs, H2_HALT_TABLE);
-    else if (hs[H2_NCL] > hs[H2_CLCAP]) h2_halt(hs, H2_HALT_CAND);
+    else if (a.world == 1 && hs[H2_NCL] > hs[H2_CLCAP]) h2_halt(hs, H2_HALT_CAND);
     hs[H2_THR] = thr; hs[H2_THR_REQ] = 0; hs[H2_PERIOD_OK] = 1; hs[H2_FRESH] = 1; hs[H2_PERIOD_LEN] = 0;
     if (req) hs[H2_ST_R2] += 1u;
     hs[H2_ST_MAXNCL] = max(hs[H2_ST_MAXNCL], hs[H2_NCL]); hs[H2_ST_MAXND] = max(hs[H2_ST_MAXND], hs[H2_ND]);
@@ -467,7 +676,7 @@ __device__ void h2_decide(const H2Args& a, unsigned char* smem) {
     //    "phi": [..nres-1], "psi": [..m], "tau": [..nres]}           (m = nres - 1 when the window ends its backbone)
     // i.e. nine lists with fixed headers.  Each list element prints as "<v>, " or "<v>]": these element strings form a
     // prefix-free set, so the byte order of two key strings equals the lexicographic order of their sequences of element
-    // ranks (a.rank: position of "<v>," / "<v>]" among all element strings in byte order).  One warp writes a key's rank
+    // ranks (a.erank: position of "<v>," / "<v>]" among all element strings in byte order).  One warp writes a key's rank
     // sequence in parallel; the tournament compares 32 ranks per step.
     int my_len = 0;
     for (u32 i = threadIdx.x; i < nt; i += H2_THREADS) {
@@ -506,7 +715,7 @@ __device__ void h2_decide(const H2Args& a, unsigned char* smem) {
 #pragma unroll
           for (int q = 0; q < 8; ++q) if (g == (u32)q && k >= seg_n[q]) { k -= seg_n[q]; g = q + 1; }
           const u32 v = seg_s[g] ? (u32)__ldg(a.rbins + (i64)seg_s[g] * a.R + r0 + k) : 0u;
-          code = __ldg(a.rank + ((k == seg_n[g] - 1u) ? 1024u : 0u) + min(v, 1023u));
+          code = __ldg(a.erank + ((k == seg_n[g] - 1u) ? 1024u : 0u) + min(v, 1023u));
         }
         cb[(size_t)i * cstride + p] = code;
       }
@@ -540,6 +749,8 @@ __device__ void h2_decide(const H2Args& a, unsigned char* smem) {
     if (nt > 1) hs[H2_ST_TIES] += 1u;
     hs[H2_FRESH] = 0; hs[H2_P1] = 0;
     hs[H2_NOCC] = 0; hs[H2_MISMATCH] = 0; hs[H2_NEWT] = 0;
+    hs[H2_NDEATH] = 0; hs[H2_NBIRTH] = 0; hs[H2_HALT_REQ] = 0; hs[H2_PERIOD_REQ] = 0;
+    if (a.world > 1) hs[H2_DSEQ] += 1u;            // this iteration's delta exchange (low bit = buffer parity)
   }
 }
 
@@ -573,7 +784,7 @@ __device__ void h2_deaths(const H2Args& a, const H2Tok& t, u32 nocc, u32 ref_r0,
   for (u32 i = wid; i < nocc; i += nw) {
     const u32 j0 = a.occ_j[i], r0tok = a.occ_r[i];
     // every occurrence's window must hold the example window's bins (a 64-bit content-hash collision is detected here)
-    const u32 r0 = t.pos[j0];
+    const u32 r0 = a.rbase + t.pos[j0];
     bool bad = ((t.ls[j0] & 0xFFFFu) + (t.ls[r0tok] & 0xFFFFu)) != nres;
     if (!bad && r0 != ref_r0) {
       for (u32 e = lane; e < 6u * nres; e += 32u) {
@@ -636,11 +847,11 @@ __device__ void h2_births_end(const H2Args& a, const H2Tok& t, u32 nocc, u64 win
     const u32 l = t.ls[j], gj = t.glue[j];
     if (!(gj & GB_LAST_FLAG)) {                // (new token, right neighbour)
       const u32 x = j + 1u + (l >> 16);
-      h2_birth(a, h2_pair_key(a, t, j, x), j, t.pos[j], (l & 0xFFFFu) + (t.ls[x] & 0xFFFFu), thr);
+      h2_birth(a, h2_pair_key(a, t, j, x), j, a.rbase + t.pos[j], (l & 0xFFFFu) + (t.ls[x] & 0xFFFFu), thr);
     }
     const u32 q = h2_prev_live(t, j);          // (left neighbour, new token); a freshly merged left neighbour has counted
     if (q != 0xFFFFFFFFu && !(t.glue[q] & GB_LAST_FLAG) && t.tid[q] != new_tid)       // this pair as its own right pair
-      h2_birth(a, h2_pair_key(a, t, q, j), q, t.pos[q], (t.ls[q] & 0xFFFFu) + (l & 0xFFFFu), thr);
+      h2_birth(a, h2_pair_key(a, t, q, j), q, a.rbase + t.pos[q], (t.ls[q] & 0xFFFFu) + (l & 0xFFFFu), thr);
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     const u32 nk = hs[H2_NEWT], cnt = hs[H2_WIN_CNT];
@@ -650,7 +861,9 @@ __device__ void h2_births_end(const H2Args& a, const H2Tok& t, u32 nocc, u64 win
     atomicSub(&a.slots[gb_slot_of(win, 64 - a.log2ns)], cnt);
     const u32 T = hs[H2_T] - nk;
     hs[H2_T] = T; hs[H2_EVN] = ev0 + nk; hs[H2_NTOK] = new_tid + 1u; hs[H2_MPREV] = cnt; hs[H2_PERIOD_LEN] += 1u;
-    if ((u64)(hs[H2_N] - T) * 4ull > (u64)hs[H2_N]) hs[H2_PERIOD_OK] = 0u;      // compaction is due
+    if ((u64)(hs[H2_N] - T) * 4ull > (u64)hs[H2_N]) {                           // compaction is due
+      if (a.world > 1) hs[H2_PERIOD_REQ] = 1u; else hs[H2_PERIOD_OK] = 0u;
+    }
     hs[H2_STEP] = step + 1u;
     if (step + 1u >= hs[H2_LOGCAP]) h2_halt(hs, H2_HALT_STEPS);
   }
@@ -677,7 +890,10 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
       continue;
     }
     u64 tm = t0 ? h2_now() : 0ull;
+    const bool dist = a.world > 1;
+    const u32 dseq0 = dist ? h2_ld(hs + H2_DSEQ) : 0u;
     h2_decide(a, smem);
+    if (dist) h2_cross_check(a, dseq0 & 1u, h2_ld(hs + H2_THR));      // (previous iteration's created pairs, blocks 1..)
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P1] += n - tm; tm = n; }
     const u32 p1 = h2_ld(hs + H2_P1);
@@ -691,6 +907,12 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
       grid.sync();
       continue;
     }
+    if (dist && !h2_ld(hs + H2_PERIOD_OK)) {         // a created pair lifted a slot to the threshold: the decision is void
+      grid.sync();
+      if (t0 && h2_ld(hs + H2_DSEQ) != dseq0) hs[H2_DSEQ] = dseq0;   // (no exchange happened for the void decision)
+      grid.sync();
+      continue;
+    }
     const int par = (int)h2_ld(hs + H2_PAR);
     const H2Tok t = h2_tok(a, par);
     const u64 win = *reinterpret_cast<volatile u64*>(&a.hs64[0]);
@@ -700,21 +922,29 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
     if (t0) a.hs64[H2_TW_P2] += h2_now() - tm;
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P2] += n - tm; tm = n; }
-    const u32 nocc = h2_ld(hs + H2_NOCC);
-    const u32 bad = nocc != cnt ? H2_HALT_COUNT : ((u64)ev0 + nocc > (u64)h2_ld(hs + H2_EVCAP) ? H2_HALT_EVLOG : 0u);
-    if (bad) {                                       // nothing has been modified yet: remove the marks, stop
+    u32 nocc = h2_ld(hs + H2_NOCC);
+    const bool evfull = (u64)ev0 + nocc > (u64)h2_ld(hs + H2_EVCAP);
+    if (!dist) {
+      const u32 bad = nocc != cnt ? H2_HALT_COUNT : (evfull ? H2_HALT_EVLOG : 0u);
+      if (bad) {                                     // nothing has been modified yet: remove the marks, stop
+        h2_unflag(a, nocc);
+        grid.sync();
+        if (t0) h2_halt(hs, bad);
+        grid.sync();
+        continue;
+      }
+    } else if (evfull) {                             // fatal on this rank: the iteration runs empty here, every rank stops after the exchange
       h2_unflag(a, nocc);
       grid.sync();
-      if (t0) h2_halt(hs, bad);
-      grid.sync();
-      continue;
+      if (t0) { hs[H2_HALT_REQ] = H2_HALT_EVLOG; hs[H2_NOCC] = 0; }
+      nocc = 0;
     }
     h2_deaths(a, t, nocc, ref_r0, nres);
     if (t0) a.hs64[H2_TW_P3] += h2_now() - tm;
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P3] += n - tm; tm = n; }
     const u32 bad3 = h2_ld(hs + H2_MISMATCH) ? H2_HALT_COLLISION : (h2_ld(hs + H2_ERR) ? H2_HALT_INTERNAL : 0u);
-    if (bad3) {                                      // the token arrays are untouched (counters are rebuilt by the host)
+    if (bad3 && !dist) {                             // the token arrays are untouched (counters are rebuilt by the host)
       h2_unflag(a, nocc);
       grid.sync();
       if (t0) h2_halt(hs, bad3);
@@ -728,7 +958,21 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
     h2_births_end(a, t, nocc, win, new_tid, thr, step, ev0);
     if (t0) a.hs64[H2_TW_P5] += h2_now() - tm;
     grid.sync();
-    if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P5] += n - tm; hs[H2_ST_LOOPS] += 1u; }
+    if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P5] += n - tm; tm = n; hs[H2_ST_LOOPS] += 1u; }
+    if (dist) {
+      // publish this rank's deltas (header last), wait for every rank's, replay the others' on the local copies
+      const u32 seq = dseq0 + 1u;
+      if (t0) {
+        const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, seq & 1u);
+        d.hdr[0] = hs[H2_NOCC]; d.hdr[1] = hs[H2_HALT_REQ] ? hs[H2_HALT_REQ] : (bad3 ? bad3 : 0u); d.hdr[2] = hs[H2_PERIOD_REQ];
+        d.hdr[3] = hs[H2_NDEATH]; d.hdr[4] = hs[H2_NBIRTH];
+      }
+      h2_signal_wait(a, 0, seq);
+      grid.sync();
+      h2_apply_remote(a, seq & 1u, cnt);
+      grid.sync();
+      if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_XCH] += n - tm; }
+    }
   }
   if (final_compact) {          // the host reads dense arrays (ls = plain residue counts)
     const u32 N = h2_ld(hs + H2_N), T = h2_ld(hs + H2_T);
@@ -743,8 +987,9 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
 // ---- host entry ------------------------------------------------------------------------------------------------------
 enum { HB_HS = 0, HB_HS64, HB_HSH0, HB_HSH1, HB_GLUE0, HB_GLUE1, HB_POS0, HB_POS1, HB_LEN0, HB_LEN1, HB_TID0, HB_TID1,
        HB_FLAGS, HB_RMARK, HB_SCRATCH, HB_POWTAB, HB_P, HB_RBINS, HB_R, HB_SLOTS, HB_LOG2NS, HB_BMAX, HB_CAND, HB_CAP, HB_CBIT,
-       HB_TK, HB_TC, HB_TR0, HB_TNRES, HB_TLIST, HB_M, HB_CLKEY, HB_CLJ, HB_OCCJ, HB_OCCR, HB_STRBUF, HB_STRIDE, HB_RANK, HB_EVL, HB_EVR, HB_EVP,
-       HB_LKEY, HB_LCNT, HB_LR0, HB_LNRES, HB_LEVS, HB_LNK, HB_THRNUM, HB_STREAMING, HB_CTAS, HB_N };
+       HB_TK, HB_TC, HB_TR0, HB_TNRES, HB_TLIST, HB_M, HB_CLKEY, HB_CLJ, HB_OCCJ, HB_OCCR, HB_STRBUF, HB_STRIDE, HB_ERANK, HB_EVL, HB_EVR, HB_EVP,
+       HB_LKEY, HB_LCNT, HB_LR0, HB_LNRES, HB_LEVS, HB_LNK, HB_THRNUM, HB_STREAMING, HB_CTAS,
+       HB_RBASE, HB_WORLD, HB_RANK, HB_PEERS /* host table u64 [3][world]: delta / export / flag block of every rank */, HB_DCAP, HB_XCAP, HB_N };
 
 __global__ void h2_set_target(u32* hs, u32 nsteps) { hs[H2_TARGET] = hs[H2_STEP] + nsteps; }
 
@@ -770,14 +1015,25 @@ extern "C" int gb_h_loop2(const int64_t* b, int n_args, int nsteps, int final_co
   a.cap = (u32)b[HB_CAP]; a.cbit = (u32*)b[HB_CBIT];
   a.tk = (u64*)b[HB_TK]; a.tc = (u32*)b[HB_TC]; a.tr0 = (u32*)b[HB_TR0]; a.tnres = (u32*)b[HB_TNRES]; a.tlist = (u32*)b[HB_TLIST]; a.M = b[HB_M];
   a.cl_key = (u64*)b[HB_CLKEY]; a.cl_j = (u32*)b[HB_CLJ]; a.occ_j = (u32*)b[HB_OCCJ]; a.occ_r = (u32*)b[HB_OCCR];
-  a.strbuf = (char*)b[HB_STRBUF]; a.stride = (int)b[HB_STRIDE]; a.rank = (const u16*)b[HB_RANK];
+  a.strbuf = (char*)b[HB_STRBUF]; a.stride = (int)b[HB_STRIDE]; a.erank = (const u16*)b[HB_ERANK];
   a.ev_left = (u32*)b[HB_EVL]; a.ev_right = (u32*)b[HB_EVR]; a.ev_p = (u32*)b[HB_EVP];
   a.log_key = (u64*)b[HB_LKEY]; a.log_cnt = (u32*)b[HB_LCNT]; a.log_r0 = (u32*)b[HB_LR0]; a.log_nres = (u32*)b[HB_LNRES];
   a.log_evs = (u32*)b[HB_LEVS]; a.log_nk = (u32*)b[HB_LNK];
   a.thr_num = (u32)b[HB_THRNUM];
   a.max_loops = (u32)(4 * nsteps + 64);
+  a.rbase = (u32)b[HB_RBASE]; a.world = b[HB_WORLD] > 1 ? (int)b[HB_WORLD] : 1; a.rank = (int)b[HB_RANK];
+  a.dcap = (u32)b[HB_DCAP]; a.xcap = (u32)b[HB_XCAP];
+  for (int r = 0; r < H2_MAXW; ++r) a.peer_d[r] = a.peer_x[r] = a.peer_f[r] = 0;
+  if (a.world > 1) {
+    const u64* pt = (const u64*)b[HB_PEERS];
+    if (!pt || a.world > H2_MAXW || a.rank < 0 || a.rank >= a.world || a.dcap < 1024 || a.xcap < 1024) {
+      gb_set_error("gb_h_loop2: bad sharding arguments (world %d, rank %d, dcap %u, xcap %u)", a.world, a.rank, a.dcap, a.xcap);
+      return -2;
+    }
+    for (int r = 0; r < a.world; ++r) { a.peer_d[r] = pt[r]; a.peer_x[r] = pt[a.world + r]; a.peer_f[r] = pt[2 * a.world + r]; }
+  }
   if (a.log2ns < 12 || a.log2ns > 30 || a.M < 1024 || (a.M & (a.M - 1)) || a.cap < 1 || a.cap > KC_SET / 2 || (a.stride & 127) ||
-      a.thr_num < 1 || a.thr_num > 16 || !a.hs || !a.hs64 || !a.cbit || !a.occ_j || !a.tlist || !a.rank) {
+      a.thr_num < 1 || a.thr_num > 16 || !a.hs || !a.hs64 || !a.cbit || !a.occ_j || !a.tlist || !a.erank) {
     gb_set_error("gb_h_loop2: bad arguments (log2ns %d, M %lld, cap %u, stride %d, thr_num %u)", a.log2ns, (long long)a.M, a.cap,
                  a.stride, a.thr_num);
     return -2;
@@ -825,3 +1081,9 @@ extern "C" int gb_rehash_tokens(const uint64_t* sym, const uint32_t* glue_res, c
   GB_LAUNCH_CK();
   return 0;
 }
+
+// sizes of the symmetric block a sharded run allocates per rank (gb_peer_alloc): [delta x 2 | export x 2 | flags]
+extern "C" int64_t gb_h_loop2_delta_bytes(int64_t dcap) { return 2 * (32 + dcap * 24); }
+extern "C" int64_t gb_h_loop2_export_bytes(int64_t xcap) { return 2 * (32 + xcap * 20); }
+extern "C" int64_t gb_h_loop2_flag_bytes(void) { return 2 * H2_MAXW * 4; }
+extern "C" int gb_h_loop2_max_world(void) { return H2_MAXW; }

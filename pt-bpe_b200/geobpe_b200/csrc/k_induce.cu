@@ -1,0 +1,156 @@
+// K7: device-resident merge replay of induce (BPE.tokenize, bpe.py:1116-1139 with step_helper 1316-1425): every vocabulary
+// merge of a medoid-mode vocabulary applied, in learned order, to ALL held-out backbones at once without a host round trip.
+// Per merge four launches on the lazily compacted token arrays (ls = len | extra << 16, 0 = dead; see k_hloop2.cu):
+//   flag     one streaming pass (cls, glue, ls: 12 B / entry): pairs whose packed key equals the merge's key -> occurrence list
+//   assign   per occurrence: NeRF coordinates of the window from the pristine internal coordinates (rmsd_super_res,
+//            tokenizer.py:347-363, nerf.py:84-210) and Kabsch RMSD to the key's medoids (algo.py:8-65); first minimum wins
+//            (np.argmin, bpe.py:655-657)
+//   apply    overlap rule (bpe.py:1909-1914: the head of every run merges the 1st, 3rd, ... occurrence) + in-place merge: the
+//            left entry takes the assigned medoid's class / token id, the right entry dies; merge events appended
+//   unflag   marks removed, per-merge event range recorded
+// The host passes the merges' parameters as plain arrays; nothing is read back until the whole vocabulary has been replayed.
+#include "common.cuh"
+#include "geom.cuh"
+
+#define KI_AMAX 97               // atoms per window handled on the device (32 residues + 1)
+
+enum { KI_NOCC0 = 0, KI_NOCC1, KI_EVN, KI_ERR, KI_WORDS = 8 };
+
+struct KITok { u32* cls; u32* glue; const u32* pos; u32* ls; u32* tid; };
+
+__global__ void __launch_bounds__(256) ki_flag(KITok t, i64 N, u64 key, u32* __restrict__ st, int par, u32* __restrict__ occ_j,
+                                               u32* __restrict__ occ_r, u8* __restrict__ flags, u8* __restrict__ rmark) {
+  for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < N; j += (i64)gridDim.x * blockDim.x) {
+    const u32 l = t.ls[j];
+    if (l == 0u) continue;
+    const u32 g = t.glue[j];
+    if (g & GB_LAST_FLAG) continue;
+    const u32 r = (u32)j + 1u + (l >> 16);
+    if (gb_key_m(t.cls[j], g, t.cls[r]) != key) continue;
+    const u32 q = atomicAdd(&st[KI_NOCC0 + par], 1u);
+    occ_j[q] = (u32)j; occ_r[q] = r;
+    flags[j] = 1; rmark[r] = 1;
+  }
+}
+
+struct KIGeo { const double* V; i64 ld; const u32* bb; const i64* offsets; const double* f3tab; };
+
+__global__ void __launch_bounds__(128) ki_assign(KITok t, KIGeo g, const u32* __restrict__ st, int par, const u32* __restrict__ occ_j,
+                                                 int nres, int A, const double* __restrict__ med, int K, u32* __restrict__ aux) {
+  const u32 nocc = st[KI_NOCC0 + par];
+  for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < nocc; i += gridDim.x * blockDim.x) {
+    const u32 j = occ_j[i];
+    const i64 r0 = t.pos[j];
+    const i64 ld = g.ld;
+    const double* V = g.V;
+    double c[3 * KI_AMAX];
+    double nca, cac, tau;
+    if (r0 == g.offsets[g.bb[r0]]) {           // the window starts its backbone: first-residue geometry of the token's class
+      const double* f = g.f3tab + 3 * (i64)t.cls[j];
+      nca = f[0]; cac = f[1]; tau = f[2];
+    } else {
+      nca = V[1 * ld + r0 - 1]; cac = V[2 * ld + r0 - 1]; tau = V[6 * ld + r0 - 1];
+    }
+    gb_v3 p0, p1, p2;
+    gb_first_residue(nca, cac, tau, p0, p1, p2);
+    int na = 0;
+    c[0] = p0.x; c[1] = p0.y; c[2] = p0.z; ++na;
+    if (na < A) { c[3] = p1.x; c[4] = p1.y; c[5] = p1.z; ++na; }
+    if (na < A) { c[6] = p2.x; c[7] = p2.y; c[8] = p2.z; ++na; }
+    for (int k = 0; na < A; ++k) {             // (same order of operations as k_window_coords)
+      const i64 r = r0 + k;
+      gb_v3 n = gb_place_dihedral(p0, p1, p2, V[7 * ld + r], V[0 * ld + r], V[4 * ld + r]);
+      c[3 * na] = n.x; c[3 * na + 1] = n.y; c[3 * na + 2] = n.z; ++na;
+      if (na >= A) break;
+      gb_v3 ca = gb_place_dihedral(p1, p2, n, V[8 * ld + r], V[1 * ld + r], V[5 * ld + r]);
+      c[3 * na] = ca.x; c[3 * na + 1] = ca.y; c[3 * na + 2] = ca.z; ++na;
+      if (na >= A) break;
+      gb_v3 cc = gb_place_dihedral(p2, n, ca, V[6 * ld + r], V[2 * ld + r], V[3 * ld + r + 1]);
+      c[3 * na] = cc.x; c[3 * na + 1] = cc.y; c[3 * na + 2] = cc.z; ++na;
+      p0 = n; p1 = ca; p2 = cc;
+    }
+    double bv = INFINITY;
+    u32 bi = 0;
+    for (int m = 0; m < K; ++m) {
+      const double d = gb_kabsch_rmsd(c, med + (i64)m * A * 3, A);
+      if (d < bv) { bv = d; bi = (u32)m; }       // strict <: first index on ties (np.argmin)
+    }
+    aux[j] = bi;
+    (void)nres;
+  }
+}
+
+__global__ void __launch_bounds__(128) ki_apply(KITok t, u32* __restrict__ st, int par, const u32* __restrict__ occ_j,
+                                                const u8* __restrict__ flags, const u8* __restrict__ rmark, const u32* __restrict__ aux,
+                                                const u32* __restrict__ p2cls, const u32* __restrict__ p2tid, u32* __restrict__ ev_left,
+                                                u32* __restrict__ ev_right, u32* __restrict__ ev_p, u32 evcap) {
+  const u32 nocc = st[KI_NOCC0 + par];
+  for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < nocc; i += gridDim.x * blockDim.x) {
+    u32 j = occ_j[i];
+    if (rmark[j]) continue;                      // not a run head: the pair to its left is an occurrence too
+    bool keep = true;
+    u32 l = t.ls[j];                             // carried along the run: a merged right token's ls is zeroed below
+    while (flags[j]) {
+      const u32 r = j + 1u + (l >> 16), lr = t.ls[r];
+      if (keep) {
+        const u32 p = aux[j];
+        const u32 q = atomicAdd(&st[KI_EVN], 1u);
+        if (q < evcap) { ev_left[q] = t.pos[j]; ev_right[q] = t.pos[r]; ev_p[q] = p; } else st[KI_ERR] = 1u;
+        t.cls[j] = p2cls[p];
+        t.tid[j] = p2tid[p];
+        t.glue[j] = t.glue[r];
+        t.ls[j] = ((l & 0xFFFFu) + (lr & 0xFFFFu)) | (((l >> 16) + 1u + (lr >> 16)) << 16);
+        t.ls[r] = 0u;
+      }
+      keep = !keep;
+      j = r; l = lr;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) ki_unflag(u32* __restrict__ st, int par, const u32* __restrict__ occ_j, const u32* __restrict__ occ_r,
+                                                 u8* __restrict__ flags, u8* __restrict__ rmark, u32* __restrict__ rep_start,
+                                                 u32* __restrict__ rep_cnt, int m, u32 ev_before_slot) {
+  const u32 nocc = st[KI_NOCC0 + par];
+  for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < nocc; i += gridDim.x * blockDim.x) {
+    flags[occ_j[i]] = 0; rmark[occ_r[i]] = 0;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    // rep_start[m] was stored by the previous merge's unflag (= EVN after it); this merge's count closes the range
+    const u32 start = rep_start[m];
+    rep_cnt[m] = st[KI_EVN] - start;
+    rep_start[m + 1] = st[KI_EVN];
+    st[KI_NOCC0 + (par ^ 1)] = 0u;               // the other parity's counter: the next merge's flag pass starts from zero
+    (void)ev_before_slot;
+  }
+}
+
+// merges with host-side parameters (the caller leaves out merges whose key cannot occur); rep_start[0] = first free event slot
+extern "C" int gb_induce_replay(uint32_t* cls, uint32_t* glue, const uint32_t* pos, uint32_t* ls, uint32_t* tid, uint8_t* flags,
+                                uint8_t* rmark, uint32_t* aux, int64_t N, const double* vals, int64_t ld, const uint32_t* bb,
+                                const int64_t* offsets, const double* f3tab, int n_merges, const uint64_t* mkey_host,
+                                const int* mK_host, const int* mA_host, const int* mnres_host, const int64_t* mmed_off_host,
+                                const int64_t* mp2_off_host, const double* med, const uint32_t* p2cls, const uint32_t* p2tid,
+                                uint32_t* occ_j, uint32_t* occ_r, uint32_t* ev_left, uint32_t* ev_right, uint32_t* ev_p,
+                                int64_t evcap, uint32_t* st, uint32_t* rep_start, uint32_t* rep_cnt, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (N <= 0 || n_merges <= 0) return 0;
+  int sms = gb_sm_count();
+  if (sms <= 0) sms = 148;
+  KITok t{cls, glue, pos, ls, tid};
+  KIGeo g{vals, ld, bb, offsets, f3tab};
+  const int flag_blocks = gb_blocks_for(N, 256 * 8, sms * 8);
+  int par = 0;
+  for (int m = 0; m < n_merges; ++m) {
+    if (mA_host[m] > KI_AMAX || mK_host[m] <= 0) { gb_set_error("gb_induce_replay: merge %d has %d medoids / spans %d atoms (device limit %d)", m, mK_host[m], mA_host[m], KI_AMAX); return -2; }
+    ki_flag<<<flag_blocks, 256, 0, s>>>(t, N, (u64)mkey_host[m], st, par, occ_j, occ_r, flags, rmark);
+    ki_assign<<<sms * 8, 128, 0, s>>>(t, g, st, par, occ_j, mnres_host[m], mA_host[m], med + mmed_off_host[m], mK_host[m], aux);
+    ki_apply<<<sms, 128, 0, s>>>(t, st, par, occ_j, flags, rmark, aux, p2cls + mp2_off_host[m], p2tid + mp2_off_host[m], ev_left,
+                                 ev_right, ev_p, (u32)evcap);
+    ki_unflag<<<sms, 256, 0, s>>>(st, par, occ_j, occ_r, flags, rmark, rep_start, rep_cnt, m, 0u);
+    par ^= 1;
+  }
+  GB_LAUNCH_CK();
+  return 0;
+}
+extern "C" int gb_induce_max_atoms(void) { return KI_AMAX; }

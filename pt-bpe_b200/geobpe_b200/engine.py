@@ -451,7 +451,7 @@ class Learner:
         self.use_graphs = True
         # device-driven loop: 2 = persistent cooperative kernel with incrementally maintained pair counts (csrc/k_hloop2.cu, one GPU),
         # 1 = per-iteration candidate pass replayed from CUDA graphs (csrc/k_hloop.cu; the sharded loop)
-        self.loop_version = int(os.environ.get("GEOBPE_LOOP", 2 if self.comm is None else 1))
+        self.loop_version = int(os.environ.get("GEOBPE_LOOP", 2))
         self._quantize()
         self._ts = TokenState(self.bb.R, mode)
         R = self.bb.R
@@ -489,8 +489,8 @@ class Learner:
         if not raw:
             return
         self._raw = []
-        for cnt, r0, nres in raw:
-            dicts = self._h_key_dicts(r0.tolist(), nres.tolist()) if nres is not None else None
+        for cnt, r0, nres, *glob in raw:
+            dicts = self._h_key_dicts(r0.tolist(), nres.tolist(), glob=bool(glob and glob[0])) if nres is not None else None
             for s in range(len(cnt)):
                 if dicts is not None:                  # (same dict json.loads(key_str) would build: keys in sorted order)
                     key_str = json.dumps(dicts[s], sort_keys=True)
@@ -634,10 +634,12 @@ class Learner:
             pw.append(pw[-1] * self.hash_base & M64)
         self.powtab = torch.from_numpy(np.array(pw, dtype=np.uint64).view(np.int64)).to(_dev())
 
-    def _h_key_dicts(self, r0s, nress):
-        """compute_geo_key's dict for fully histogram-quantised windows (bpe.py:1225-1298); one batched gather"""
+    def _h_key_dicts(self, r0s, nress, glob=False):
+        """compute_geo_key's dict for fully histogram-quantised windows (bpe.py:1225-1298); one batched gather
+        (glob: r0s index the residues of ALL ranks -- the sharded loop logs example windows of whichever rank held one)"""
         idx = np.concatenate([np.arange(r, r + n) for r, n in zip(r0s, nress)])
-        rb_all = self.rbins.view(9, self.bb.R)[:, torch.from_numpy(idx).to(_dev())].cpu().numpy().astype(np.int64) & 0xFFFF
+        src = self.hl.rbins_g if glob else self.rbins.view(9, self.bb.R)
+        rb_all = src[:, torch.from_numpy(idx).to(_dev())].cpu().numpy().astype(np.int64) & 0xFFFF
         out, o = [], 0
         for nres in nress:
             rb = rb_all[:, o:o + nres]
@@ -895,6 +897,18 @@ class Learner:
         transport (collective: every rank calls it; a barrier makes sure no peer kernel still reads this rank's block).
         The learner stays usable: it falls back to the NCCL exchanges afterwards."""
         self.sync()
+        if self.hl is not None and getattr(self.hl, "v2", False):
+            if self.hl.peer is not None:
+                torch.cuda.synchronize()
+                self.comm.all_reduce(torch.zeros(1, device=_dev()))
+                torch.cuda.synchronize()
+                self._materialise_log()      # (example windows of the logged iterations index the replicated rbins)
+                self._peer_release(self.hl.peer)
+                self.hl.peer = None
+                stats = (self.hl.steps, self.hl.halts, self.hl.stats, self.hl.times_ns)
+                self.hl = None               # (a later enqueue sets the loop up again, collectively)
+                self._closed_stats = stats
+            return
         d = self.hl.dist if self.hl is not None else None
         if d is None:
             return
@@ -973,7 +987,7 @@ class Learner:
 
     def enqueue(self, nsteps):
         """enqueue `nsteps` merge iterations on the device; nothing is read back until sync()"""
-        if self.loop_version == 2 and self.comm is None:
+        if self.loop_version == 2:
             return self._h2_enqueue(nsteps)
         if self.hl is None:
             self._hl_init()
@@ -1022,7 +1036,7 @@ class Learner:
         if not self.async_steps:
             return
         self.sync()
-        if self.loop_version == 2 and self.comm is None:
+        if self.loop_version == 2:
             return                                          # one cooperative kernel per enqueue: nothing to capture
         if self.hl is None:
             self._hl_init()
@@ -1146,9 +1160,10 @@ class Learner:
               C1=13, NCAND=14, NCL=15, CLCAP=16, NOCC=17, M1=18, NT=19, P1=20, WIN_SLOT=21, WIN_R0=22, WIN_NRES=23, WIN_CNT=24,
               MISMATCH=25, NEWT=26, OVF=27, ERR=28, HALT_STEP=29, NTMAX=30, CMPT=31, FRESH=32, ND=33, NZ=34, MPREV=35,
               ST_PERIODS=36, ST_CROSS=37, ST_INCONCL=38, ST_COMPACT=39, ST_R2=40, ST_FULL=41, ST_LOOPS=42, PERIOD_LEN=43,
-              ST_MAXNCL=44, ST_MAXND=45, ST_MAXNCAND=46, ST_TIES=47)
+              ST_MAXNCL=44, ST_MAXND=45, ST_MAXNCAND=46, ST_TIES=47,
+              HALT_REQ=48, PERIOD_REQ=49, NDEATH=50, NBIRTH=51, DSEQ=52, XSEQ=53, ST_WAIT_US=54)
     H2_TIMES = ("period_start", "decide", "flag", "deaths", "apply", "births", "compaction", "candidate_pass",
-                "flag_block0_work", "deaths_block0_work", "apply_block0_work", "births_block0_work")
+                "flag_block0_work", "deaths_block0_work", "apply_block0_work", "births_block0_work", "exchange")
     H2_HALT_NAMES = {**HALT_NAMES, 10: "internal", 11: "guard"}
     H2_TABLE_LOG2 = 15
 
@@ -1156,11 +1171,36 @@ class Learner:
         ts = self._ts
         lib = _lib.load()
         maxwin = int(self.bb.lens_host.max()) if self.bb.S else 2
-        if self.sketch is None:
+        if self.sketch is None and self.comm is None:
             self.sketch = SlotSketch(ts.T)
-        sk = self.sketch
-        hl = types.SimpleNamespace(v2=True, dist=None)
+        hl = types.SimpleNamespace(v2=True, dist=None, peer=None, rbins_g=None, rbase=0, R_total=self.bb.R, dseq=0, xseq=0)
         assert lib.gb_h_loop2_state_words() == 64
+        comm = self.comm
+        if comm is not None:
+            # the rows of every rank's rbins, so that any rank can order / check any key (example windows are global ranges)
+            R_all = comm.all_gather_object(self.bb.R)
+            hl.rbase, hl.R_total = int(sum(R_all[:comm.rank])), int(sum(R_all))
+            if hl.R_total >= (1 << 32) - 2:
+                raise ValueError("a sharded run holds at most 2^32-2 residues in total (u32 example windows)")
+            Rmax = max(R_all)
+            pad = _zeros(9 * Rmax, torch.int16).view(9, Rmax)
+            pad[:, :self.bb.R] = self.rbins.view(9, self.bb.R)
+            allr = _empty(comm.world * 9 * Rmax, torch.int16)
+            comm.all_gather_into(allr, pad.view(-1))
+            allr = allr.view(comm.world, 9, Rmax)
+            g = _empty(9 * hl.R_total, torch.int16).view(9, hl.R_total)
+            o = 0
+            for r, Rr in enumerate(R_all):
+                g[:, o:o + Rr] = allr[r, :, :Rr]
+                o += Rr
+            hl.rbins_g = g.contiguous()
+            del allr, pad
+            if self.sketch is None:      # the slot counters are replicated: sized for the pairs of ALL ranks
+                Tg = int(comm.all_reduce(torch.tensor([ts.T], device=_dev(), dtype=torch.int64), "sum").item())
+                self.sketch = SlotSketch(Tg)
+            mw = comm.all_reduce(torch.tensor([maxwin], device=_dev(), dtype=torch.int64), "max")
+            maxwin = int(mw.item())
+        sk = self.sketch
         hl.hs = _zeros(64, torch.int32)
         hl.hs64 = _zeros(16, torch.int64)
         hl.stride = ((39 * maxwin + 200) + 127) // 128 * 128
@@ -1177,6 +1217,8 @@ class Learner:
         hl.occ_j = _empty(ts.cap, torch.int32)
         hl.occ_r = _empty(ts.cap, torch.int32)
         hl.nargs = lib.gb_h_loop2_nargs()
+        hl.dcap = next_pow2(max(1 << 16, self.bb.R // 8))
+        hl.xcap = 1 << 17
         hl.thr_num = int(os.environ.get("GEOBPE_H2_THR16", 14))
         hl.ctas = int(os.environ.get("GEOBPE_H2_CTAS", 2))
         hl.period = 64                 # (reported by bench.py; periods end on the device when the threshold is crossed)
@@ -1191,6 +1233,8 @@ class Learner:
         self._last_count = self._pop_log[-1][0] if self._pop_log else 0
         self.hl = hl
         self._h2_table(hl.M)
+        if comm is not None:
+            self._h2_peer_setup()
 
     def _h2_table(self, M):
         hl = self.hl
@@ -1201,6 +1245,51 @@ class Learner:
         hl.tnres = _zeros(M, torch.int32)
         hl.tlist = _zeros(M, torch.int32)
 
+    def _h2_peer_setup(self):
+        """one symmetric block [delta x 2 | export x 2 | flags] per rank, mapped into every other rank through CUDA IPC"""
+        import socket
+        lib, comm, hl = _lib.load(), self.comm, self.hl
+        if hl.peer is not None:
+            torch.cuda.synchronize()
+            comm.all_reduce(torch.zeros(1, device=_dev()))
+            torch.cuda.synchronize()
+            self._peer_release(hl.peer)
+            hl.peer = None
+        if comm.world > int(lib.gb_h_loop2_max_world()):
+            raise NotImplementedError(f"the sharded loop is built for up to {lib.gb_h_loop2_max_world()} ranks")
+        while hl.xcap < hl.M // 2:
+            hl.xcap *= 2
+        al = lambda n: (int(n) + 255) // 256 * 256
+        o_x = al(lib.gb_h_loop2_delta_bytes(hl.dcap))
+        o_f = o_x + al(lib.gb_h_loop2_export_bytes(hl.xcap))
+        total = o_f + al(lib.gb_h_loop2_flag_bytes())
+        pr = types.SimpleNamespace(base=None, opened=[], lib=lib)
+        base, h = C.c_void_p(), (C.c_ubyte * 64)()
+        err = None
+        if lib.gb_peer_alloc(total, C.byref(base), h) != 0:
+            err = lib.gb_last_error().decode()
+        else:
+            pr.base = base.value
+        infos = comm.all_gather_object((socket.gethostname(), bytes(h), err))
+        if any(e is not None for _, _, e in infos) or len({hn for hn, _, _ in infos}) != 1:
+            raise RuntimeError(f"peer-memory setup failed: {[e for _, _, e in infos if e]} (one node, CUDA IPC)")
+        bases = []
+        for r, (_, hb, _) in enumerate(infos):
+            if r == comm.rank:
+                bases.append(pr.base)
+                continue
+            q = C.c_void_p()
+            if lib.gb_peer_open((C.c_ubyte * 64).from_buffer_copy(hb), C.byref(q)) != 0:
+                raise RuntimeError("gb_peer_open: " + lib.gb_last_error().decode())
+            pr.opened.append(q.value)
+            bases.append(q.value)
+        pr.table = (C.c_uint64 * (3 * comm.world))(*([b for b in bases] + [b + o_x for b in bases] + [b + o_f for b in bases]))
+        hl.peer = pr
+        hl.dseq = hl.xseq = 0            # (fresh, zeroed flag rows on every rank)
+        torch.cuda.synchronize()
+        comm.all_reduce(torch.zeros(1, device=_dev()))          # every block is zeroed and mapped before the first signal
+        torch.cuda.synchronize()
+
     def _h2_args(self):
         ts, sk, hl = self._ts, self.sketch, self.hl
         if hl.buf0 is None or not ((ts.a is hl.buf0 and ts.b is hl.buf1) or (ts.a is hl.buf1 and ts.b is hl.buf0)):
@@ -1209,11 +1298,13 @@ class Learner:
         P = _lib.ptr
         vals = [P(hl.hs), P(hl.hs64), P(a["hsh"]), P(b["hsh"]), P(a["glue"]), P(b["glue"]), P(a["pos"]), P(b["pos"]),
                 P(a["len"]), P(b["len"]), P(a["tid"]), P(b["tid"]), P(ts.flags), P(hl.rmark), P(ts.scratch), P(self.powtab), self.hash_base,
-                P(self.rbins), self.bb.R, P(sk.slots), sk.log2ns, P(sk.bmax), P(sk.cand), sk.CAP, P(hl.cbit),
+                P(hl.rbins_g) if hl.rbins_g is not None else P(self.rbins), hl.R_total, P(sk.slots), sk.log2ns, P(sk.bmax), P(sk.cand), sk.CAP, P(hl.cbit),
                 P(hl.tk), P(hl.tc), P(hl.tr0), P(hl.tnres), P(hl.tlist), hl.M, P(hl.cl_key), P(hl.cl_j), P(hl.occ_j), P(hl.occ_r),
                 P(hl.strbuf), hl.stride, P(hl.rank), P(self._evl), P(self._evr), P(self._evp), P(hl.log_key),
                 P(hl.log["cnt"]), P(hl.log["r0"]), P(hl.log["nres"]), P(hl.log["evstart"]), P(hl.log["nk"]),
-                hl.thr_num, 1 if 16 * ts.cap > SlotSketch.STREAM_BYTES else 0, hl.ctas]
+                hl.thr_num, 1 if 16 * ts.cap > SlotSketch.STREAM_BYTES else 0, hl.ctas,
+                hl.rbase, self.comm.world if self.comm is not None else 1, self.comm.rank if self.comm is not None else 0,
+                C.addressof(hl.peer.table) if hl.peer is not None else 0, hl.dcap, hl.xcap]
         assert len(vals) == hl.nargs, (len(vals), hl.nargs)
         return (C.c_int64 * len(vals))(*[v if v < (1 << 63) else v - (1 << 64) for v in vals])
 
@@ -1231,7 +1322,8 @@ class Learner:
         h[H["CLCAP"]] = hl.cl_key.numel()
         h[H["PAR"]] = 0 if ts.a is hl.buf0 else 1
         h[H["MPREV"]] = self._last_count
-        hl.hs.copy_(torch.from_numpy(h.astype(np.int32)))
+        h[H["DSEQ"]], h[H["XSEQ"]] = hl.dseq, hl.xseq       # sequence numbers of the peer exchanges live as long as the flag rows
+        hl.hs.copy_(torch.from_numpy(h.astype(np.int64).astype(np.uint32).view(np.int32)))
         hl.hs64.zero_()
         if not hl.slots_valid:
             ts.flags.zero_()             # (the host path leaves its occurrence flags behind)
@@ -1248,6 +1340,8 @@ class Learner:
             if ev is not None:
                 e1.record()
                 ev.append((e0, e1, ts.T))
+            if self.comm is not None:            # replicated global counters (once per recount; kept exact by the delta exchange)
+                self.comm.all_reduce(sk.slots, "sum")
             hl.slots_valid = True
 
     def _h2_enqueue(self, nsteps):
@@ -1276,9 +1370,11 @@ class Learner:
             h = hl.hs.cpu().numpy().astype(np.int64) & 0xFFFFFFFF            # the one blocking read
             tm = hl.hs64.cpu().numpy()
             done, halt = int(h[H["STEP"]]), int(h[H["HALT"]])
+            hl.dseq, hl.xseq = int(h[H["DSEQ"]]), int(h[H["XSEQ"]])
             want = self._pending
             self._pending = 0
             self.n_steps -= want
+            hl.stats["peer_wait_us"] = hl.stats.get("peer_wait_us", 0) + int(h[H["ST_WAIT_US"]])
             for k, name in enumerate(self.H2_TIMES):
                 hl.times_ns[name] += int(tm[2 + k])
             for name, word in (("periods", "ST_PERIODS"), ("inconclusive", "ST_INCONCL"), ("compactions", "ST_COMPACT"),
@@ -1289,7 +1385,7 @@ class Learner:
             if done:
                 keys = hl.log_key[:done].cpu().numpy().astype(np.uint64).tolist()
                 lg = {k: _u32(v[:done]) for k, v in hl.log.items()}
-                self._raw.append((lg["cnt"], lg["r0"], lg["nres"]))      # formatted lazily (_materialise_log)
+                self._raw.append((lg["cnt"], lg["r0"], lg["nres"], hl.rbins_g is not None))      # formatted lazily (_materialise_log)
                 for s in range(done):
                     self._step_events.append((self._ntok + s, int(lg["evstart"][s]), int(lg["nk"][s]), keys[s]))
                 self._ntok += done
@@ -1316,11 +1412,19 @@ class Learner:
             if halt:
                 hl.halts[halt] = hl.halts.get(halt, 0) + 1
                 if halt == 3:          # two windows with different bins share a 64-bit content hash: re-key everything
+                    if self.comm is not None:
+                        raise RuntimeError("64-bit content-hash collision detected (window bins differ) in a sharded run")
                     self.rehash()
-                elif halt == 4:        # the exact table was too small for this period's candidate keys
+                elif halt == 4:        # the exact table (or the delta buffers) were too small for this period
                     self._h2_table(hl.M * 4)
+                    if self.comm is not None:
+                        hl.dcap *= 2
+                        self._h2_peer_setup()
                 elif halt in (1, 2):   # ties / candidates: this one iteration on the host path
-                    self._step_h_host()
+                    if self.comm is not None:
+                        self._step_h_dist()        # (every rank halts at the same iteration)
+                    else:
+                        self._step_h_host()
                     hl.slots_valid = False
                     rest -= 1
             self._h2_push_state()
@@ -1987,30 +2091,120 @@ class Inducer(Learner):
             bad = torch.from_numpy(self.failed).to(_dev())[self.bb.bb.to(torch.int64)]
             ts.a["glue"][:R] = torch.where(bad, torch.full_like(self.glue_res, -(1 << 31)), self.glue_res)
         # ---- merge replay in learned order (bpe.py:1116-1139)
-        self.replay = []                     # per vocabulary merge: (event start, event count) -- (0, 0) if it never fired
-        for n, key_str in list(zip(ns, geo_keys))[2:]:
-            self.replay.append((self.ev_n, 0))
+        merges = list(zip(ns, geo_keys))[2:]
+        plan = []                            # per vocabulary merge: None (cannot fire) or (key, geos, p2cls, tid0, nres, A)
+        nb = lambda g: len(g["N:CA"]) + len(g["CA:C"]) + len(g.get("0C:1N", []))
+        for n, key_str in merges:
             gl, glue, gr = parse_m_key(key_str)
             cL, cR = self.class_of.get(json.dumps(gl)), self.class_of.get(json.dumps(gr))
             geos = sphere_dict[key_str]
-            p2cls = torch.tensor([self.intern_class(g) for g in geos], dtype=torch.int32, device=_dev())
+            p2cls = [self.intern_class(g) for g in geos]
             if cL is None or cR is None:
-                continue                                   # a constituent motif never occurred -> key not in geo_dict
-            key = pack_m_key(cL, glue, cR)
+                plan.append(None)            # a constituent motif never occurred -> key not in geo_dict
+                continue
+            length = nb(gl) + nb(gr)
+            plan.append((pack_m_key(cL, glue, cR), geos, p2cls, tid_of[(n, 0)], (length + 1) // 3, length + 1))
+        amax = int(_lib.load().gb_induce_max_atoms())
+        if os.environ.get("GEOBPE_INDUCE_HOST") == "1" or any(pl is not None and pl[5] > amax for pl in plan):
+            self._replay_host(merges, plan)
+        else:
+            self._replay_device(plan)
+
+    def _replay_device(self, plan):
+        """all vocabulary merges applied on the device without a host round trip (csrc/k_induce.cu)"""
+        ts, dev = self.ts, _dev()
+        live = [pl for pl in plan if pl is not None]
+        R, N = self.bb.R, ts.T
+        nm = len(live)
+        if nm == 0 or N == 0:
+            self.replay = [(self.ev_n, 0)] * len(plan)
+            return
+        # medoid coordinates of every merge: one K4 call per window size
+        by_A = {}
+        for i, pl in enumerate(live):
+            by_A.setdefault(pl[5], []).append(i)
+        med_parts, med_off, p2_off, cur, curp = [], [0] * nm, [0] * nm, 0, 0
+        p2cls_all, p2tid_all = [], []
+        for A, idxs in by_A.items():
+            geos = [g for i in idxs for g in live[i][1]]
+            mc = self.geo_coords(geos, A).reshape(-1)
+            o = 0
+            for i in idxs:
+                med_off[i] = cur + o
+                o += len(live[i][1]) * A * 3
+            med_parts.append(mc)
+            cur += mc.numel()
+        for i, pl in enumerate(live):
+            p2_off[i] = curp
+            p2cls_all += pl[2]
+            p2tid_all += list(range(pl[3], pl[3] + len(pl[1])))
+            curp += len(pl[1])
+        med = torch.cat(med_parts).contiguous()
+        p2cls = torch.tensor(p2cls_all, dtype=torch.int32, device=dev)
+        p2tid = torch.tensor(p2tid_all, dtype=torch.int32, device=dev)
+        st = _zeros(8, torch.int32)
+        rep_start = _zeros(nm + 1, torch.int32)
+        rep_cnt = _zeros(nm, torch.int32)
+        rmark = _zeros(ts.cap, torch.uint8)
+        occ_r = _empty(ts.cap, torch.int32)
+        ts.flags.zero_()
+        arr = lambda xs, ct: (ct * nm)(*xs)
+        mkey = arr([pl[0] for pl in live], C.c_uint64)
+        mK, mA, mnres = arr([len(pl[1]) for pl in live], C.c_int), arr([pl[5] for pl in live], C.c_int), arr([pl[4] for pl in live], C.c_int)
+        moff, poff = arr(med_off, C.c_int64), arr(p2_off, C.c_int64)
+        bb = self.bb
+        _lib.call_n("gb_induce_replay", 4 * nm, ts.p("cls"), ts.p("glue"), ts.p("pos"), ts.p("len"), ts.p("tid"), _lib.ptr(ts.flags),
+                    _lib.ptr(rmark), _lib.ptr(ts.aux), N, _lib.ptr(bb.vals), R, _lib.ptr(bb.bb), _lib.ptr(bb.offsets), _lib.ptr(self.f3tab()),
+                    nm, mkey, mK, mA, mnres, moff, poff, _lib.ptr(med), _lib.ptr(p2cls), _lib.ptr(p2tid), _lib.ptr(ts.idx), _lib.ptr(occ_r),
+                    _lib.ptr(self._evl), _lib.ptr(self._evr), _lib.ptr(self._evp), self._evl.numel(), _lib.ptr(st), _lib.ptr(rep_start),
+                    _lib.ptr(rep_cnt))
+        # one compaction at the end: the host sees dense arrays (len = plain residue counts)
+        ls = ts.a["len"][:N]
+        idx = torch.nonzero(ls != 0).flatten()
+        T = int(idx.numel())
+        for f in ts.a:
+            ts.b[f][:T] = ts.a[f][:N][idx] if f != "len" else (ls[idx] & 0xFFFF)
+        ts.swap()
+        ts.T = T
+        sth = _u32(st)
+        if int(sth[3]):
+            raise RuntimeError("merge-event log overflow")
+        self._ev_n = int(sth[2])
+        cnt = _u32(rep_cnt)
+        start = _u32(rep_start)
+        if self._ev_n > 1:
+            self._sort_events(0, self._ev_n, rep_cnt)
+        self.replay, k, at = [], 0, 0
+        for pl in plan:
+            if pl is None:
+                self.replay.append((at, 0))
+                continue
+            self.replay.append((int(start[k]), int(cnt[k])))
+            at = int(start[k]) + int(cnt[k])
+            k += 1
+        self.n_steps = int((cnt > 0).sum())
+
+    def _replay_host(self, merges, plan):
+        """host-driven replay (one K2 compaction and one read-back per merge): windows beyond the device kernel's atom limit"""
+        ts = self.ts
+        tid_of = {k: i for i, k in enumerate(self.token_keys)}
+        self.replay = []
+        for (n, key_str), pl in zip(merges, plan):
+            self.replay.append((self.ev_n, 0))
+            if pl is None:
+                continue
+            key, geos, p2cls_l, tid0, nres, A = pl
+            p2cls = torch.tensor(p2cls_l, dtype=torch.int32, device=_dev())
             _lib.call("gb_flag_pairs_m", ts.p("cls"), ts.p("glue"), ts.T, key, _lib.ptr(ts.flags))
             N = ts.select(1, ts.idx)
             if N == 0:
                 continue
-            nb = lambda g: len(g["N:CA"]) + len(g["CA:C"]) + len(g.get("0C:1N", []))
-            length = nb(gl) + nb(gr)
-            nres, A = (length + 1) // 3, length + 1
             occ = ts.idx[:N].to(torch.int64)
             r0 = ts.a["pos"][occ].contiguous(); f3c = ts.a["cls"][occ].contiguous()
             allc = self.coords(r0, N, nres, A, f3c)
             medc = self.geo_coords(geos, A)
             asg = self.assign(allc, medc)
             _lib.call("gb_scatter_u32", _lib.ptr(ts.idx), _lib.ptr(asg), N, _lib.ptr(ts.aux))
-            tid0 = tid_of[(n, 0)]
             p2tid = torch.arange(tid0, tid0 + len(geos), dtype=torch.int32, device=_dev())
             e0 = self.ev_n
             self._merge(key, n, p2cls, p2tid)

@@ -200,3 +200,23 @@ def test_driver_call_sequences(tmp_path):
     pickle.dump(src, open(os.path.join(save, "out.pkl"), "wb+"))
     out = pickle.load(open(os.path.join(save, "out.pkl"), "rb"))
     assert out.n == [N, len(toks)] and len(out.tokenizers) == N + len(toks)
+
+
+def test_induce_device_replay_equals_host_replay(monkeypatch):
+    """K7 (csrc/k_induce.cu: all vocabulary merges replayed on the device, in-place merges on lazily compacted arrays) against
+    the host-driven replay (one K2 compaction + read-back per merge) on a held-out batch: token arrays, merge events, L trace"""
+    from geobpe_b200 import engine as E
+    bpe, _ = learn(HP_M, S=40, n=48, seed=51, steps=60)
+    hv, ho = synthetic.generate(30, 56, seed=52, ragged=True)
+    outs = []
+    for host in ("0", "1"):
+        monkeypatch.setenv("GEOBPE_INDUCE_HOST", host)
+        ind = E.Inducer(hv, ho, bpe._tokens, bpe._sphere_dict, bpe._thresholds, bpe.std_bonds)
+        ts = ind.ts
+        n = ind.ev_n
+        outs.append(([E._u32(ts.a[f][:ts.T]).tolist() for f in ("pos", "len", "tid", "cls", "glue")],
+                     E._u32(ind.ev_left[:n]).tolist(), E._u32(ind.ev_right[:n]).tolist(), E._u32(ind.ev_p[:n]).tolist(),
+                     [c for _, c in ind.replay], ind.n_steps, ind.failed.tolist()))
+    assert outs[0][4] == outs[1][4], "events per vocabulary merge differ"
+    assert outs[0] == outs[1]
+    assert outs[0][5] > 10

@@ -15,9 +15,10 @@ GEN = (40, 48, 31)
 STEPS = 80          # crosses one compaction period of the device-driven loop
 
 
-def worker(rank, world, port, q, mode):
+def worker(rank, world, port, q, mode, uneven=False):
     async_steps = mode != "host"
     os.environ["GEOBPE_PEER"] = "1" if mode == "peer" else "0"
+    os.environ["GEOBPE_LOOP"] = "2" if mode == "loop2" else "1"
     for p in (os.path.join(ROOT, "pt-bpe_b200"),):
         sys.path.insert(0, p)
     import torch.distributed as dist
@@ -28,6 +29,9 @@ def worker(rank, world, port, q, mode):
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     vals, offs = synthetic.generate(GEN[0], GEN[1], seed=GEN[2], ragged=True)
     a, b = shard_ranges(np.diff(offs), world)[rank]
+    if uneven:                       # rank 0 holds all but the last two backbones
+        cut = len(offs) - 1 - 2
+        a, b = (0, cut) if rank == 0 else (cut, len(offs) - 1)
     v = vals[:, offs[a]:offs[b]]
     o = offs[a:b + 1] - offs[a]
     L = E.Learner(v, o, mode="H", comm=Comm(), async_steps=async_steps, **HP)
@@ -40,24 +44,31 @@ def worker(rank, world, port, q, mode):
         lo, hi = np.searchsorted(pos, o[i]), np.searchsorted(pos, o[i + 1])
         segs.append([[int(3 * (pos[j] - o[i])), int(tid[j]), int(3 * ln[j] - (1 if glue[j] & E.LAST else 0))]
                      for j in range(lo, hi)])
-    transport = "peer" if (L.hl is not None and L.hl.dist is not None and L.hl.dist.peer is not None) else "nccl"
+    if L.hl is not None and getattr(L.hl, "v2", False):
+        transport = "peer2" if L.hl.peer is not None else "none"
+    else:
+        transport = "peer" if (L.hl is not None and L.hl.dist is not None and L.hl.dist.peer is not None) else "nccl"
     halts = dict(L.hl.halts) if L.hl is not None else {}
-    q.put((rank, a, [list(p) for p in L.pop_log], [[k, v] for k, v in L.tokens.items()], segs, transport, halts))
+    dev_steps = L.hl.steps if L.hl is not None else 0
+    q.put((rank, a, [list(p) for p in L.pop_log], [[k, v] for k, v in L.tokens.items()], segs, transport, halts, dev_steps))
     L.close()           # graphs holding captured NCCL collectives / the peer-memory block go before the process group
     del L
     dist.destroy_process_group()
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("mode", ["peer", "nccl", "host"], ids=["device-loop-peer-memory", "device-loop-nccl", "host-driven"])
-def test_two_gpu_h_mode_matches_oracle(mode):
+@pytest.mark.parametrize("mode,uneven", [("loop2", False), ("loop2", True), ("peer", False), ("nccl", False), ("host", False)],
+                         ids=["loop2-replicated-counts-delta-exchange", "loop2-uneven-shards", "device-loop-peer-memory", "device-loop-nccl",
+                              "host-driven"])
+def test_two_gpu_h_mode_matches_oracle(mode, uneven):
     import torch.multiprocessing as mp
     import geobpe_oracle as O
     from geobpe_b200 import synthetic
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = 29500 + os.getpid() % 1000
-    ps = [ctx.Process(target=worker, args=(r, 2, port + {"peer": 0, "nccl": 7, "host": 14}[mode], q, mode)) for r in range(2)]
+    ps = [ctx.Process(target=worker, args=(r, 2, port + {"peer": 0, "nccl": 7, "host": 14, "loop2": 21}[mode] + int(uneven), q, mode, uneven))
+          for r in range(2)]
     [p.start() for p in ps]
     res = sorted(q.get(timeout=300) for _ in ps)
     [p.join(60) for p in ps]
@@ -68,9 +79,11 @@ def test_two_gpu_h_mode_matches_oracle(mode):
         ora.step()
     want_pops = [list(p) for p in ora.pop_log]
     want_tokens = [[k, v] for k, v in ora._tokens.items()]
-    for rank, a, pops, tokens, segs, transport, halts in res:
+    for rank, a, pops, tokens, segs, transport, halts, dev_steps in res:
         if mode == "peer":           # the exchanges really went through peer memory, and no rank timed out on a signal
             assert transport == "peer" and 9 not in halts
+        if mode == "loop2":
+            assert transport == "peer2" and 9 not in halts and dev_steps >= STEPS // 2
         assert pops == want_pops
         assert tokens == want_tokens
         for i, seg in enumerate(segs):
