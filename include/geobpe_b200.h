@@ -270,18 +270,25 @@ int gb_h_loop2_state_words(void);
 /* sharded run of the same loop (args: rbase = global index of the shard's first residue -- rbins then holds the rows of ALL
  * ranks --, world, rank, host table u64 [3][world] of every rank's delta / export / flag block inside its gb_peer_alloc'ed
  * symmetric block, dcap, xcap): slot counters, candidate bitmap and exact table are replicated; per iteration every rank
- * publishes the keys of the pairs its merges destroyed / created (bpe.py:1924-1950, 1992-2006) and replays the other
- * ranks' over NVLink / NVSwitch loads inside the kernel; per period the exact (key, count, example window) lists.  This
+ * publishes the keys of the pairs its merges destroyed / created (bpe.py:1924-1950, 1992-2006) by STORING them into its
+ * inbox slot of every rank's block over NVLink / NVSwitch from inside the kernel, and replays the other ranks' slots of its own block; per period the exact (key, count, example window) lists.  This
  * replaces the reference's single-process _geo_dict with one replicated priority structure -- "pair counts combined ...
  * merges applied locally" (north_star). */
-int64_t gb_h_loop2_delta_bytes(int64_t dcap);
-int64_t gb_h_loop2_export_bytes(int64_t xcap);
+int64_t gb_h_loop2_delta_bytes(int64_t dcap, int world);
+int64_t gb_h_loop2_export_bytes(int64_t xcap, int world);
 int64_t gb_h_loop2_flag_bytes(void);
 int gb_h_loop2_max_world(void);
 /* hsh[j] = content hash under base P of token j's symbol sequence (residue symbols sym, glue symbols glue_res + 1) --
  * the value the merges build with (H(L) P + g) P^|R| + H(R); used to re-key a run after a detected 64-bit collision */
 int gb_rehash_tokens(const uint64_t* sym, const uint32_t* glue_res, const uint32_t* pos, const uint32_t* len, int64_t T,
                      uint64_t P, uint64_t* hsh, void* stream);
+
+/* ---- token-stream export: Tokenizer.tokenize (tokenizer.py:379-392) + BPE.quantize (bpe.py:928-956) of every
+ *      backbone in one pass.  out i64 [4 T - 3 S]: token j of backbone b writes at 4 j - 3 b its motif id tid[j] and, unless it
+ *      is the backbone's last token, V + off_omega + bin(omega), V + off_phi + bin(phi), V + off_cn + bin(C:1N:1CA) -- the
+ *      reference's order DIHEDRAL, DIHEDRAL, BOND_ANGLE behind a residue-aligned token; off_* = cum_bin_count(type). */
+int gb_token_stream(const uint32_t* tid, const uint32_t* glue, const uint32_t* pos, const uint32_t* bb, int64_t T,
+                    uint32_t V, uint32_t off_omega, uint32_t off_phi, uint32_t off_cn, int64_t* out, void* stream);
 
 /* ---- K7: induce merge replay on the device (bpe.py:1116-1139 BPE.tokenize's loop over the learned merges + step_helper
  *      1316-1425, for a whole batch of held-out backbones at once).  Token arrays are the medoid-mode SoA in the lazily

@@ -55,10 +55,11 @@ SIGNATURES = {
     "gb_h_loop2_nargs": [],
     "gb_induce_replay": [P] * 8 + [I64, P, I64, P, P, P, I32] + [P] * 6 + [P, P, P] + [P] * 5 + [I64, P, P, P, P],
     "gb_induce_max_atoms": [],
+    "gb_token_stream": [P, P, P, P, I64, U32, U32, U32, U32, P, P],
     "gb_rehash_tokens": [P, P, P, P, I64, U64, P, P],
     "gb_h_loop2_state_words": [],
-    "gb_h_loop2_delta_bytes": [I64],
-    "gb_h_loop2_export_bytes": [I64],
+    "gb_h_loop2_delta_bytes": [I64, I32],
+    "gb_h_loop2_export_bytes": [I64, I32],
     "gb_h_loop2_flag_bytes": [],
     "gb_h_loop2_max_world": [],
     "gb_h_loop_part": [P, I32, I32, I32, P],

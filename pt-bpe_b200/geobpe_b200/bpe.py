@@ -645,10 +645,34 @@ class BPE(_View):
                 at += nb
         return t_new
 
+    def token_stream(self):
+        """quantize(t.tokenize()) of EVERY backbone in one device pass (csrc/k_export.cu): (ids int64 device tensor, offsets
+        int64 numpy [S+1]); the reference loops list(_tokens).index() per token in a process pool (bpe.py:928-945)"""
+        import torch
+        L = self._learner
+        ts = L.ts
+        T, S = ts.T, L.bb.S
+        V = len(self._tokens)
+        out = E._empty(4 * T - 3 * S, torch.int64)
+        E._lib.call("gb_token_stream", ts.p("tid"), ts.p("glue"), ts.p("pos"), E._lib.ptr(L.bb.bb), T, V, self.cum_bin_count("omega"),
+                    self.cum_bin_count("phi"), self.cum_bin_count("C:1N:1CA"), E._lib.ptr(out))
+        first = np.searchsorted(self._token_arrays()[0], L.bb.offsets_host)
+        return out, 4 * first.astype(np.int64) - 3 * np.arange(S + 1, dtype=np.int64)
+
+    def codebook_utility(self):
+        """get_codebook_utility (plotting.py:78-95) over the token streams of all backbones, computed on the device"""
+        from foldingdiff.plotting import get_codebook_utility
+        return get_codebook_utility(self.token_stream()[0], self.vocab_size)
+
     def quantize(self, tokenized):
         if isinstance(tokenized, Tokenizer):
             return self.quantize(tokenized.tokenize())
         if isinstance(tokenized, list) and tokenized and isinstance(tokenized[0], Tokenizer):
+            if (self._learner is not None and len(tokenized) == self._learner.bb.S == len(self.tokenizers)
+                    and all(a is b for a, b in zip(tokenized, self.tokenizers)) and not any(getattr(t, "_local", False) for t in tokenized)):
+                ids, offs = self.token_stream()          # all tokenizers of this BPE (bin/encode.py:343,411): one device pass
+                ids = ids.cpu().numpy()
+                return [ids[offs[i]:offs[i + 1]].tolist() for i in range(len(offs) - 1)]
             return [self.quantize(t) for t in tokenized]
         ids = {k: i for i, k in enumerate(self._tokens)}
         out = []

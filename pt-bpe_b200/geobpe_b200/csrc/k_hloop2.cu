@@ -53,7 +53,7 @@ enum {
   H2_MISMATCH, H2_NEWT, H2_OVF, H2_ERR, H2_HALT_STEP, H2_NTMAX, H2_CMPT, H2_FRESH, H2_ND, H2_NZ, H2_MPREV,
   H2_ST_PERIODS, H2_ST_CROSS, H2_ST_INCONCL, H2_ST_COMPACT, H2_ST_R2, H2_ST_FULL, H2_ST_LOOPS, H2_PERIOD_LEN,
   H2_ST_MAXNCL, H2_ST_MAXND, H2_ST_MAXNCAND, H2_ST_TIES,
-  H2_HALT_REQ, H2_PERIOD_REQ, H2_NDEATH, H2_NBIRTH, H2_DSEQ, H2_XSEQ, H2_ST_WAIT_US,
+  H2_HALT_REQ, H2_PERIOD_REQ, H2_NDEATH, H2_NBIRTH, H2_DSEQ, H2_XSEQ, H2_ST_WAIT_US, H2_TRACE,
   H2_WORDS = 64
 };
 // hs64: [0] popped key, [1] spare, [2..] nanoseconds accumulated per phase (block 0's view)
@@ -81,10 +81,13 @@ struct H2Args {
   u64 peer_x[H2_MAXW];            // every rank's export blocks  [2 parities][header | key, count, r0, nres]
   u64 peer_f[H2_MAXW];            // every rank's flag rows      u32 [2 stages][H2_MAXW]
   u32 dcap, xcap;
+  u64 timeout_ns;                 // a rank that sees no signal from a peer for this long halts (code 9) instead of spinning on
 };
 
 // ---- peer memory: release / acquire flags and loads that bypass L1 (another GPU writes these addresses) ------------------
-__device__ __forceinline__ void h2p_st_release(u32* p, u32 v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+// signal = a system-scope reduction performed at the flag's home memory (the peer's L2), not a store that could sit in a
+// local cache of peer lines while this kernel keeps running
+__device__ __forceinline__ void h2p_st_release(u32* p, u32 v) { asm volatile("red.release.sys.global.max.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 __device__ __forceinline__ u32 h2p_ld_acquire(const u32* p) {
   u32 v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -104,8 +107,10 @@ __device__ __forceinline__ u64 h2p_ld64(const u64* p) {
 // u32 br0[dcap], u32 bnres[dcap]
 struct H2D { u32* hdr; u64* dkey; u64* bkey; u32* br0; u32* bnres; };
 __device__ __forceinline__ size_t h2d_bytes(u32 dcap) { return 32 + (size_t)dcap * 24; }
-__device__ __forceinline__ H2D h2d_at(u64 base, u32 dcap, u32 par) {
-  unsigned char* p = reinterpret_cast<unsigned char*>(base) + (size_t)par * h2d_bytes(dcap);
+// (push model: rank r WRITES its list into slot [par][r] of every rank's block; a rank only ever READS its own block, whose
+//  home is its own L2 -- remote lines cached by a long-running kernel are never relied upon)
+__device__ __forceinline__ H2D h2d_at(u64 base, u32 dcap, u32 par, int world, int src) {
+  unsigned char* p = reinterpret_cast<unsigned char*>(base) + ((size_t)par * world + src) * h2d_bytes(dcap);
   H2D d;
   d.hdr = reinterpret_cast<u32*>(p);
   d.dkey = reinterpret_cast<u64*>(p + 32);
@@ -117,8 +122,8 @@ __device__ __forceinline__ H2D h2d_at(u64 base, u32 dcap, u32 par) {
 // export block of one parity: u32 hdr[8] = {n, halt_req}, u64 key[xcap], u32 cnt[xcap], u32 r0[xcap], u32 nres[xcap]
 struct H2X { u32* hdr; u64* key; u32* cnt; u32* r0; u32* nres; };
 __device__ __forceinline__ size_t h2x_bytes(u32 xcap) { return 32 + (size_t)xcap * 20; }
-__device__ __forceinline__ H2X h2x_at(u64 base, u32 xcap, u32 par) {
-  unsigned char* p = reinterpret_cast<unsigned char*>(base) + (size_t)par * h2x_bytes(xcap);
+__device__ __forceinline__ H2X h2x_at(u64 base, u32 xcap, u32 par, int world, int src) {
+  unsigned char* p = reinterpret_cast<unsigned char*>(base) + ((size_t)par * world + src) * h2x_bytes(xcap);
   H2X x;
   x.hdr = reinterpret_cast<u32*>(p);
   x.key = reinterpret_cast<u64*>(p + 32);
@@ -136,6 +141,10 @@ __device__ __forceinline__ u64 h2_now() {
 }
 __device__ __forceinline__ void h2_halt(u32* hs, u32 code) {
   if (atomicCAS(&hs[H2_HALT], 0u, code) == 0u) hs[H2_HALT_STEP] = hs[H2_STEP];
+}
+// progress marker of block 0 (readable from a second stream while the kernel runs: multi-GPU bring-up)
+__device__ __forceinline__ void h2_trace(u32* hs, u32 v) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) { *reinterpret_cast<volatile u32*>(hs + H2_TRACE) = v; __threadfence_system(); }
 }
 __device__ __forceinline__ bool h2_cbit(const u32* cbit, u32 s) { return (cbit[s >> 5] >> (s & 31u)) & 1u; }
 
@@ -213,9 +222,9 @@ __device__ __forceinline__ void h2_death(const H2Args& a, u64 key) {
   const u32 s = gb_slot_of(key, 64 - a.log2ns);
   atomicSub(&a.slots[s], 1u);
   if (a.world > 1) {                               // the other ranks replay it on their copies
-    const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, a.hs[H2_DSEQ] & 1u);
-    const u32 g = atomicAdd(&a.hs[H2_NDEATH], 1u);
-    if (g < a.dcap) d.dkey[g] = key; else a.hs[H2_HALT_REQ] = H2_HALT_TABLE;
+    const u32 g = atomicAdd(&a.hs[H2_NDEATH], 1u), par = a.hs[H2_DSEQ] & 1u;
+    if (g < a.dcap) { for (int q = 0; q < a.world; ++q) h2d_at(a.peer_d[q], a.dcap, par, a.world, a.rank).dkey[g] = key; }
+    else a.hs[H2_HALT_REQ] = H2_HALT_TABLE;
   }
   if (h2_cbit(a.cbit, s)) {
     const i64 t = h2_table_find(a, key);
@@ -229,9 +238,13 @@ __device__ __forceinline__ void h2_birth(const H2Args& a, u64 key, u32 left, u32
   // (sharded: whatever ends a period must end it on every rank -- requests travel with the deltas, the threshold test runs on
   //  the final global counters in the next iteration's first phase)
   if (dist) {
-    const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, a.hs[H2_DSEQ] & 1u);
-    const u32 g = atomicAdd(&a.hs[H2_NBIRTH], 1u);
-    if (g < a.dcap) { d.bkey[g] = key; d.br0[g] = r0; d.bnres[g] = nres; } else a.hs[H2_HALT_REQ] = H2_HALT_TABLE;
+    const u32 g = atomicAdd(&a.hs[H2_NBIRTH], 1u), par = a.hs[H2_DSEQ] & 1u;
+    if (g < a.dcap) {
+      for (int q = 0; q < a.world; ++q) {
+        const H2D d = h2d_at(a.peer_d[q], a.dcap, par, a.world, a.rank);
+        d.bkey[g] = key; d.br0[g] = r0; d.bnres[g] = nres;
+      }
+    } else a.hs[H2_HALT_REQ] = H2_HALT_TABLE;
   }
   if (h2_cbit(a.cbit, s)) {
     if (h2_table_add(a, key, r0, nres) < 0) { if (dist) a.hs[H2_HALT_REQ] = H2_HALT_TABLE; else a.hs[H2_PERIOD_OK] = 0u; }
@@ -251,12 +264,13 @@ __device__ void h2_signal_wait(const H2Args& a, int stage, u32 seq) {
     __threadfence_system();
     for (int q = 0; q < a.world; ++q)
       h2p_st_release(reinterpret_cast<u32*>(a.peer_f[q]) + stage * H2_MAXW + a.rank, seq);
+    __threadfence_system();
     const u32* mine = reinterpret_cast<const u32*>(a.peer_f[a.rank]) + stage * H2_MAXW;
     const u64 t0 = h2_now();
     bool ok = a.hs[H2_HALT] != H2_HALT_PEER;
     for (int q = 0; q < a.world && ok; ++q)
       while ((int)(h2p_ld_acquire(mine + q) - seq) < 0)
-        if (h2_now() - t0 > H2_TIMEOUT_NS) { h2_halt(a.hs, H2_HALT_PEER); ok = false; break; }
+        if (h2_now() - t0 > a.timeout_ns) { h2_halt(a.hs, H2_HALT_PEER); ok = false; break; }
     a.hs[H2_ST_WAIT_US] += (u32)((h2_now() - t0) / 1000ull);
   }
 }
@@ -266,7 +280,7 @@ __device__ void h2_apply_remote(const H2Args& a, u32 par, u32 cnt) {
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     u32 tot = 0, halt = 0, per = 0;
     for (int r = 0; r < a.world; ++r) {
-      const H2D d = h2d_at(a.peer_d[r], a.dcap, par);
+      const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, par, a.world, r);
       tot += h2p_ld32(d.hdr + 0);
       const u32 h = h2p_ld32(d.hdr + 1);
       if (!halt) halt = h;
@@ -279,7 +293,7 @@ __device__ void h2_apply_remote(const H2Args& a, u32 par, u32 cnt) {
   const i64 gtid = (i64)blockIdx.x * H2_THREADS + threadIdx.x, gsz = (i64)gridDim.x * H2_THREADS;
   for (int r = 0; r < a.world; ++r) {
     if (r == a.rank) continue;
-    const H2D d = h2d_at(a.peer_d[r], a.dcap, par);
+    const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, par, a.world, r);
     const u32 nd = min(h2p_ld32(d.hdr + 3), a.dcap), nb = min(h2p_ld32(d.hdr + 4), a.dcap);
     for (i64 i = gtid; i < nd; i += gsz) {
       const u64 key = h2p_ld64(d.dkey + i);
@@ -304,7 +318,7 @@ __device__ void h2_cross_check(const H2Args& a, u32 par, u32 thr) {
   if (blockIdx.x == 0 || gridDim.x < 2) return;
   const i64 gtid = (i64)(blockIdx.x - 1) * H2_THREADS + threadIdx.x, gsz = (i64)(gridDim.x - 1) * H2_THREADS;
   for (int r = 0; r < a.world; ++r) {
-    const H2D d = h2d_at(a.peer_d[r], a.dcap, par);
+    const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, par, a.world, r);
     const u32 nb = min(h2p_ld32(d.hdr + 4), a.dcap);
     for (i64 i = gtid; i < nb; i += gsz) {
       const u32 s = gb_slot_of(h2p_ld64(d.bkey + i), 64 - a.log2ns);
@@ -314,31 +328,40 @@ __device__ void h2_cross_check(const H2Args& a, u32 par, u32 thr) {
 }
 // period start: every rank publishes the exact (key, count, example window) entries of its shard; all ranks add the others'
 __device__ void h2_export_table(const H2Args& a, u32 par) {
-  const H2X x = h2x_at(a.peer_x[a.rank], a.xcap, par);
   const u32 nd = min(h2_ld(a.hs + H2_ND), (u32)a.M);
   const i64 gtid = (i64)blockIdx.x * H2_THREADS + threadIdx.x, gsz = (i64)gridDim.x * H2_THREADS;
   for (i64 i = gtid; i < nd && i < a.xcap; i += gsz) {
     const u32 sl = a.tlist[i];
-    x.key[i] = a.tk[sl]; x.cnt[i] = a.tc[sl]; x.r0[i] = a.tr0[sl]; x.nres[i] = a.tnres[sl];
+    const u64 k = a.tk[sl];
+    const u32 c = a.tc[sl], r0 = a.tr0[sl], nr = a.tnres[sl];
+    for (int q = 0; q < a.world; ++q) {
+      if (q == a.rank) continue;
+      const H2X x = h2x_at(a.peer_x[q], a.xcap, par, a.world, a.rank);
+      x.key[i] = k; x.cnt[i] = c; x.r0[i] = r0; x.nres[i] = nr;
+    }
   }
   if (gtid == 0) {
-    x.hdr[0] = min(nd, a.xcap);
-    x.hdr[1] = (nd > a.xcap || a.hs[H2_OVF]) ? (u32)H2_HALT_TABLE : (a.hs[H2_NCL] > a.hs[H2_CLCAP] ? (u32)H2_HALT_CAND : 0u);
+    const u32 halt = (nd > a.xcap || a.hs[H2_OVF]) ? (u32)H2_HALT_TABLE : (a.hs[H2_NCL] > a.hs[H2_CLCAP] ? (u32)H2_HALT_CAND : 0u);
+    for (int q = 0; q < a.world; ++q) {
+      const H2X x = h2x_at(a.peer_x[q], a.xcap, par, a.world, a.rank);
+      x.hdr[0] = min(nd, a.xcap); x.hdr[1] = halt;
+    }
   }
+  __threadfence_system();        // this thread's stores into the peers' blocks are performed before the barrier / the signal
 }
 __device__ void h2_import_tables(const H2Args& a, u32 par) {
   const i64 gtid = (i64)blockIdx.x * H2_THREADS + threadIdx.x, gsz = (i64)gridDim.x * H2_THREADS;
   if (gtid == 0) {
     u32 halt = 0;
     for (int r = 0; r < a.world; ++r) {
-      const u32 h = h2p_ld32(h2x_at(a.peer_x[r], a.xcap, par).hdr + 1);
+      const u32 h = h2p_ld32(h2x_at(a.peer_x[a.rank], a.xcap, par, a.world, r).hdr + 1);
       if (!halt) halt = h;
     }
     if (halt) h2_halt(a.hs, halt);
   }
   for (int r = 0; r < a.world; ++r) {
     if (r == a.rank) continue;
-    const H2X x = h2x_at(a.peer_x[r], a.xcap, par);
+    const H2X x = h2x_at(a.peer_x[a.rank], a.xcap, par, a.world, r);
     const u32 n = min(h2p_ld32(x.hdr + 0), a.xcap);
     for (i64 i = gtid; i < n; i += gsz) {
       const u32 c = h2p_ld32(x.cnt + i);
@@ -534,6 +557,7 @@ __device__ void h2_period_start(const H2Args& a, cg::grid_group& grid, unsigned 
     }
   }
   const int par = (int)h2_ld(hs + H2_PAR);
+  h2_trace(hs, 0x20000u | 1u);
   // (A) reset: table, candidate bitmap, counters
   if (t0) { hs[H2_C1] = 0; hs[H2_NCAND] = 0; hs[H2_NCL] = 0; hs[H2_NZ] = 0; hs[H2_OVF] = 0; hs[H2_ND] = 0; hs[H2_ST_PERIODS] += 1u; }
   const i64 gtid = (i64)blockIdx.x * H2_THREADS + threadIdx.x, gsz = (i64)gridDim.x * H2_THREADS;
@@ -593,6 +617,7 @@ __device__ void h2_period_start(const H2Args& a, cg::grid_group& grid, unsigned 
     return;
   }
   // (D) exact counts + pair list of the candidate slots
+  h2_trace(hs, 0x20000u | 4u);
   const u64 tm1 = t0 ? h2_now() : 0ull;
   {
     u32* s_set = reinterpret_cast<u32*>(smem);
@@ -604,10 +629,14 @@ __device__ void h2_period_start(const H2Args& a, cg::grid_group& grid, unsigned 
   grid.sync();
   if (a.world > 1) {       // the table becomes global: every rank adds the other ranks' exact counts of the same candidate slots
     const u32 xseq = h2_ld(hs + H2_XSEQ) + 1u;
+    h2_trace(hs, 0x10000u | 1u);
     h2_export_table(a, xseq & 1u);
     grid.sync();
+    h2_trace(hs, 0x10000u | 2u);
     h2_signal_wait(a, 1, xseq);
+    h2_trace(hs, 0x10000u | 3u);
     grid.sync();
+    h2_trace(hs, 0x10000u | 4u);
     h2_import_tables(a, xseq & 1u);
     if (t0) hs[H2_XSEQ] = xseq;
     grid.sync();
@@ -891,6 +920,7 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
     }
     u64 tm = t0 ? h2_now() : 0ull;
     const bool dist = a.world > 1;
+    h2_trace(hs, (loops << 8) | 1u);
     const u32 dseq0 = dist ? h2_ld(hs + H2_DSEQ) : 0u;
     h2_decide(a, smem);
     if (dist) h2_cross_check(a, dseq0 & 1u, h2_ld(hs + H2_THR));      // (previous iteration's created pairs, blocks 1..)
@@ -918,6 +948,7 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
     const u64 win = *reinterpret_cast<volatile u64*>(&a.hs64[0]);
     const u32 ref_r0 = h2_ld(hs + H2_WIN_R0), nres = h2_ld(hs + H2_WIN_NRES), cnt = h2_ld(hs + H2_WIN_CNT);
     const u32 new_tid = h2_ld(hs + H2_NTOK), ev0 = h2_ld(hs + H2_EVN), thr = h2_ld(hs + H2_THR);
+    h2_trace(hs, (loops << 8) | 2u);
     h2_flag(a, t, win);
     if (t0) a.hs64[H2_TW_P2] += h2_now() - tm;
     grid.sync();
@@ -939,7 +970,9 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
       if (t0) { hs[H2_HALT_REQ] = H2_HALT_EVLOG; hs[H2_NOCC] = 0; }
       nocc = 0;
     }
+    h2_trace(hs, (loops << 8) | 3u);
     h2_deaths(a, t, nocc, ref_r0, nres);
+    if (dist) __threadfence_system();              // (the keys pushed into the peers' blocks)
     if (t0) a.hs64[H2_TW_P3] += h2_now() - tm;
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P3] += n - tm; tm = n; }
@@ -951,11 +984,14 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
       grid.sync();
       continue;
     }
+    h2_trace(hs, (loops << 8) | 4u);
     h2_apply(a, t, nocc, win, new_tid, ev0);
     if (t0) a.hs64[H2_TW_P4] += h2_now() - tm;
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P4] += n - tm; tm = n; }
+    h2_trace(hs, (loops << 8) | 5u);
     h2_births_end(a, t, nocc, win, new_tid, thr, step, ev0);
+    if (dist) __threadfence_system();
     if (t0) a.hs64[H2_TW_P5] += h2_now() - tm;
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P5] += n - tm; tm = n; hs[H2_ST_LOOPS] += 1u; }
@@ -963,12 +999,17 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
       // publish this rank's deltas (header last), wait for every rank's, replay the others' on the local copies
       const u32 seq = dseq0 + 1u;
       if (t0) {
-        const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, seq & 1u);
-        d.hdr[0] = hs[H2_NOCC]; d.hdr[1] = hs[H2_HALT_REQ] ? hs[H2_HALT_REQ] : (bad3 ? bad3 : 0u); d.hdr[2] = hs[H2_PERIOD_REQ];
-        d.hdr[3] = hs[H2_NDEATH]; d.hdr[4] = hs[H2_NBIRTH];
+        for (int q = 0; q < a.world; ++q) {
+          const H2D d = h2d_at(a.peer_d[q], a.dcap, seq & 1u, a.world, a.rank);
+          d.hdr[0] = hs[H2_NOCC]; d.hdr[1] = hs[H2_HALT_REQ] ? hs[H2_HALT_REQ] : (bad3 ? bad3 : 0u); d.hdr[2] = hs[H2_PERIOD_REQ];
+          d.hdr[3] = hs[H2_NDEATH]; d.hdr[4] = hs[H2_NBIRTH];
+        }
       }
+      h2_trace(hs, (loops << 8) | 6u);
       h2_signal_wait(a, 0, seq);
+      h2_trace(hs, (loops << 8) | 7u);
       grid.sync();
+      h2_trace(hs, (loops << 8) | 8u);
       h2_apply_remote(a, seq & 1u, cnt);
       grid.sync();
       if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_XCH] += n - tm; }
@@ -989,7 +1030,7 @@ enum { HB_HS = 0, HB_HS64, HB_HSH0, HB_HSH1, HB_GLUE0, HB_GLUE1, HB_POS0, HB_POS
        HB_FLAGS, HB_RMARK, HB_SCRATCH, HB_POWTAB, HB_P, HB_RBINS, HB_R, HB_SLOTS, HB_LOG2NS, HB_BMAX, HB_CAND, HB_CAP, HB_CBIT,
        HB_TK, HB_TC, HB_TR0, HB_TNRES, HB_TLIST, HB_M, HB_CLKEY, HB_CLJ, HB_OCCJ, HB_OCCR, HB_STRBUF, HB_STRIDE, HB_ERANK, HB_EVL, HB_EVR, HB_EVP,
        HB_LKEY, HB_LCNT, HB_LR0, HB_LNRES, HB_LEVS, HB_LNK, HB_THRNUM, HB_STREAMING, HB_CTAS,
-       HB_RBASE, HB_WORLD, HB_RANK, HB_PEERS /* host table u64 [3][world]: delta / export / flag block of every rank */, HB_DCAP, HB_XCAP, HB_N };
+       HB_RBASE, HB_WORLD, HB_RANK, HB_PEERS /* host table u64 [3][world]: delta / export / flag block of every rank */, HB_DCAP, HB_XCAP, HB_TIMEOUT_MS, HB_N };
 
 __global__ void h2_set_target(u32* hs, u32 nsteps) { hs[H2_TARGET] = hs[H2_STEP] + nsteps; }
 
@@ -1023,6 +1064,7 @@ extern "C" int gb_h_loop2(const int64_t* b, int n_args, int nsteps, int final_co
   a.max_loops = (u32)(4 * nsteps + 64);
   a.rbase = (u32)b[HB_RBASE]; a.world = b[HB_WORLD] > 1 ? (int)b[HB_WORLD] : 1; a.rank = (int)b[HB_RANK];
   a.dcap = (u32)b[HB_DCAP]; a.xcap = (u32)b[HB_XCAP];
+  a.timeout_ns = b[HB_TIMEOUT_MS] > 0 ? (u64)b[HB_TIMEOUT_MS] * 1000000ull : H2_TIMEOUT_NS;
   for (int r = 0; r < H2_MAXW; ++r) a.peer_d[r] = a.peer_x[r] = a.peer_f[r] = 0;
   if (a.world > 1) {
     const u64* pt = (const u64*)b[HB_PEERS];
@@ -1083,7 +1125,7 @@ extern "C" int gb_rehash_tokens(const uint64_t* sym, const uint32_t* glue_res, c
 }
 
 // sizes of the symmetric block a sharded run allocates per rank (gb_peer_alloc): [delta x 2 | export x 2 | flags]
-extern "C" int64_t gb_h_loop2_delta_bytes(int64_t dcap) { return 2 * (32 + dcap * 24); }
-extern "C" int64_t gb_h_loop2_export_bytes(int64_t xcap) { return 2 * (32 + xcap * 20); }
+extern "C" int64_t gb_h_loop2_delta_bytes(int64_t dcap, int world) { return 2 * (int64_t)world * (32 + dcap * 24); }
+extern "C" int64_t gb_h_loop2_export_bytes(int64_t xcap, int world) { return 2 * (int64_t)world * (32 + xcap * 20); }
 extern "C" int64_t gb_h_loop2_flag_bytes(void) { return 2 * H2_MAXW * 4; }
 extern "C" int gb_h_loop2_max_world(void) { return H2_MAXW; }

@@ -9,6 +9,7 @@ matrix (algo.py:184-211).
 import ctypes as C
 import os
 import json
+import time
 import types
 import math
 
@@ -90,6 +91,13 @@ def _dev():
     return torch.device("cuda", torch.cuda.current_device())
 
 
+def _dbg(msg):
+    """GEOBPE_DEBUG=1: synchronise and print a progress marker (multi-GPU bring-up)"""
+    if os.environ.get("GEOBPE_DEBUG"):
+        torch.cuda.synchronize()
+        print(f"[geobpe rank {os.environ.get('RANK', 0)}] {msg}", flush=True)
+
+
 def _empty(n, dtype):
     return torch.empty(max(int(n), 1), dtype=dtype, device=_dev())
 
@@ -117,7 +125,10 @@ class Backbones:
         self.lens_host = np.diff(offsets)
         if self.R >= (1 << 32) - 2:
             raise ValueError("a shard holds at most 2^32-2 residues (u32 positions)")
-        self.vals = torch.from_numpy(vals).pin_memory().to(_dev(), non_blocking=True)
+        hv = torch.from_numpy(vals)
+        if vals.nbytes >= (1 << 20):                 # large inputs go through pinned memory; the small per-key windows of
+            hv = hv.pin_memory()                     # geo_coords / compute_coords are not worth a cudaHostAlloc
+        self.vals = hv.to(_dev(), non_blocking=True)
         self.offsets = torch.from_numpy(offsets).to(_dev())
         self.bb = _empty(self.R, torch.int32)
         _lib.call("gb_residue_backbone", _lib.ptr(self.offsets), self.S, self.R, _lib.ptr(self.bb))
@@ -1161,7 +1172,7 @@ class Learner:
               MISMATCH=25, NEWT=26, OVF=27, ERR=28, HALT_STEP=29, NTMAX=30, CMPT=31, FRESH=32, ND=33, NZ=34, MPREV=35,
               ST_PERIODS=36, ST_CROSS=37, ST_INCONCL=38, ST_COMPACT=39, ST_R2=40, ST_FULL=41, ST_LOOPS=42, PERIOD_LEN=43,
               ST_MAXNCL=44, ST_MAXND=45, ST_MAXNCAND=46, ST_TIES=47,
-              HALT_REQ=48, PERIOD_REQ=49, NDEATH=50, NBIRTH=51, DSEQ=52, XSEQ=53, ST_WAIT_US=54)
+              HALT_REQ=48, PERIOD_REQ=49, NDEATH=50, NBIRTH=51, DSEQ=52, XSEQ=53, ST_WAIT_US=54, TRACE=55)
     H2_TIMES = ("period_start", "decide", "flag", "deaths", "apply", "births", "compaction", "candidate_pass",
                 "flag_block0_work", "deaths_block0_work", "apply_block0_work", "births_block0_work", "exchange")
     H2_HALT_NAMES = {**HALT_NAMES, 10: "internal", 11: "guard"}
@@ -1186,7 +1197,7 @@ class Learner:
             pad = _zeros(9 * Rmax, torch.int16).view(9, Rmax)
             pad[:, :self.bb.R] = self.rbins.view(9, self.bb.R)
             allr = _empty(comm.world * 9 * Rmax, torch.int16)
-            comm.all_gather_into(allr, pad.view(-1))
+            comm.all_gather_into(allr.view(torch.uint8), pad.view(-1).view(torch.uint8))      # (NCCL has no 16-bit integer type)
             allr = allr.view(comm.world, 9, Rmax)
             g = _empty(9 * hl.R_total, torch.int16).view(9, hl.R_total)
             o = 0
@@ -1200,6 +1211,7 @@ class Learner:
                 self.sketch = SlotSketch(Tg)
             mw = comm.all_reduce(torch.tensor([maxwin], device=_dev(), dtype=torch.int64), "max")
             maxwin = int(mw.item())
+            _dbg(f"h2_init: rbins replicated, R_total {hl.R_total}, rbase {hl.rbase}, slots 2^{self.sketch.log2ns}")
         sk = self.sketch
         hl.hs = _zeros(64, torch.int32)
         hl.hs64 = _zeros(16, torch.int64)
@@ -1217,7 +1229,7 @@ class Learner:
         hl.occ_j = _empty(ts.cap, torch.int32)
         hl.occ_r = _empty(ts.cap, torch.int32)
         hl.nargs = lib.gb_h_loop2_nargs()
-        hl.dcap = next_pow2(max(1 << 16, self.bb.R // 8))
+        hl.dcap = next_pow2(max(1 << 16, self.bb.R // 64))
         hl.xcap = 1 << 17
         hl.thr_num = int(os.environ.get("GEOBPE_H2_THR16", 14))
         hl.ctas = int(os.environ.get("GEOBPE_H2_CTAS", 2))
@@ -1235,6 +1247,7 @@ class Learner:
         self._h2_table(hl.M)
         if comm is not None:
             self._h2_peer_setup()
+            _dbg("h2_init: peer blocks mapped")
 
     def _h2_table(self, M):
         hl = self.hl
@@ -1260,8 +1273,8 @@ class Learner:
         while hl.xcap < hl.M // 2:
             hl.xcap *= 2
         al = lambda n: (int(n) + 255) // 256 * 256
-        o_x = al(lib.gb_h_loop2_delta_bytes(hl.dcap))
-        o_f = o_x + al(lib.gb_h_loop2_export_bytes(hl.xcap))
+        o_x = al(lib.gb_h_loop2_delta_bytes(hl.dcap, comm.world))
+        o_f = o_x + al(lib.gb_h_loop2_export_bytes(hl.xcap, comm.world))
         total = o_f + al(lib.gb_h_loop2_flag_bytes())
         pr = types.SimpleNamespace(base=None, opened=[], lib=lib)
         base, h = C.c_void_p(), (C.c_ubyte * 64)()
@@ -1304,7 +1317,8 @@ class Learner:
                 P(hl.log["cnt"]), P(hl.log["r0"]), P(hl.log["nres"]), P(hl.log["evstart"]), P(hl.log["nk"]),
                 hl.thr_num, 1 if 16 * ts.cap > SlotSketch.STREAM_BYTES else 0, hl.ctas,
                 hl.rbase, self.comm.world if self.comm is not None else 1, self.comm.rank if self.comm is not None else 0,
-                C.addressof(hl.peer.table) if hl.peer is not None else 0, hl.dcap, hl.xcap]
+                C.addressof(hl.peer.table) if hl.peer is not None else 0, hl.dcap, hl.xcap,
+                int(os.environ.get("GEOBPE_PEER_TIMEOUT_MS", 20000))]
         assert len(vals) == hl.nargs, (len(vals), hl.nargs)
         return (C.c_int64 * len(vals))(*[v if v < (1 << 63) else v - (1 << 64) for v in vals])
 
@@ -1341,7 +1355,9 @@ class Learner:
                 e1.record()
                 ev.append((e0, e1, ts.T))
             if self.comm is not None:            # replicated global counters (once per recount; kept exact by the delta exchange)
+                _dbg("push_state: local slot count done")
                 self.comm.all_reduce(sk.slots, "sum")
+                _dbg("push_state: slot counters reduced")
             hl.slots_valid = True
 
     def _h2_enqueue(self, nsteps):
@@ -1358,7 +1374,9 @@ class Learner:
     def _h2_flush(self, final_compact):
         hl = self.hl
         if hl.lazy > 0 or final_compact:
+            _dbg(f"launching the loop kernel: {hl.lazy} iterations")
             _lib.call_n("gb_h_loop2", 2, hl.args, hl.nargs, hl.lazy, final_compact)
+            _dbg("loop kernel finished")
             hl.stats["launches"] += 1
             hl.lazy = 0
 
@@ -1405,8 +1423,10 @@ class Learner:
             hl.ntmax = max(hl.ntmax, int(h[H["NTMAX"]]))
             rest = want - done
             if halt in (5, 8, 9, 10):
+                where = (f" (iteration {int(h[H['STEP']])}, exchange {int(h[H['DSEQ']])}, period exchange {int(h[H['XSEQ']])}, "
+                         f"marker {int(h[H['TRACE']]):#x})") if self.comm is not None else ""
                 raise RuntimeError({5: "merge-event log overflow", 8: "flagged occurrences differ from the exact pair count",
-                                    9: "peer timeout", 10: "incremental pair counts became inconsistent"}[halt])
+                                    9: "a peer rank did not signal in time", 10: "incremental pair counts became inconsistent"}[halt] + where)
             if halt == 6:
                 raise IndexError("no adjacent pairs left (the reference's peekitem(0) raises here too)")
             if halt:

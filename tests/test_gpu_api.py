@@ -220,3 +220,19 @@ def test_induce_device_replay_equals_host_replay(monkeypatch):
     assert outs[0][4] == outs[1][4], "events per vocabulary merge differ"
     assert outs[0] == outs[1]
     assert outs[0][5] > 10
+
+
+@pytest.mark.parametrize("hp", [HP_H, HP_M], ids=["H", "M"])
+def test_token_stream_export_equals_per_token_quantize(hp):
+    """f-3: one device pass over the token arrays against the reference-shaped per-token host loop, + codebook statistics"""
+    import torch
+    from foldingdiff.plotting import get_codebook_utility
+    bpe, _ = learn(hp, S=30, n=44, seed=61, steps=35)
+    want = [bpe.quantize(t.tokenize()) for t in bpe.tokenizers]
+    got = bpe.quantize(bpe.tokenizers)
+    assert got == want
+    ids, offs = bpe.token_stream()
+    assert offs[-1] == ids.numel() == sum(len(w) for w in want)
+    u = bpe.codebook_utility()
+    v = get_codebook_utility(torch.as_tensor(sum(want, [])), bpe.vocab_size)
+    assert u.keys() == v.keys() and all(abs(u[k] - v[k]) < 1e-5 for k in u)

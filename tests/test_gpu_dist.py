@@ -19,6 +19,7 @@ def worker(rank, world, port, q, mode, uneven=False):
     async_steps = mode != "host"
     os.environ["GEOBPE_PEER"] = "1" if mode == "peer" else "0"
     os.environ["GEOBPE_LOOP"] = "2" if mode == "loop2" else "1"
+    os.environ.setdefault("GEOBPE_PEER_TIMEOUT_MS", "8000")
     for p in (os.path.join(ROOT, "pt-bpe_b200"),):
         sys.path.insert(0, p)
     import torch.distributed as dist
@@ -70,8 +71,13 @@ def test_two_gpu_h_mode_matches_oracle(mode, uneven):
     ps = [ctx.Process(target=worker, args=(r, 2, port + {"peer": 0, "nccl": 7, "host": 14, "loop2": 21}[mode] + int(uneven), q, mode, uneven))
           for r in range(2)]
     [p.start() for p in ps]
-    res = sorted(q.get(timeout=300) for _ in ps)
-    [p.join(60) for p in ps]
+    try:
+        res = sorted(q.get(timeout=150) for _ in ps)
+        [p.join(60) for p in ps]
+    finally:                         # a failed rank must not leave the other one spinning on the box
+        for p in ps:
+            if p.is_alive():
+                p.kill()
     vals, offs = synthetic.generate(GEN[0], GEN[1], seed=GEN[2], ragged=True)
     ora = O.BPE(synthetic.to_structures(vals, offs), res_init=True, seed=0, rmsd_partition_min_size=float("inf"), **HP)
     ora.initialize(); ora.bin()
