@@ -43,7 +43,7 @@ namespace cg = cooperative_groups;
 #define H2_CHUNK (H2_THREADS * 8)
 #define H2_PROBES 1024
 
-enum { H2_HALT_TIES = 1, H2_HALT_CAND = 2, H2_HALT_COLLISION = 3, H2_HALT_TABLE = 4, H2_HALT_EVLOG = 5, H2_HALT_EMPTY = 6,
+enum { H2_HALT_DIVERGED = 12, H2_HALT_TIES = 1, H2_HALT_CAND = 2, H2_HALT_COLLISION = 3, H2_HALT_TABLE = 4, H2_HALT_EVLOG = 5, H2_HALT_EMPTY = 6,
        H2_HALT_STEPS = 7, H2_HALT_COUNT = 8, H2_HALT_PEER = 9, H2_HALT_INTERNAL = 10, H2_HALT_GUARD = 11 };
 
 // device state block (u32 words)
@@ -53,12 +53,13 @@ enum {
   H2_MISMATCH, H2_NEWT, H2_OVF, H2_ERR, H2_HALT_STEP, H2_NTMAX, H2_CMPT, H2_FRESH, H2_ND, H2_NZ, H2_MPREV,
   H2_ST_PERIODS, H2_ST_CROSS, H2_ST_INCONCL, H2_ST_COMPACT, H2_ST_R2, H2_ST_FULL, H2_ST_LOOPS, H2_PERIOD_LEN,
   H2_ST_MAXNCL, H2_ST_MAXND, H2_ST_MAXNCAND, H2_ST_TIES,
-  H2_HALT_REQ, H2_PERIOD_REQ, H2_NDEATH, H2_NBIRTH, H2_DSEQ, H2_XSEQ, H2_ST_WAIT_US, H2_TRACE,
+  H2_HALT_REQ, H2_PERIOD_REQ, H2_NDEATH, H2_NBIRTH, H2_DSEQ, H2_XSEQ, H2_ST_WAIT_US, H2_TRACE, H2_WAIT_STAGE, H2_WAIT_SEQ, H2_WAIT_SEEN0, H2_WAIT_SEEN1, H2_ST_RETRY, H2_XCROSS,
   H2_WORDS = 64
 };
 // hs64: [0] popped key, [1] spare, [2..] nanoseconds accumulated per phase (block 0's view)
 enum { H2_TM_PS = 2, H2_TM_P1, H2_TM_P2, H2_TM_P3, H2_TM_P4, H2_TM_P5, H2_TM_CMP, H2_TM_CAND,
-       H2_TW_P2 /* block 0's own work (before the barrier) */, H2_TW_P3, H2_TW_P4, H2_TW_P5, H2_TM_XCH, H2_W64 = 16 };
+       H2_TW_P2 /* block 0's own work (before the barrier) */, H2_TW_P3, H2_TW_P4, H2_TW_P5, H2_TM_XCH,
+       H2_CK_OUT = 16 /* checksum of the keys this rank pushed this iteration */, H2_CK_ACC, H2_CK_EXP, H2_W64 = 32 };
 
 struct H2Args {
   u32* hs; u64* hs64;
@@ -225,6 +226,7 @@ __device__ __forceinline__ void h2_death(const H2Args& a, u64 key) {
     const u32 g = atomicAdd(&a.hs[H2_NDEATH], 1u), par = a.hs[H2_DSEQ] & 1u;
     if (g < a.dcap) { for (int q = 0; q < a.world; ++q) h2d_at(a.peer_d[q], a.dcap, par, a.world, a.rank).dkey[g] = key; }
     else a.hs[H2_HALT_REQ] = H2_HALT_TABLE;
+    atomicAdd(&a.hs64[H2_CK_OUT], key);
   }
   if (h2_cbit(a.cbit, s)) {
     const i64 t = h2_table_find(a, key);
@@ -245,6 +247,7 @@ __device__ __forceinline__ void h2_birth(const H2Args& a, u64 key, u32 left, u32
         d.bkey[g] = key; d.br0[g] = r0; d.bnres[g] = nres;
       }
     } else a.hs[H2_HALT_REQ] = H2_HALT_TABLE;
+    atomicAdd(&a.hs64[H2_CK_OUT], 3ull * key + r0);
   }
   if (h2_cbit(a.cbit, s)) {
     if (h2_table_add(a, key, r0, nres) < 0) { if (dist) a.hs[H2_HALT_REQ] = H2_HALT_TABLE; else a.hs[H2_PERIOD_OK] = 0u; }
@@ -270,8 +273,34 @@ __device__ void h2_signal_wait(const H2Args& a, int stage, u32 seq) {
     bool ok = a.hs[H2_HALT] != H2_HALT_PEER;
     for (int q = 0; q < a.world && ok; ++q)
       while ((int)(h2p_ld_acquire(mine + q) - seq) < 0)
-        if (h2_now() - t0 > a.timeout_ns) { h2_halt(a.hs, H2_HALT_PEER); ok = false; break; }
+        if (h2_now() - t0 > a.timeout_ns) {
+          a.hs[H2_WAIT_STAGE] = (u32)stage; a.hs[H2_WAIT_SEQ] = seq;              // what this rank was waiting for, what it saw
+          a.hs[H2_WAIT_SEEN0] = h2p_ld_acquire(mine + 0); a.hs[H2_WAIT_SEEN1] = h2p_ld_acquire(mine + 1);
+          h2_halt(a.hs, H2_HALT_PEER); ok = false; break;
+        }
     a.hs[H2_ST_WAIT_US] += (u32)((h2_now() - t0) / 1000ull);
+  }
+}
+// checksum of what has LANDED in this rank's inbox (the other ranks' slots), to be compared with the sum the writers announce
+__device__ void h2_inbox_checksum(const H2Args& a, u32 par) {
+  const i64 gtid = (i64)blockIdx.x * H2_THREADS + threadIdx.x, gsz = (i64)gridDim.x * H2_THREADS;
+  u64 acc = 0;
+  for (int r = 0; r < a.world; ++r) {
+    if (r == a.rank) continue;
+    const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, par, a.world, r);
+    const u32 nd = min(h2p_ld32(d.hdr + 3), a.dcap), nb = min(h2p_ld32(d.hdr + 4), a.dcap);
+    for (i64 i = gtid; i < nd; i += gsz) acc += h2p_ld64(d.dkey + i);
+    for (i64 i = gtid; i < nb; i += gsz) acc += 3ull * h2p_ld64(d.bkey + i) + h2p_ld32(d.br0 + i);
+  }
+  if (acc) atomicAdd(&a.hs64[H2_CK_ACC], acc);
+  if (gtid == 0) {
+    u64 e = 0;
+    for (int r = 0; r < a.world; ++r)
+      if (r != a.rank) {
+        const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, par, a.world, r);
+        e += (u64)h2p_ld32(d.hdr + 5) | ((u64)h2p_ld32(d.hdr + 6) << 32);
+      }
+    a.hs64[H2_CK_EXP] = e;
   }
 }
 // replay the other ranks' deltas of this iteration on the local copies; block 0 thread 0 folds the headers
@@ -285,6 +314,7 @@ __device__ void h2_apply_remote(const H2Args& a, u32 par, u32 cnt) {
       const u32 h = h2p_ld32(d.hdr + 1);
       if (!halt) halt = h;
       per |= h2p_ld32(d.hdr + 2);
+      if (h2p_ld32(d.hdr + 7) != (cnt ^ (u32)*reinterpret_cast<volatile u64*>(&a.hs64[0])) && !halt) halt = H2_HALT_DIVERGED;
     }
     if (halt) h2_halt(hs, halt);
     else if (tot != cnt) h2_halt(hs, H2_HALT_COUNT);
@@ -322,7 +352,7 @@ __device__ void h2_cross_check(const H2Args& a, u32 par, u32 thr) {
     const u32 nb = min(h2p_ld32(d.hdr + 4), a.dcap);
     for (i64 i = gtid; i < nb; i += gsz) {
       const u32 s = gb_slot_of(h2p_ld64(d.bkey + i), 64 - a.log2ns);
-      if (!h2_cbit(a.cbit, s) && a.slots[s] >= thr) { a.hs[H2_PERIOD_OK] = 0u; a.hs[H2_ST_CROSS] = 1u; }
+      if (!h2_cbit(a.cbit, s) && a.slots[s] >= thr) a.hs[H2_XCROSS] = 1u;
     }
   }
 }
@@ -779,7 +809,6 @@ __device__ void h2_decide(const H2Args& a, unsigned char* smem) {
     hs[H2_FRESH] = 0; hs[H2_P1] = 0;
     hs[H2_NOCC] = 0; hs[H2_MISMATCH] = 0; hs[H2_NEWT] = 0;
     hs[H2_NDEATH] = 0; hs[H2_NBIRTH] = 0; hs[H2_HALT_REQ] = 0; hs[H2_PERIOD_REQ] = 0;
-    if (a.world > 1) hs[H2_DSEQ] += 1u;            // this iteration's delta exchange (low bit = buffer parity)
   }
 }
 
@@ -937,12 +966,13 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
       grid.sync();
       continue;
     }
-    if (dist && !h2_ld(hs + H2_PERIOD_OK)) {         // a created pair lifted a slot to the threshold: the decision is void
-      grid.sync();
-      if (t0 && h2_ld(hs + H2_DSEQ) != dseq0) hs[H2_DSEQ] = dseq0;   // (no exchange happened for the void decision)
+    if (dist && h2_ld(hs + H2_XCROSS)) {             // a created pair lifted a slot to the threshold: the decision is void
+      grid.sync();                                   // (every CTA has read the word before the control words change)
+      if (t0) { hs[H2_XCROSS] = 0; hs[H2_PERIOD_OK] = 0; hs[H2_ST_CROSS] += 1u; }
       grid.sync();
       continue;
     }
+    if (dist && t0) hs[H2_DSEQ] = dseq0 + 1u;        // this iteration's delta exchange (low bit = buffer parity; read from P3 on)
     const int par = (int)h2_ld(hs + H2_PAR);
     const H2Tok t = h2_tok(a, par);
     const u64 win = *reinterpret_cast<volatile u64*>(&a.hs64[0]);
@@ -972,7 +1002,7 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
     }
     h2_trace(hs, (loops << 8) | 3u);
     h2_deaths(a, t, nocc, ref_r0, nres);
-    if (dist) __threadfence_system();              // (the keys pushed into the peers' blocks)
+    if (dist && (threadIdx.x & 31) == 0) __threadfence_system();     // (lane 0 pushed this warp's keys into the peers' blocks)
     if (t0) a.hs64[H2_TW_P3] += h2_now() - tm;
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P3] += n - tm; tm = n; }
@@ -1003,12 +1033,35 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
           const H2D d = h2d_at(a.peer_d[q], a.dcap, seq & 1u, a.world, a.rank);
           d.hdr[0] = hs[H2_NOCC]; d.hdr[1] = hs[H2_HALT_REQ] ? hs[H2_HALT_REQ] : (bad3 ? bad3 : 0u); d.hdr[2] = hs[H2_PERIOD_REQ];
           d.hdr[3] = hs[H2_NDEATH]; d.hdr[4] = hs[H2_NBIRTH];
+          const u64 ck = a.hs64[H2_CK_OUT];
+          d.hdr[5] = (u32)ck; d.hdr[6] = (u32)(ck >> 32); d.hdr[7] = cnt ^ (u32)win;
         }
+        a.hs64[H2_CK_OUT] = 0ull;
       }
       h2_trace(hs, (loops << 8) | 6u);
       h2_signal_wait(a, 0, seq);
       h2_trace(hs, (loops << 8) | 7u);
       grid.sync();
+      // the other ranks' lists must have LANDED completely before they are replayed: compare the checksum of what is visible here
+      // with the sum the writers announce; re-read until they agree (bounded)
+      bool landed = false;
+      for (int attempt = 0; attempt < 2000 && !landed; ++attempt) {
+        if (t0) a.hs64[H2_CK_ACC] = 0ull;
+        grid.sync();
+        h2_inbox_checksum(a, seq & 1u);
+        grid.sync();
+        landed = *reinterpret_cast<volatile u64*>(&a.hs64[H2_CK_ACC]) == *reinterpret_cast<volatile u64*>(&a.hs64[H2_CK_EXP]);
+        if (!landed) {                               // (every CTA has compared before the accumulator is reset)
+          grid.sync();
+          if (t0) hs[H2_ST_RETRY] += 1u;
+        }
+      }
+      if (!landed) {
+        grid.sync();
+        if (t0) h2_halt(hs, H2_HALT_DIVERGED);
+        grid.sync();
+        continue;
+      }
       h2_trace(hs, (loops << 8) | 8u);
       h2_apply_remote(a, seq & 1u, cnt);
       grid.sync();

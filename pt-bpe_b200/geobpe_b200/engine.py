@@ -1172,7 +1172,7 @@ class Learner:
               MISMATCH=25, NEWT=26, OVF=27, ERR=28, HALT_STEP=29, NTMAX=30, CMPT=31, FRESH=32, ND=33, NZ=34, MPREV=35,
               ST_PERIODS=36, ST_CROSS=37, ST_INCONCL=38, ST_COMPACT=39, ST_R2=40, ST_FULL=41, ST_LOOPS=42, PERIOD_LEN=43,
               ST_MAXNCL=44, ST_MAXND=45, ST_MAXNCAND=46, ST_TIES=47,
-              HALT_REQ=48, PERIOD_REQ=49, NDEATH=50, NBIRTH=51, DSEQ=52, XSEQ=53, ST_WAIT_US=54, TRACE=55)
+              HALT_REQ=48, PERIOD_REQ=49, NDEATH=50, NBIRTH=51, DSEQ=52, XSEQ=53, ST_WAIT_US=54, TRACE=55, WAIT_STAGE=56, WAIT_SEQ=57, WAIT_SEEN0=58, WAIT_SEEN1=59, ST_RETRY=60, XCROSS=61)
     H2_TIMES = ("period_start", "decide", "flag", "deaths", "apply", "births", "compaction", "candidate_pass",
                 "flag_block0_work", "deaths_block0_work", "apply_block0_work", "births_block0_work", "exchange")
     H2_HALT_NAMES = {**HALT_NAMES, 10: "internal", 11: "guard"}
@@ -1194,6 +1194,7 @@ class Learner:
             if hl.R_total >= (1 << 32) - 2:
                 raise ValueError("a sharded run holds at most 2^32-2 residues in total (u32 example windows)")
             Rmax = max(R_all)
+            self.hl_R_max = Rmax                 # buffer sizes that define the symmetric block's layout must agree on every rank
             pad = _zeros(9 * Rmax, torch.int16).view(9, Rmax)
             pad[:, :self.bb.R] = self.rbins.view(9, self.bb.R)
             allr = _empty(comm.world * 9 * Rmax, torch.int16)
@@ -1214,7 +1215,7 @@ class Learner:
             _dbg(f"h2_init: rbins replicated, R_total {hl.R_total}, rbase {hl.rbase}, slots 2^{self.sketch.log2ns}")
         sk = self.sketch
         hl.hs = _zeros(64, torch.int32)
-        hl.hs64 = _zeros(16, torch.int64)
+        hl.hs64 = _zeros(32, torch.int64)
         hl.stride = ((39 * maxwin + 200) + 127) // 128 * 128
         hl.strbuf = _zeros(self.HL_TB_CAP * hl.stride, torch.uint8)
         hl.log_cap = self.HL_LOG_CAP
@@ -1229,10 +1230,10 @@ class Learner:
         hl.occ_j = _empty(ts.cap, torch.int32)
         hl.occ_r = _empty(ts.cap, torch.int32)
         hl.nargs = lib.gb_h_loop2_nargs()
-        hl.dcap = next_pow2(max(1 << 16, self.bb.R // 64))
+        hl.dcap = next_pow2(max(1 << 16, (self.hl_R_max if hasattr(self, 'hl_R_max') else self.bb.R) // 64))
         hl.xcap = 1 << 17
         hl.thr_num = int(os.environ.get("GEOBPE_H2_THR16", 14))
-        hl.ctas = int(os.environ.get("GEOBPE_H2_CTAS", 2))
+        hl.ctas = int(os.environ.get("GEOBPE_H2_CTAS", 1))     # one CTA per SM: cheaper grid barriers (measured 45 vs 56 us / iteration)
         hl.period = 64                 # (reported by bench.py; periods end on the device when the threshold is crossed)
         hl.lazy = 0
         hl.slots_valid = False
@@ -1422,11 +1423,14 @@ class Learner:
             hl.r2 += int(h[H["ST_R2"]])
             hl.ntmax = max(hl.ntmax, int(h[H["NTMAX"]]))
             rest = want - done
-            if halt in (5, 8, 9, 10):
+            hl.stats["inbox_rereads"] = hl.stats.get("inbox_rereads", 0) + int(h[H["ST_RETRY"]])
+            if halt in (5, 8, 9, 10, 12):
                 where = (f" (iteration {int(h[H['STEP']])}, exchange {int(h[H['DSEQ']])}, period exchange {int(h[H['XSEQ']])}, "
-                         f"marker {int(h[H['TRACE']]):#x})") if self.comm is not None else ""
+                         f"marker {int(h[H['TRACE']]):#x}; waited for stage {int(h[H['WAIT_STAGE']])} seq {int(h[H['WAIT_SEQ']])}, flags seen "
+                         f"{int(h[H['WAIT_SEEN0']])} {int(h[H['WAIT_SEEN1']])}, rank {self.comm.rank})") if self.comm is not None else ""
                 raise RuntimeError({5: "merge-event log overflow", 8: "flagged occurrences differ from the exact pair count",
-                                    9: "a peer rank did not signal in time", 10: "incremental pair counts became inconsistent"}[halt] + where)
+                                    9: "a peer rank did not signal in time", 10: "incremental pair counts became inconsistent",
+                                    12: "the ranks' replicated pair counts diverged"}[halt] + where)
             if halt == 6:
                 raise IndexError("no adjacent pairs left (the reference's peekitem(0) raises here too)")
             if halt:
