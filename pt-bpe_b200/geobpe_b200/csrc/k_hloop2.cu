@@ -82,6 +82,7 @@ struct H2Args {
   u64 peer_x[H2_MAXW];            // every rank's export blocks  [2 parities][header | key, count, r0, nres]
   u64 peer_f[H2_MAXW];            // every rank's flag rows      u32 [2 stages][H2_MAXW]
   u32 dcap, xcap;
+  int verify_inbox;               // re-read the inbox until its checksum equals the sum the writers announce (bring-up aid)
   u64 timeout_ns;                 // a rank that sees no signal from a peer for this long halts (code 9) instead of spinning on
 };
 
@@ -836,7 +837,7 @@ __device__ void h2_unflag(const H2Args& a, u32 nocc) {
 }
 
 // ---- P3: exact window check, overlap rule, the pairs the merges destroy (one warp per occurrence) -------------------
-__device__ void h2_deaths(const H2Args& a, const H2Tok& t, u32 nocc, u32 ref_r0, u32 nres) {
+__device__ void h2_deaths(const H2Args& a, const H2Tok& t, u32 nocc, u32 ref_r0, u32 nres, bool& pushed) {
   const unsigned lane = threadIdx.x & 31;
   const u32 wid = (blockIdx.x * H2_THREADS + threadIdx.x) >> 5, nw = gridDim.x * (H2_THREADS / 32);
   for (u32 i = wid; i < nocc; i += nw) {
@@ -856,7 +857,7 @@ __device__ void h2_deaths(const H2Args& a, const H2Tok& t, u32 nocc, u32 ref_r0,
     if (bad) atomicAdd(&a.hs[H2_MISMATCH], 1u);
     if (a.rmark[j0]) continue;                 // not a run head: the pair to its left is an occurrence too
     const u32 q = h2_prev_live(t, j0);
-    if (q != 0xFFFFFFFFu && !(t.glue[q] & GB_LAST_FLAG)) h2_death(a, h2_pair_key(a, t, q, j0));
+    if (q != 0xFFFFFFFFu && !(t.glue[q] & GB_LAST_FLAG)) { h2_death(a, h2_pair_key(a, t, q, j0)); pushed = true; }
     // the head walks its run: the 1st, 3rd, ... occurrence merges (flags 2), the others lost their left token (bpe.py:1909-1914)
     u32 j = j0, tail = j0;
     bool keep = true, last_kept = false;
@@ -871,7 +872,7 @@ __device__ void h2_deaths(const H2Args& a, const H2Tok& t, u32 nocc, u32 ref_r0,
     if (last_kept && !(t.glue[tail] & GB_LAST_FLAG)) {
       const u32 x = tail + 1u + (t.ls[tail] >> 16);
       // (a flagged right neighbour is the head of the next run: it accounts for this pair as its own left pair)
-      if (!a.flags[x]) h2_death(a, h2_pair_key(a, t, tail, x));
+      if (!a.flags[x]) { h2_death(a, h2_pair_key(a, t, tail, x)); pushed = true; }
     }
   }
 }
@@ -895,7 +896,7 @@ __device__ void h2_apply(const H2Args& a, const H2Tok& t, u32 nocc, u64 win, u32
 }
 
 // ---- P5: the pairs the merges create, marks removed, step committed -------------------------------------------------
-__device__ void h2_births_end(const H2Args& a, const H2Tok& t, u32 nocc, u64 win, u32 new_tid, u32 thr, u32 step, u32 ev0) {
+__device__ void h2_births_end(const H2Args& a, const H2Tok& t, u32 nocc, u64 win, u32 new_tid, u32 thr, u32 step, u32 ev0, bool& pushed) {
   u32* hs = a.hs;
   for (u32 i = blockIdx.x * H2_THREADS + threadIdx.x; i < nocc; i += gridDim.x * H2_THREADS) {
     const u32 j = a.occ_j[i];
@@ -906,10 +907,11 @@ __device__ void h2_births_end(const H2Args& a, const H2Tok& t, u32 nocc, u64 win
     if (!(gj & GB_LAST_FLAG)) {                // (new token, right neighbour)
       const u32 x = j + 1u + (l >> 16);
       h2_birth(a, h2_pair_key(a, t, j, x), j, a.rbase + t.pos[j], (l & 0xFFFFu) + (t.ls[x] & 0xFFFFu), thr);
+      pushed = true;
     }
     const u32 q = h2_prev_live(t, j);          // (left neighbour, new token); a freshly merged left neighbour has counted
     if (q != 0xFFFFFFFFu && !(t.glue[q] & GB_LAST_FLAG) && t.tid[q] != new_tid)       // this pair as its own right pair
-      h2_birth(a, h2_pair_key(a, t, q, j), q, a.rbase + t.pos[q], (t.ls[q] & 0xFFFFu) + (l & 0xFFFFu), thr);
+{ h2_birth(a, h2_pair_key(a, t, q, j), q, a.rbase + t.pos[q], (t.ls[q] & 0xFFFFu) + (l & 0xFFFFu), thr); pushed = true; }
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     const u32 nk = hs[H2_NEWT], cnt = hs[H2_WIN_CNT];
@@ -1001,8 +1003,8 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
       nocc = 0;
     }
     h2_trace(hs, (loops << 8) | 3u);
-    h2_deaths(a, t, nocc, ref_r0, nres);
-    if (dist && (threadIdx.x & 31) == 0) __threadfence_system();     // (lane 0 pushed this warp's keys into the peers' blocks)
+    bool pushed = false;
+    h2_deaths(a, t, nocc, ref_r0, nres, pushed);
     if (t0) a.hs64[H2_TW_P3] += h2_now() - tm;
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P3] += n - tm; tm = n; }
@@ -1020,8 +1022,8 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P4] += n - tm; tm = n; }
     h2_trace(hs, (loops << 8) | 5u);
-    h2_births_end(a, t, nocc, win, new_tid, thr, step, ev0);
-    if (dist) __threadfence_system();
+    h2_births_end(a, t, nocc, win, new_tid, thr, step, ev0, pushed);
+    if (dist && pushed) __threadfence_system();              // this thread's pushes (P3 and P5) have landed in the peers' blocks before the signal
     if (t0) a.hs64[H2_TW_P5] += h2_now() - tm;
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P5] += n - tm; tm = n; hs[H2_ST_LOOPS] += 1u; }
@@ -1044,7 +1046,7 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
       grid.sync();
       // the other ranks' lists must have LANDED completely before they are replayed: compare the checksum of what is visible here
       // with the sum the writers announce; re-read until they agree (bounded)
-      bool landed = false;
+      bool landed = !a.verify_inbox;
       for (int attempt = 0; attempt < 2000 && !landed; ++attempt) {
         if (t0) a.hs64[H2_CK_ACC] = 0ull;
         grid.sync();
@@ -1083,7 +1085,7 @@ enum { HB_HS = 0, HB_HS64, HB_HSH0, HB_HSH1, HB_GLUE0, HB_GLUE1, HB_POS0, HB_POS
        HB_FLAGS, HB_RMARK, HB_SCRATCH, HB_POWTAB, HB_P, HB_RBINS, HB_R, HB_SLOTS, HB_LOG2NS, HB_BMAX, HB_CAND, HB_CAP, HB_CBIT,
        HB_TK, HB_TC, HB_TR0, HB_TNRES, HB_TLIST, HB_M, HB_CLKEY, HB_CLJ, HB_OCCJ, HB_OCCR, HB_STRBUF, HB_STRIDE, HB_ERANK, HB_EVL, HB_EVR, HB_EVP,
        HB_LKEY, HB_LCNT, HB_LR0, HB_LNRES, HB_LEVS, HB_LNK, HB_THRNUM, HB_STREAMING, HB_CTAS,
-       HB_RBASE, HB_WORLD, HB_RANK, HB_PEERS /* host table u64 [3][world]: delta / export / flag block of every rank */, HB_DCAP, HB_XCAP, HB_TIMEOUT_MS, HB_N };
+       HB_RBASE, HB_WORLD, HB_RANK, HB_PEERS /* host table u64 [3][world]: delta / export / flag block of every rank */, HB_DCAP, HB_XCAP, HB_TIMEOUT_MS, HB_VERIFY, HB_N };
 
 __global__ void h2_set_target(u32* hs, u32 nsteps) { hs[H2_TARGET] = hs[H2_STEP] + nsteps; }
 
@@ -1117,6 +1119,7 @@ extern "C" int gb_h_loop2(const int64_t* b, int n_args, int nsteps, int final_co
   a.max_loops = (u32)(4 * nsteps + 64);
   a.rbase = (u32)b[HB_RBASE]; a.world = b[HB_WORLD] > 1 ? (int)b[HB_WORLD] : 1; a.rank = (int)b[HB_RANK];
   a.dcap = (u32)b[HB_DCAP]; a.xcap = (u32)b[HB_XCAP];
+  a.verify_inbox = b[HB_VERIFY] != 0;
   a.timeout_ns = b[HB_TIMEOUT_MS] > 0 ? (u64)b[HB_TIMEOUT_MS] * 1000000ull : H2_TIMEOUT_NS;
   for (int r = 0; r < H2_MAXW; ++r) a.peer_d[r] = a.peer_x[r] = a.peer_f[r] = 0;
   if (a.world > 1) {

@@ -1319,7 +1319,7 @@ class Learner:
                 hl.thr_num, 1 if 16 * ts.cap > SlotSketch.STREAM_BYTES else 0, hl.ctas,
                 hl.rbase, self.comm.world if self.comm is not None else 1, self.comm.rank if self.comm is not None else 0,
                 C.addressof(hl.peer.table) if hl.peer is not None else 0, hl.dcap, hl.xcap,
-                int(os.environ.get("GEOBPE_PEER_TIMEOUT_MS", 20000))]
+                int(os.environ.get("GEOBPE_PEER_TIMEOUT_MS", 20000)), int(os.environ.get("GEOBPE_H2_VERIFY_INBOX", 0))]
         assert len(vals) == hl.nargs, (len(vals), hl.nargs)
         return (C.c_int64 * len(vals))(*[v if v < (1 << 63) else v - (1 << 64) for v in vals])
 

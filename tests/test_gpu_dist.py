@@ -20,6 +20,8 @@ def worker(rank, world, port, q, mode, uneven=False):
     os.environ["GEOBPE_PEER"] = "1" if mode == "peer" else "0"
     os.environ["GEOBPE_LOOP"] = "2" if mode == "loop2" else "1"
     os.environ.setdefault("GEOBPE_PEER_TIMEOUT_MS", "8000")
+    if uneven:
+        os.environ["GEOBPE_H2_VERIFY_INBOX"] = "1"      # (one variant also runs the inbox checksum verification)
     for p in (os.path.join(ROOT, "pt-bpe_b200"),):
         sys.path.insert(0, p)
     import torch.distributed as dist
