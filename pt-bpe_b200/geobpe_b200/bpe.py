@@ -88,8 +88,11 @@ class Tokenizer:
                 raise RuntimeError("Tokenizer is not attached to an initialised BPE")
             df = self._structure["angles"]             # stand-alone: the structure's own DataFrame (tokenizer.py:24-31)
             cur = {c: [float(x) for x in df[c]] for c in E.COLUMNS}
-            self._mat = {"bond_to_token": None, "cur": cur, "orig": {c: list(v) for c, v in cur.items()},
-                         "init": [E.INIT_N_CA, E.INIT_CA_C, E.INIT_TAU]}
+            st = {"bond_to_token": None, "cur": cur, "orig": {c: list(v) for c, v in cur.items()},
+                  "init": [E.INIT_N_CA, E.INIT_CA_C, E.INIT_TAU]}
+            if b is not None:                           # owned by a BPE that is not initialised yet (encode.py:308 reads the
+                return st                               # reference coordinates first): nothing to keep
+            self._mat = st
             self._local = True
             return self._mat
         key = (id(b._learner), b._learner.n_steps, len(b._learner.pop_log))
@@ -112,7 +115,8 @@ class Tokenizer:
         if "orig" in st:
             return st["orig"]
         b = self._bpe
-        a, e = int(b._offsets[self._i]), int(b._offsets[self._i + 1])
+        offs = b._learner.bb.offsets_host if getattr(b, "_learner", None) is not None else b._offsets
+        a, e = int(offs[self._i]), int(offs[self._i + 1])
         return {c: [float(x) for x in b._vals[E.COL[c], a:e]] for c in E.COLUMNS}
 
     @property

@@ -1465,6 +1465,7 @@ class Learner:
         order = torch.argsort((seg << 32) | el)
         self._evl[e0:e1] = self._evl[e0:e1][order]
         self._evr[e0:e1] = self._evr[e0:e1][order]
+        self._evp[e0:e1] = self._evp[e0:e1][order]
 
     def rehash(self, base=None):
         """give every live token its content hash under another base (two different windows shared a 64-bit hash: the
@@ -2127,7 +2128,7 @@ class Inducer(Learner):
                 plan.append(None)            # a constituent motif never occurred -> key not in geo_dict
                 continue
             length = nb(gl) + nb(gr)
-            plan.append((pack_m_key(cL, glue, cR), geos, p2cls, tid_of[(n, 0)], (length + 1) // 3, length + 1))
+            plan.append((pack_m_key(cL, glue, cR), geos, p2cls, tid_of[(n, 0)], (length + 1) // 3, length + 1, n))
         amax = int(_lib.load().gb_induce_max_atoms())
         if os.environ.get("GEOBPE_INDUCE_HOST") == "1" or any(pl is not None and pl[5] > amax for pl in plan):
             self._replay_host(merges, plan)
@@ -2204,6 +2205,8 @@ class Inducer(Learner):
                 self.replay.append((at, 0))
                 continue
             self.replay.append((int(start[k]), int(cnt[k])))
+            if cnt[k]:
+                self._step_events.append((pl[6], int(start[k]), int(cnt[k]), pl[0]))
             at = int(start[k]) + int(cnt[k])
             k += 1
         self.n_steps = int((cnt > 0).sum())
@@ -2217,7 +2220,7 @@ class Inducer(Learner):
             self.replay.append((self.ev_n, 0))
             if pl is None:
                 continue
-            key, geos, p2cls_l, tid0, nres, A = pl
+            key, geos, p2cls_l, tid0, nres, A, _n = pl
             p2cls = torch.tensor(p2cls_l, dtype=torch.int32, device=_dev())
             _lib.call("gb_flag_pairs_m", ts.p("cls"), ts.p("glue"), ts.T, key, _lib.ptr(ts.flags))
             N = ts.select(1, ts.idx)
