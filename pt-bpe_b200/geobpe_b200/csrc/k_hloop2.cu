@@ -227,7 +227,7 @@ __device__ __forceinline__ void h2_death(const H2Args& a, u64 key) {
     const u32 g = atomicAdd(&a.hs[H2_NDEATH], 1u), par = a.hs[H2_DSEQ] & 1u;
     if (g < a.dcap) { for (int q = 0; q < a.world; ++q) h2d_at(a.peer_d[q], a.dcap, par, a.world, a.rank).dkey[g] = key; }
     else a.hs[H2_HALT_REQ] = H2_HALT_TABLE;
-    atomicAdd(&a.hs64[H2_CK_OUT], key);
+    if (a.verify_inbox) atomicAdd(&a.hs64[H2_CK_OUT], key);
   }
   if (h2_cbit(a.cbit, s)) {
     const i64 t = h2_table_find(a, key);
@@ -248,7 +248,7 @@ __device__ __forceinline__ void h2_birth(const H2Args& a, u64 key, u32 left, u32
         d.bkey[g] = key; d.br0[g] = r0; d.bnres[g] = nres;
       }
     } else a.hs[H2_HALT_REQ] = H2_HALT_TABLE;
-    atomicAdd(&a.hs64[H2_CK_OUT], 3ull * key + r0);
+    if (a.verify_inbox) atomicAdd(&a.hs64[H2_CK_OUT], 3ull * key + r0);
   }
   if (h2_cbit(a.cbit, s)) {
     if (h2_table_add(a, key, r0, nres) < 0) { if (dist) a.hs[H2_HALT_REQ] = H2_HALT_TABLE; else a.hs[H2_PERIOD_OK] = 0u; }

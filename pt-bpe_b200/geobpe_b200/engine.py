@@ -503,9 +503,10 @@ class Learner:
         for cnt, r0, nres, *glob in raw:
             dicts = self._h_key_dicts(r0.tolist(), nres.tolist(), glob=bool(glob and glob[0])) if nres is not None else None
             for s in range(len(cnt)):
-                if dicts is not None:                  # (same dict json.loads(key_str) would build: keys in sorted order)
-                    key_str = json.dumps(dicts[s], sort_keys=True)
-                    self._tokens[len(self._tokens)] = {k: dicts[s][k] for k in sorted(dicts[s])}
+                if dicts is not None:                  # (same string / dict as json.dumps(d, sort_keys=True) and its json.loads:
+                    items = sorted(dicts[s].items())   #  the values are lists of python ints, which str() prints like json)
+                    key_str = "{" + ", ".join(f'"{k}": {v}' for k, v in items) + "}"
+                    self._tokens[len(self._tokens)] = dict(items)
                 else:
                     key_str = r0[s]
                     self._tokens[len(self._tokens)] = json.loads(key_str)
