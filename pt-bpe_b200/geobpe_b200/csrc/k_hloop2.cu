@@ -146,7 +146,7 @@ __device__ __forceinline__ void h2_halt(u32* hs, u32 code) {
 }
 // progress marker of block 0 (readable from a second stream while the kernel runs: multi-GPU bring-up)
 __device__ __forceinline__ void h2_trace(u32* hs, u32 v) {
-  if (blockIdx.x == 0 && threadIdx.x == 0) { *reinterpret_cast<volatile u32*>(hs + H2_TRACE) = v; __threadfence_system(); }
+  if (blockIdx.x == 0 && threadIdx.x == 0) *reinterpret_cast<volatile u32*>(hs + H2_TRACE) = v;      // (no fence: a marker, not a signal)
 }
 __device__ __forceinline__ bool h2_cbit(const u32* cbit, u32 s) { return (cbit[s >> 5] >> (s & 31u)) & 1u; }
 
@@ -264,23 +264,23 @@ __device__ __forceinline__ void h2_birth(const H2Args& a, u64 key, u32 left, u32
 // ---- sharded run: signal / wait, the per-iteration delta exchange, the per-period table exchange --------------------------
 // stage 0 = deltas, 1 = exports; seq = this use's sequence number (its low bit selects the buffer parity)
 __device__ void h2_signal_wait(const H2Args& a, int stage, u32 seq) {
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    __threadfence_system();
-    for (int q = 0; q < a.world; ++q)
-      h2p_st_release(reinterpret_cast<u32*>(a.peer_f[q]) + stage * H2_MAXW + a.rank, seq);
-    __threadfence_system();
-    const u32* mine = reinterpret_cast<const u32*>(a.peer_f[a.rank]) + stage * H2_MAXW;
-    const u64 t0 = h2_now();
-    bool ok = a.hs[H2_HALT] != H2_HALT_PEER;
-    for (int q = 0; q < a.world && ok; ++q)
-      while ((int)(h2p_ld_acquire(mine + q) - seq) < 0)
-        if (h2_now() - t0 > a.timeout_ns) {
-          a.hs[H2_WAIT_STAGE] = (u32)stage; a.hs[H2_WAIT_SEQ] = seq;              // what this rank was waiting for, what it saw
-          a.hs[H2_WAIT_SEEN0] = h2p_ld_acquire(mine + 0); a.hs[H2_WAIT_SEEN1] = h2p_ld_acquire(mine + 1);
-          h2_halt(a.hs, H2_HALT_PEER); ok = false; break;
-        }
-    a.hs[H2_ST_WAIT_US] += (u32)((h2_now() - t0) / 1000ull);
-  }
+  if (blockIdx.x != 0 || threadIdx.x >= 32) return;
+  const int q = (int)threadIdx.x;              // lane q signals rank q and waits for rank q: the NVLink round trips overlap
+  __threadfence_system();                       // (this lane's header stores to rank q precede its signal)
+  if (q < a.world) h2p_st_release(reinterpret_cast<u32*>(a.peer_f[q]) + stage * H2_MAXW + a.rank, seq);
+  __threadfence_system();
+  const u32* mine = reinterpret_cast<const u32*>(a.peer_f[a.rank]) + stage * H2_MAXW;
+  const u64 t0 = h2_now();
+  if (q < a.world && a.hs[H2_HALT] != H2_HALT_PEER)
+    while ((int)(h2p_ld_acquire(mine + q) - seq) < 0)
+      if (h2_now() - t0 > a.timeout_ns) {
+        a.hs[H2_WAIT_STAGE] = (u32)stage; a.hs[H2_WAIT_SEQ] = seq;              // what this rank was waiting for, what it saw
+        a.hs[H2_WAIT_SEEN0] = h2p_ld_acquire(mine + 0); a.hs[H2_WAIT_SEEN1] = h2p_ld_acquire(mine + 1);
+        h2_halt(a.hs, H2_HALT_PEER);
+        break;
+      }
+  __syncwarp();
+  if (q == 0) a.hs[H2_ST_WAIT_US] += (u32)((h2_now() - t0) / 1000ull);
 }
 // checksum of what has LANDED in this rank's inbox (the other ranks' slots), to be compared with the sum the writers announce
 __device__ void h2_inbox_checksum(const H2Args& a, u32 par) {
@@ -307,25 +307,39 @@ __device__ void h2_inbox_checksum(const H2Args& a, u32 par) {
 // replay the other ranks' deltas of this iteration on the local copies; block 0 thread 0 folds the headers
 __device__ void h2_apply_remote(const H2Args& a, u32 par, u32 cnt) {
   u32* hs = a.hs;
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    u32 tot = 0, halt = 0, per = 0;
-    for (int r = 0; r < a.world; ++r) {
+  if (blockIdx.x == 0 && threadIdx.x < 32) {       // lane r folds rank r's header
+    const int r = (int)threadIdx.x;
+    u32 n = 0, h = 0, pr = 0, dv = 0;
+    if (r < a.world) {
       const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, par, a.world, r);
-      tot += h2p_ld32(d.hdr + 0);
-      const u32 h = h2p_ld32(d.hdr + 1);
-      if (!halt) halt = h;
-      per |= h2p_ld32(d.hdr + 2);
-      if (h2p_ld32(d.hdr + 7) != (cnt ^ (u32)*reinterpret_cast<volatile u64*>(&a.hs64[0])) && !halt) halt = H2_HALT_DIVERGED;
+      n = h2p_ld32(d.hdr + 0); h = h2p_ld32(d.hdr + 1); pr = h2p_ld32(d.hdr + 2);
+      dv = h2p_ld32(d.hdr + 7) != (cnt ^ (u32)*reinterpret_cast<volatile u64*>(&a.hs64[0]));
     }
-    if (halt) h2_halt(hs, halt);
-    else if (tot != cnt) h2_halt(hs, H2_HALT_COUNT);
-    if (per) hs[H2_PERIOD_OK] = 0u;
+    for (int o = 16; o; o >>= 1) { n += __shfl_xor_sync(0xffffffffu, n, o); pr |= __shfl_xor_sync(0xffffffffu, pr, o); dv |= __shfl_xor_sync(0xffffffffu, dv, o); }
+    const unsigned hb = __ballot_sync(0xffffffffu, h != 0);
+    const u32 halt = hb ? __shfl_sync(0xffffffffu, h, __ffs(hb) - 1) : 0u;      // the lowest rank's request: the same on every rank
+    if (r == 0) {
+      if (halt) h2_halt(hs, halt);
+      else if (dv) h2_halt(hs, H2_HALT_DIVERGED);
+      else if (n != cnt) h2_halt(hs, H2_HALT_COUNT);
+      if (pr) hs[H2_PERIOD_OK] = 0u;
+    }
   }
   const i64 gtid = (i64)blockIdx.x * H2_THREADS + threadIdx.x, gsz = (i64)gridDim.x * H2_THREADS;
-  for (int r = 0; r < a.world; ++r) {
-    if (r == a.rank) continue;
+  u32 nds[H2_MAXW], nbs[H2_MAXW];
+#pragma unroll
+  for (int r = 0; r < H2_MAXW; ++r) {              // all counts first: the loads overlap instead of gating each rank's loop
+    nds[r] = nbs[r] = 0;
+    if (r < a.world && r != a.rank) {
+      const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, par, a.world, r);
+      nds[r] = h2p_ld32(d.hdr + 3); nbs[r] = h2p_ld32(d.hdr + 4);
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < H2_MAXW; ++r) {
+    if (r >= a.world || r == a.rank) continue;
     const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, par, a.world, r);
-    const u32 nd = min(h2p_ld32(d.hdr + 3), a.dcap), nb = min(h2p_ld32(d.hdr + 4), a.dcap);
+    const u32 nd = min(nds[r], a.dcap), nb = min(nbs[r], a.dcap);
     for (i64 i = gtid; i < nd; i += gsz) {
       const u64 key = h2p_ld64(d.dkey + i);
       const u32 s = gb_slot_of(key, 64 - a.log2ns);
@@ -348,9 +362,15 @@ __device__ void h2_apply_remote(const H2Args& a, u32 par, u32 cnt) {
 __device__ void h2_cross_check(const H2Args& a, u32 par, u32 thr) {
   if (blockIdx.x == 0 || gridDim.x < 2) return;
   const i64 gtid = (i64)(blockIdx.x - 1) * H2_THREADS + threadIdx.x, gsz = (i64)(gridDim.x - 1) * H2_THREADS;
-  for (int r = 0; r < a.world; ++r) {
+  u32 nbs[H2_MAXW];
+#pragma unroll
+  for (int r = 0; r < H2_MAXW; ++r)
+    nbs[r] = r < a.world ? h2p_ld32(h2d_at(a.peer_d[a.rank], a.dcap, par, a.world, r).hdr + 4) : 0u;
+#pragma unroll
+  for (int r = 0; r < H2_MAXW; ++r) {
+    if (r >= a.world) continue;
     const H2D d = h2d_at(a.peer_d[a.rank], a.dcap, par, a.world, r);
-    const u32 nb = min(h2p_ld32(d.hdr + 4), a.dcap);
+    const u32 nb = min(nbs[r], a.dcap);
     for (i64 i = gtid; i < nb; i += gsz) {
       const u32 s = gb_slot_of(h2p_ld64(d.bkey + i), 64 - a.log2ns);
       if (!h2_cbit(a.cbit, s) && a.slots[s] >= thr) a.hs[H2_XCROSS] = 1u;
@@ -1030,15 +1050,17 @@ __global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_comp
     if (dist) {
       // publish this rank's deltas (header last), wait for every rank's, replay the others' on the local copies
       const u32 seq = dseq0 + 1u;
-      if (t0) {
-        for (int q = 0; q < a.world; ++q) {
+      if (blockIdx.x == 0 && threadIdx.x < 32) {     // lane q writes this rank's header into rank q's block
+        const int q = (int)threadIdx.x;
+        const u64 ck = a.hs64[H2_CK_OUT];
+        if (q < a.world) {
           const H2D d = h2d_at(a.peer_d[q], a.dcap, seq & 1u, a.world, a.rank);
           d.hdr[0] = hs[H2_NOCC]; d.hdr[1] = hs[H2_HALT_REQ] ? hs[H2_HALT_REQ] : (bad3 ? bad3 : 0u); d.hdr[2] = hs[H2_PERIOD_REQ];
           d.hdr[3] = hs[H2_NDEATH]; d.hdr[4] = hs[H2_NBIRTH];
-          const u64 ck = a.hs64[H2_CK_OUT];
           d.hdr[5] = (u32)ck; d.hdr[6] = (u32)(ck >> 32); d.hdr[7] = cnt ^ (u32)win;
         }
-        a.hs64[H2_CK_OUT] = 0ull;
+        __syncwarp();
+        if (q == 0) a.hs64[H2_CK_OUT] = 0ull;
       }
       h2_trace(hs, (loops << 8) | 6u);
       h2_signal_wait(a, 0, seq);
