@@ -531,7 +531,7 @@ def main():
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s"
     tr = {}
-    tp = os.path.join(ROOT, "profiles", "r1_k1_traffic.json")
+    tp = os.path.join(ROOT, "profiles", "r2_k1_traffic.json")
     if os.path.exists(tp) and args.mode == "H":      # dram__bytes_read + write per launch from the committed ncu --set full capture
         tr = json.load(open(tp))
     roof = None
