@@ -32,7 +32,6 @@ extern "C" {
 #define GB_EMPTY_KEY 0xFFFFFFFFFFFFFFFFull
 #define GB_LAST_FLAG 0x80000000u
 #define GB_NOBIN 0x3FFu
-#define GB_P61 0x1FFFFFFFFFFFFFFFull
 
 const char* gb_last_error(void);
 int gb_abi_version(void);
@@ -82,7 +81,7 @@ int gb_table_clear(uint64_t* tkeys, uint32_t* tcnt, uint32_t* tmin, int64_t M, v
 /* medoid mode: key = cls[j]<<45 | cls[j+1]<<27 | glue27(j).  overflow (device i32) set if the table is full */
 int gb_pair_count_m(const uint32_t* cls, const uint32_t* glue, int64_t T, uint64_t* tkeys,
                     uint32_t* tcnt, uint32_t* tmin, int64_t M, int32_t* overflow, void* stream);
-/* histogram mode: key = polynomial hash (mod 2^61-1, base P) of the concatenated window content
+/* histogram mode: key = polynomial hash over Z/2^64 (odd base P, natural wrap-around) of the concatenated window content
  * hsh[j] . gluesym(j) . hsh[j+1]; powtab u64 [>= 2*maxlen] holds P^m */
 int gb_pair_count_h(const uint64_t* hsh, const uint32_t* glue, const uint32_t* len, int64_t T,
                     const uint64_t* powtab, uint64_t P, uint64_t* tkeys, uint32_t* tcnt,

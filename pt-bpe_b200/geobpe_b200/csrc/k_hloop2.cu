@@ -838,8 +838,9 @@ __device__ void h2_flag(const H2Args& a, const H2Tok& t, u64 win) {
   u32* hs = a.hs;
   const u32 ncl = min(h2_ld(hs + H2_NCL), h2_ld(hs + H2_CLCAP));
   for (u32 i = blockIdx.x * H2_THREADS + threadIdx.x; i < ncl; i += gridDim.x * H2_THREADS) {
-    if (a.cl_key[i] != win) continue;
-    const u32 j = a.cl_j[i];
+    const u64 k = a.cl_key[i];
+    const u32 j = a.cl_j[i];                     // (loaded with the key, not after the compare: one round trip less for a match)
+    if (k != win) continue;
     const u32 l = t.ls[j];
     const u32 gj = t.glue[j];
     if (l == 0u || (gj & GB_LAST_FLAG)) continue;           // the entry is stale when the pair no longer exists
@@ -951,7 +952,7 @@ __device__ void h2_births_end(const H2Args& a, const H2Tok& t, u32 nocc, u64 win
 
 // ---- the loop --------------------------------------------------------------------------------------------------------
 template <bool CS>
-__global__ void __launch_bounds__(H2_THREADS, 2) h2_run(H2Args a, int final_compact) {
+__global__ void __launch_bounds__(H2_THREADS, 1) h2_run(H2Args a, int final_compact) {
   cg::grid_group grid = cg::this_grid();
   __shared__ __align__(16) unsigned char smem[sizeof(u32) * KC_SET + sizeof(u64) * H2_BLK_LIST + sizeof(u32) * H2_BLK_LIST + 64];
   u32* hs = a.hs;

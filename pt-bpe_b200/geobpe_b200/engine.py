@@ -510,7 +510,16 @@ class Learner:
                 else:
                     key_str = r0[s]
                     self._tokens[len(self._tokens)] = json.loads(key_str)
+                self._check_not_popped(key_str)
                 self._pop_log.append((int(cnt[s]), key_str))
+
+    def _check_not_popped(self, key_str):
+        """histogram mode: [A][BC] and [AB][C] share a key, so a popped key could become the argmax again; the reference stops
+        there (`if key in self._tokens.values(): breakpoint()`, bpe.py:1808) -- here it raises"""
+        seen = self.__dict__.setdefault("_popped", set())
+        if key_str in seen:
+            raise RuntimeError("a key that already owns a token became the most frequent pair again (bpe.py:1808 invariant)")
+        seen.add(key_str)
 
     @property
     def step_events(self):
@@ -763,6 +772,7 @@ class Learner:
         cands = [(json.dumps(d, sort_keys=True), t[0], r0, nr) for t, d, r0, nr in zip(ties, dicts, p0, nress)]
         key_str, key, r0, nres = min(cands)            # SortedDict order: (-count, key string)
         n = len(self.tokens)
+        self._check_not_popped(key_str)
         self.tokens[n] = json.loads(key_str)
         self.pop_log.append((mx, key_str))
         self._ntok, self._last_count = n + 1, mx
@@ -926,6 +936,7 @@ class Learner:
             return
         torch.cuda.synchronize()
         d.graphs = {}
+        _lib.load().gb_h_loop_incremental(1)         # (also forgets the C-side period graphs captured for this learner's buffers)
         if d.peer is None:
             return
         torch.cuda.synchronize()
@@ -1810,6 +1821,7 @@ class Learner:
         self._step_events = list(st["step_events"])
         self._pop_log = list(st["pop_log"])
         self._tokens = st["tokens"]
+        self._popped = {k for _, k in self._pop_log} if self.mode == "H" else set()
         self.n_steps = int(st["n_steps"])
         if self.mode == "H":
             _lib.call("gb_rehash_tokens", _lib.ptr(self.sym), _lib.ptr(self.glue_res), ts.p("pos"), ts.p("len"), T, self.hash_base, ts.p("hsh"))
@@ -2085,7 +2097,9 @@ class Inducer(Learner):
         is_last = torch.zeros(R, dtype=torch.bool, device=_dev())
         is_last[(self.bb.offsets[1:] - 1)] = True
         lists = {3: torch.nonzero(~is_last).flatten().to(torch.int32), 2: torch.nonzero(is_last).flatten().to(torch.int32)}
-        order = [3, 2] if self.bb.lens_host[0] > 1 else [2, 3]
+        # which of the (0, p) / (1, p) groups holds the inner-residue medoids is a property of the VOCABULARY (a 3-bond residue token
+        # carries psi / 0C:1N, the 2-bond last-residue token does not), not of the first held-out backbone's length
+        order = [3, 2] if "psi" in tokens[(0, 0)] else [2, 3]
         cls_res = _zeros(R, torch.int32); tid_res = _zeros(R, torch.int32)
         for n, size in enumerate(order):
             occ = lists[size].contiguous()
