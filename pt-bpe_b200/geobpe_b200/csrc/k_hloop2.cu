@@ -834,21 +834,51 @@ __device__ void h2_decide(const H2Args& a, unsigned char* smem) {
 }
 
 // ---- P2: the winner's occurrences from the pair list --------------------------------------------------------------
-__device__ void h2_flag(const H2Args& a, const H2Tok& t, u64 win) {
+#define H2_FLAG_ENT 4           // list entries per thread and round: their loads are issued together (one chain of round trips)
+__device__ void h2_flag(const H2Args& a, const H2Tok& t, u64 win, u32* s_u32) {
   u32* hs = a.hs;
   const u32 ncl = min(h2_ld(hs + H2_NCL), h2_ld(hs + H2_CLCAP));
-  for (u32 i = blockIdx.x * H2_THREADS + threadIdx.x; i < ncl; i += gridDim.x * H2_THREADS) {
-    const u64 k = a.cl_key[i];
-    const u32 j = a.cl_j[i];                     // (loaded with the key, not after the compare: one round trip less for a match)
-    if (k != win) continue;
-    const u32 l = t.ls[j];
-    const u32 gj = t.glue[j];
-    if (l == 0u || (gj & GB_LAST_FLAG)) continue;           // the entry is stale when the pair no longer exists
-    const u32 r = j + 1u + (l >> 16);
-    if (gb_key_h(t.hsh[j], gj, t.hsh[r], a.P, __ldg(a.powtab + (2u * (t.ls[r] & 0xFFFFu) - 1u))) != win) continue;
-    const u32 q = atomicAdd(&hs[H2_NOCC], 1u);
-    a.occ_j[q] = j; a.occ_r[q] = r;
-    a.flags[j] = 1; a.rmark[r] = 1;
+  // (block-uniform trip count: the occurrence slots are reserved once per CTA and round -- a single hot counter bumped by
+  //  every matching thread costs a serialised L2 atomic per warp)
+  for (u32 base = blockIdx.x * (H2_THREADS * H2_FLAG_ENT); base < ncl; base += gridDim.x * (H2_THREADS * H2_FLAG_ENT)) {
+    u64 k[H2_FLAG_ENT];
+    u32 j[H2_FLAG_ENT], r[H2_FLAG_ENT], l[H2_FLAG_ENT], g[H2_FLAG_ENT];
+    bool valid[H2_FLAG_ENT];
+#pragma unroll
+    for (int e = 0; e < H2_FLAG_ENT; ++e) {
+      const u32 i = base + e * H2_THREADS + threadIdx.x;
+      k[e] = i < ncl ? a.cl_key[i] : ~win;
+      j[e] = i < ncl ? a.cl_j[i] : 0u;         // (loaded with the key, not after the compare: one round trip less for a match)
+    }
+#pragma unroll
+    for (int e = 0; e < H2_FLAG_ENT; ++e) {
+      valid[e] = k[e] == win;
+      l[e] = valid[e] ? t.ls[j[e]] : 0u;
+      g[e] = valid[e] ? t.glue[j[e]] : GB_LAST_FLAG;
+    }
+    u32 nv = 0;
+#pragma unroll
+    for (int e = 0; e < H2_FLAG_ENT; ++e) {
+      valid[e] = valid[e] && l[e] != 0u && !(g[e] & GB_LAST_FLAG);      // the entry is stale when the pair no longer exists
+      r[e] = j[e] + 1u + (l[e] >> 16);
+      if (valid[e])
+        valid[e] = gb_key_h(t.hsh[j[e]], g[e], t.hsh[r[e]], a.P, __ldg(a.powtab + (2u * (t.ls[r[e]] & 0xFFFFu) - 1u))) == win;
+      nv += valid[e];
+    }
+    if (threadIdx.x == 0) s_u32[0] = 0;
+    __syncthreads();
+    u32 my = nv ? atomicAdd(&s_u32[0], nv) : 0u;
+    __syncthreads();
+    if (threadIdx.x == 0 && s_u32[0]) s_u32[1] = atomicAdd(&hs[H2_NOCC], s_u32[0]);
+    __syncthreads();
+#pragma unroll
+    for (int e = 0; e < H2_FLAG_ENT; ++e)
+      if (valid[e]) {
+        const u32 q = s_u32[1] + my++;
+        a.occ_j[q] = j[e]; a.occ_r[q] = r[e];
+        a.flags[j[e]] = 1; a.rmark[r[e]] = 1;
+      }
+    __syncthreads();
   }
 }
 __device__ void h2_unflag(const H2Args& a, u32 nocc) {
@@ -899,20 +929,31 @@ __device__ void h2_deaths(const H2Args& a, const H2Tok& t, u32 nocc, u32 ref_r0,
 }
 
 // ---- P4: merges in place ------------------------------------------------------------------------------------------------
-__device__ void h2_apply(const H2Args& a, const H2Tok& t, u32 nocc, u64 win, u32 new_tid, u32 ev0) {
-  for (u32 i = blockIdx.x * H2_THREADS + threadIdx.x; i < nocc; i += gridDim.x * H2_THREADS) {
-    const u32 j = a.occ_j[i];
-    if (a.flags[j] != 2) continue;
-    const u32 r = a.occ_r[i];
-    const u32 l = t.ls[j], lr = t.ls[r];
-    const u32 q = ev0 + atomicAdd(&a.hs[H2_NEWT], 1u);
-    a.ev_left[q] = t.pos[j]; a.ev_right[q] = t.pos[r]; a.ev_p[q] = 0u;
-    t.hsh[j] = win;
-    t.glue[j] = t.glue[r];
-    t.ls[j] = ((l & 0xFFFFu) + (lr & 0xFFFFu)) | (((l >> 16) + 1u + (lr >> 16)) << 16);
-    t.tid[j] = new_tid;
-    t.ls[r] = 0u;                              // dead until the next compaction; tid keeps the way back to the absorbing token
-    t.tid[r] = j;
+__device__ void h2_apply(const H2Args& a, const H2Tok& t, u32 nocc, u64 win, u32 new_tid, u32 ev0, u32* s_u32) {
+  for (u32 base = blockIdx.x * H2_THREADS; base < nocc; base += gridDim.x * H2_THREADS) {
+    const u32 i = base + threadIdx.x;
+    u32 j = 0;
+    bool kept = false;
+    if (i < nocc) { j = a.occ_j[i]; kept = a.flags[j] == 2; }
+    if (threadIdx.x == 0) s_u32[0] = 0;
+    __syncthreads();
+    const u32 my = kept ? atomicAdd(&s_u32[0], 1u) : 0u;        // event slots reserved once per CTA and round
+    __syncthreads();
+    if (threadIdx.x == 0 && s_u32[0]) s_u32[1] = atomicAdd(&a.hs[H2_NEWT], s_u32[0]);
+    __syncthreads();
+    if (kept) {
+      const u32 r = a.occ_r[i];
+      const u32 l = t.ls[j], lr = t.ls[r];
+      const u32 q = ev0 + s_u32[1] + my;
+      a.ev_left[q] = t.pos[j]; a.ev_right[q] = t.pos[r]; a.ev_p[q] = 0u;
+      t.hsh[j] = win;
+      t.glue[j] = t.glue[r];
+      t.ls[j] = ((l & 0xFFFFu) + (lr & 0xFFFFu)) | (((l >> 16) + 1u + (lr >> 16)) << 16);
+      t.tid[j] = new_tid;
+      t.ls[r] = 0u;                              // dead until the next compaction; tid keeps the way back to the absorbing token
+      t.tid[r] = j;
+    }
+    __syncthreads();
   }
 }
 
@@ -925,14 +966,17 @@ __device__ void h2_births_end(const H2Args& a, const H2Tok& t, u32 nocc, u64 win
     a.flags[j] = 0; a.rmark[a.occ_r[i]] = 0;
     if (f != 2) continue;
     const u32 l = t.ls[j], gj = t.glue[j];
-    if (!(gj & GB_LAST_FLAG)) {                // (new token, right neighbour)
-      const u32 x = j + 1u + (l >> 16);
-      h2_birth(a, h2_pair_key(a, t, j, x), j, a.rbase + t.pos[j], (l & 0xFFFFu) + (t.ls[x] & 0xFFFFu), thr);
-      pushed = true;
-    }
-    const u32 q = h2_prev_live(t, j);          // (left neighbour, new token); a freshly merged left neighbour has counted
-    if (q != 0xFFFFFFFFu && !(t.glue[q] & GB_LAST_FLAG) && t.tid[q] != new_tid)       // this pair as its own right pair
-{ h2_birth(a, h2_pair_key(a, t, q, j), q, a.rbase + t.pos[q], (t.ls[q] & 0xFFFFu) + (l & 0xFFFFu), thr); pushed = true; }
+    // both neighbours first (their loads overlap), then the two updates
+    const bool has_r = !(gj & GB_LAST_FLAG);          // (new token, right neighbour)
+    const u32 x = j + 1u + (l >> 16);
+    const u32 q = h2_prev_live(t, j);                   // (left neighbour, new token); a freshly merged left neighbour has counted
+    const bool has_l = q != 0xFFFFFFFFu && !(t.glue[q] & GB_LAST_FLAG) && t.tid[q] != new_tid;       // this pair as its own right pair
+    u64 kr = 0, kl = 0;
+    u32 nr = 0, nl = 0, pj = t.pos[j], pq = 0;
+    if (has_r) { kr = h2_pair_key(a, t, j, x); nr = (l & 0xFFFFu) + (t.ls[x] & 0xFFFFu); }
+    if (has_l) { kl = h2_pair_key(a, t, q, j); nl = (t.ls[q] & 0xFFFFu) + (l & 0xFFFFu); pq = t.pos[q]; }
+    if (has_r) { h2_birth(a, kr, j, a.rbase + pj, nr, thr); pushed = true; }
+    if (has_l) { h2_birth(a, kl, q, a.rbase + pq, nl, thr); pushed = true; }
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     const u32 nk = hs[H2_NEWT], cnt = hs[H2_WIN_CNT];
@@ -1002,7 +1046,7 @@ __global__ void __launch_bounds__(H2_THREADS, 1) h2_run(H2Args a, int final_comp
     const u32 ref_r0 = h2_ld(hs + H2_WIN_R0), nres = h2_ld(hs + H2_WIN_NRES), cnt = h2_ld(hs + H2_WIN_CNT);
     const u32 new_tid = h2_ld(hs + H2_NTOK), ev0 = h2_ld(hs + H2_EVN), thr = h2_ld(hs + H2_THR);
     h2_trace(hs, (loops << 8) | 2u);
-    h2_flag(a, t, win);
+    h2_flag(a, t, win, reinterpret_cast<u32*>(smem));
     if (t0) a.hs64[H2_TW_P2] += h2_now() - tm;
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P2] += n - tm; tm = n; }
@@ -1038,7 +1082,7 @@ __global__ void __launch_bounds__(H2_THREADS, 1) h2_run(H2Args a, int final_comp
       continue;
     }
     h2_trace(hs, (loops << 8) | 4u);
-    h2_apply(a, t, nocc, win, new_tid, ev0);
+    h2_apply(a, t, nocc, win, new_tid, ev0, reinterpret_cast<u32*>(smem));
     if (t0) a.hs64[H2_TW_P4] += h2_now() - tm;
     grid.sync();
     if (t0) { const u64 n = h2_now(); a.hs64[H2_TM_P4] += n - tm; tm = n; }
