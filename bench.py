@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--backbones", type=int, default=10000)
     ap.add_argument("--residues", type=int, default=256)
     ap.add_argument("--bins", type=int, default=None)
-    ap.add_argument("--reps", type=int, default=3, help="repetitions of the e2e / full_config legs (median reported)")
+    ap.add_argument("--reps", type=int, default=5, help="repetitions of the e2e / full_config legs (median reported)")
     ap.add_argument("--cpu-backbones", type=int, default=None,
                     help="backbones of the CPU sample (default: the whole workload for --impl reference, 320 for the cpu_baseline leg)")
     ap.add_argument("--induce-backbones", type=int, default=100000, help="held-out backbones x 512 residues (BASELINE configs[2])")
@@ -309,7 +309,7 @@ def induce_arm(args, rank, world, barrier):
            "vocabulary_merges": args.induce_merges, "vocabulary_tokens": len(tokens), "tokens_out_per_rank": int(ts.T),
            "rejected_backbones_rank0": int(ind.failed.sum()), "merges_fired_rank0": int(ind.n_steps),
            "h2d_bytes": int(hv.nbytes + ho.nbytes), "d2h_bytes": int(sum(o.numel() * o.element_size() for o in out)),
-           "vocabulary_learn_seconds": t_learn,
+           "vocabulary_learn_seconds": t_learn, "stages_s": getattr(ind, "stage_s", None),
            "note": "host arrays -> H2D -> K3 binning -> residue medoid assignment (K4/K5) -> merge replay (K2 + K4/K5 per vocabulary "
                    "merge) -> D2H of the segmentation; backbones whose glue angles leave the training range are rejected like the "
                    "reference's ValueError (bpe.py:1105-1108)"}
@@ -494,8 +494,10 @@ def main():
         if ms < 600:                                 # keep the GPU busy until nvidia-smi has sampled the clocks a few times
             t_end = time.time() + 0.9
             Lb = mk() if world == 1 else None
-            while Lb is not None and time.time() < t_end and Lb.n_steps < 1500:
-                for _ in range(64):
+            while Lb is not None and time.time() < t_end:
+                if Lb.n_steps >= 1500:
+                    Lb = mk()
+                for _ in range(100):
                     Lb.step()
                 Lb.sync()
             del Lb

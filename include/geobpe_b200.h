@@ -289,6 +289,17 @@ int gb_rehash_tokens(const uint64_t* sym, const uint32_t* glue_res, const uint32
 int gb_token_stream(const uint32_t* tid, const uint32_t* glue, const uint32_t* pos, const uint32_t* bb, int64_t T,
                     uint32_t V, uint32_t off_omega, uint32_t off_phi, uint32_t off_cn, int64_t* out, void* stream);
 
+/* ---- reconstruction metrics for every backbone (bin/encode.py:341-359 computes them per reference tokenizer through
+ *      Tokenizer.compute_coords + ProteinChain.rmsd): current value of every residue-major slot (bin centres centres f64
+ *      [9][cstride]; medoid mode: the live token's class geometry cg f64 [ncls][maxres][9], NaN = absent, glue at token ends from
+ *      the bins; cg == NULL in histogram mode), pristine values in the same layout, full-chain NeRF of both (coords f64
+ *      [3 R][3]) and the Kabsch backbone RMSD per backbone (rmsd f64 [S]).  tok_of u32 [R], slots_* f64 [9][R] are scratch. */
+int gb_reconstruction(const uint16_t* rbins, int64_t R, const double* centres, int cstride, const uint32_t* pos,
+                      const uint32_t* len, const uint32_t* cls, int64_t T, const double* cg, int maxres,
+                      const double* vals, int64_t ld, const uint32_t* bb, const int64_t* offsets, int64_t S,
+                      double i_nca, double i_cac, double i_tau, uint32_t* tok_of, double* slots_cur, double* slots_orig,
+                      double* coords_cur, double* coords_orig, double* rmsd, void* stream);
+
 /* ---- K7: induce merge replay on the device (bpe.py:1116-1139 BPE.tokenize's loop over the learned merges + step_helper
  *      1316-1425, for a whole batch of held-out backbones at once).  Token arrays are the medoid-mode SoA in the lazily
  *      compacted layout (ls = len | extra << 16, 0 = dead entry; dense on entry).  Merge m (host arrays, launch order =

@@ -663,6 +663,11 @@ class BPE(_View):
         first = np.searchsorted(self._token_arrays()[0], L.bb.offsets_host)
         return out, 4 * first.astype(np.int64) - 3 * np.arange(S + 1, dtype=np.int64)
 
+    def reconstruction_rmsd(self):
+        """backbone RMSD (Kabsch, N / CA / C atoms) of every backbone's current quantised geometry against its pristine
+        structure, one device pass -- what bin/encode.py:341-359 computes for its reference tokenizers one by one"""
+        return self._learner.reconstruction()[0].cpu().numpy()
+
     def codebook_utility(self):
         """get_codebook_utility (plotting.py:78-95) over the token streams of all backbones, computed on the device"""
         from foldingdiff.plotting import get_codebook_utility

@@ -2014,6 +2014,40 @@ class Learner:
                   _lib.ptr(r0), K, nres, A, _lib.ptr(f3c), _lib.ptr(f3t), 0.0, 0.0, 0.0, None, None, 0, _lib.ptr(out))
         return out.view(K, A * 3)
 
+    def reconstruction(self):
+        """f-4: full-chain coordinates of the CURRENT (quantised) geometry and of the pristine structure for every backbone, and
+        their Kabsch backbone RMSD -- (rmsd f64 [S], coords_cur f64 [3R, 3], coords_orig f64 [3R, 3]) device tensors
+        (csrc/k_recon.cu; the reference computes this per reference tokenizer, bin/encode.py:341-359)"""
+        ts, bb = self.ts, self.bb
+        R, S, T = bb.R, bb.S, ts.T
+        th = self.th.thresholds[self.size0]
+        B = max(len(v) for v in th.values())
+        cen = np.zeros((9, B))
+        for i, k in enumerate(SLOTS):
+            if k in th:
+                cen[i, :len(th[k])] = [(a + b) / 2 for a, b in th[k]]
+            elif k in BOND_TYPES:
+                cen[i, 0] = BOND_LENGTHS[BOND_TYPES.index(k)]          # std_bonds: bond bins are all 0
+        cen_d = torch.from_numpy(cen).to(_dev())
+        cg, maxres = None, 0
+        if self.mode == "M":
+            maxres = max((len(g["N:CA"]) for g in self.class_geo), default=1)
+            tab = np.full((len(self.class_geo), maxres, 9), np.nan)
+            for c, g in enumerate(self.class_geo):
+                for i, k in enumerate(SLOTS):
+                    v = g.get(k, [])
+                    tab[c, :len(v), i] = v
+            cg = torch.from_numpy(tab).to(_dev())
+        tok_of = _empty(R, torch.int32)
+        s_cur, s_org = _empty(9 * R, torch.float64), _empty(9 * R, torch.float64)
+        c_cur, c_org = _empty(9 * R, torch.float64), _empty(9 * R, torch.float64)
+        rmsd = _empty(S, torch.float64)
+        _lib.call_n("gb_reconstruction", 6, _lib.ptr(self.rbins), R, _lib.ptr(cen_d), B, ts.p("pos"), ts.p("len"), ts.p("cls"), T,
+                    _lib.ptr(cg) if cg is not None else None, maxres, _lib.ptr(bb.vals), R, _lib.ptr(bb.bb), _lib.ptr(bb.offsets), S,
+                    INIT_N_CA, INIT_CA_C, INIT_TAU, _lib.ptr(tok_of), _lib.ptr(s_cur), _lib.ptr(s_org), _lib.ptr(c_cur), _lib.ptr(c_org),
+                    _lib.ptr(rmsd))
+        return rmsd, c_cur.view(3 * R, 3), c_org.view(3 * R, 3)
+
     def step(self):
         if self.mode == "H":
             self.step_h()
@@ -2062,6 +2096,7 @@ class Inducer(Learner):
             raise NotImplementedError("induce is built for rmsd_super_res=True vocabularies")
         if not all(isinstance(k, tuple) for k in tokens):
             raise NotImplementedError("BPE.tokenize needs a medoid-mode vocabulary (bpe.py:1077,1117)")
+        t_stage = [time.perf_counter()]
         self.mode = "M"
         self.std_bonds = std_bonds
         self.size0 = 1
@@ -2145,10 +2180,13 @@ class Inducer(Learner):
             length = nb(gl) + nb(gr)
             plan.append((pack_m_key(cL, glue, cR), geos, p2cls, tid_of[(n, 0)], (length + 1) // 3, length + 1, n))
         amax = int(_lib.load().gb_induce_max_atoms())
+        torch.cuda.synchronize(); t_stage.append(time.perf_counter())
         if os.environ.get("GEOBPE_INDUCE_HOST") == "1" or any(pl is not None and pl[5] > amax for pl in plan):
             self._replay_host(merges, plan)
         else:
             self._replay_device(plan)
+        torch.cuda.synchronize(); t_stage.append(time.perf_counter())
+        self.stage_s = {"upload_quantise_residue_tokens_plan": t_stage[1] - t_stage[0], "merge_replay": t_stage[2] - t_stage[1]}
 
     def _replay_device(self, plan):
         """all vocabulary merges applied on the device without a host round trip (csrc/k_induce.cu)"""

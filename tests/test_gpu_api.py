@@ -236,3 +236,25 @@ def test_token_stream_export_equals_per_token_quantize(hp):
     u = bpe.codebook_utility()
     v = get_codebook_utility(torch.as_tensor(sum(want, [])), bpe.vocab_size)
     assert u.keys() == v.keys() and all(abs(u[k] - v[k]) < 1e-5 for k in u)
+
+
+@pytest.mark.parametrize("hp", [HP_H, HP_M], ids=["H", "M"])
+def test_reconstruction_metrics_for_all_backbones(hp):
+    """f-4: full-chain NeRF + Kabsch backbone RMSD of every backbone on the device against the per-tokenizer path (compute_coords
+    of the materialised tokenizer + the oracle's Kabsch RMSD); north_star tolerance 1e-4 A, asserted at 1e-7"""
+    from foldingdiff.tokenizer import Tokenizer
+    bpe, strucs = learn(hp, S=16, n=36, seed=71, steps=20)
+    rmsd, c_cur, c_org = bpe._learner.reconstruction()
+    rmsd, c_cur, c_org = rmsd.cpu().numpy(), c_cur.cpu().numpy(), c_org.cpu().numpy()
+    offs = bpe._offsets
+    assert rmsd.shape == (len(bpe.tokenizers),) and np.all(np.isfinite(rmsd)) and rmsd.max() > 0
+    for i in (0, 3, 9, 15):
+        t = bpe.tokenizers[i]
+        a, b = 3 * int(offs[i]), 3 * int(offs[i + 1])
+        cur = t.compute_coords()
+        org = Tokenizer(strucs[i]).compute_coords()       # the pristine structure (encode.py:308 takes ref_coords before initialize())
+        np.testing.assert_allclose(c_cur[a:b], cur, rtol=0, atol=1e-7)
+        np.testing.assert_allclose(c_org[a:b], org, rtol=0, atol=1e-7)
+        want = O.compute_rmsd(cur, org)
+        assert abs(rmsd[i] - want) < 1e-7
+    assert np.array_equal(bpe.reconstruction_rmsd(), rmsd)
