@@ -1,7 +1,8 @@
 // K7: device-resident merge replay of induce (BPE.tokenize, bpe.py:1116-1139 with step_helper 1316-1425): every vocabulary
 // merge of a medoid-mode vocabulary applied, in learned order, to ALL held-out backbones at once without a host round trip.
 // Per merge four launches on the lazily compacted token arrays (ls = len | extra << 16, 0 = dead; see k_hloop2.cu):
-//   flag     one streaming pass (cls, glue, ls: 12 B / entry): pairs whose packed key equals the merge's key -> occurrence list
+//   flag     one streaming pass (cls: 4 B / entry; glue, ls only where the left class matches): pairs whose packed key equals the
+//            merge's key -> occurrence list
 //   assign   per occurrence: NeRF coordinates of the window from the pristine internal coordinates (rmsd_super_res,
 //            tokenizer.py:347-363, nerf.py:84-210) and Kabsch RMSD to the key's medoids (algo.py:8-65); first minimum wins
 //            (np.argmin, bpe.py:655-657)
@@ -20,13 +21,15 @@ struct KITok { u32* cls; u32* glue; const u32* pos; u32* ls; u32* tid; };
 
 __global__ void __launch_bounds__(256) ki_flag(KITok t, i64 N, u64 key, u32* __restrict__ st, int par, u32* __restrict__ occ_j,
                                                u32* __restrict__ occ_r, u8* __restrict__ flags, u8* __restrict__ rmark) {
+  const u32 cL = (u32)(key >> 45) & 0x3FFFFu;
   for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < N; j += (i64)gridDim.x * blockDim.x) {
+    if (t.cls[j] != cL) continue;              // 4 B / entry for almost every entry (a dead entry keeps its class: ls decides below)
     const u32 l = t.ls[j];
     if (l == 0u) continue;
     const u32 g = t.glue[j];
     if (g & GB_LAST_FLAG) continue;
     const u32 r = (u32)j + 1u + (l >> 16);
-    if (gb_key_m(t.cls[j], g, t.cls[r]) != key) continue;
+    if (gb_key_m(cL, g, t.cls[r]) != key) continue;
     const u32 q = atomicAdd(&st[KI_NOCC0 + par], 1u);
     occ_j[q] = (u32)j; occ_r[q] = r;
     flags[j] = 1; rmark[r] = 1;
