@@ -19,67 +19,125 @@ enum { KI_NOCC0 = 0, KI_NOCC1, KI_EVN, KI_ERR, KI_WORDS = 8 };
 
 struct KITok { u32* cls; u32* glue; const u32* pos; u32* ls; u32* tid; };
 
+__device__ __forceinline__ void ki_flag_one(const KITok& t, u32 j, u32 cL, u64 key, u32* st, int par, u32* occ_j, u32* occ_r, u8* flags,
+                                            u8* rmark) {
+  const u32 l = t.ls[j];                         // (a dead entry keeps its class: ls decides)
+  if (l == 0u) return;
+  const u32 g = t.glue[j];
+  if (g & GB_LAST_FLAG) return;
+  const u32 r = j + 1u + (l >> 16);
+  if (gb_key_m(cL, g, t.cls[r]) != key) return;
+  const u32 q = atomicAdd(&st[KI_NOCC0 + par], 1u);
+  occ_j[q] = j; occ_r[q] = r;
+  flags[j] = 1; rmark[r] = 1;
+}
+
+// the class array streams through as 16-byte loads, four in flight per thread (one 4-byte load per thread in flight keeps
+// ~1.2 MB outstanding on 148 SMs, a quarter of what HBM needs); glue / ls are touched only where the left class matches
 __global__ void __launch_bounds__(256) ki_flag(KITok t, i64 N, u64 key, u32* __restrict__ st, int par, u32* __restrict__ occ_j,
                                                u32* __restrict__ occ_r, u8* __restrict__ flags, u8* __restrict__ rmark) {
   const u32 cL = (u32)(key >> 45) & 0x3FFFFu;
-  for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < N; j += (i64)gridDim.x * blockDim.x) {
-    if (t.cls[j] != cL) continue;              // 4 B / entry for almost every entry (a dead entry keeps its class: ls decides below)
-    const u32 l = t.ls[j];
-    if (l == 0u) continue;
-    const u32 g = t.glue[j];
-    if (g & GB_LAST_FLAG) continue;
-    const u32 r = (u32)j + 1u + (l >> 16);
-    if (gb_key_m(cL, g, t.cls[r]) != key) continue;
-    const u32 q = atomicAdd(&st[KI_NOCC0 + par], 1u);
-    occ_j[q] = (u32)j; occ_r[q] = r;
-    flags[j] = 1; rmark[r] = 1;
+  const uint4* c4 = reinterpret_cast<const uint4*>(t.cls);
+  const i64 N4 = N >> 2, stride = (i64)gridDim.x * blockDim.x;
+  for (i64 q0 = (i64)blockIdx.x * blockDim.x + threadIdx.x; q0 < N4; q0 += 4 * stride) {
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const i64 q = q0 + u * stride;
+      v[u] = q < N4 ? __ldg(c4 + q) : make_uint4(~0u, ~0u, ~0u, ~0u);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const u32 j = (u32)((q0 + u * stride) << 2);
+      if (v[u].x == cL) ki_flag_one(t, j, cL, key, st, par, occ_j, occ_r, flags, rmark);
+      if (v[u].y == cL) ki_flag_one(t, j + 1u, cL, key, st, par, occ_j, occ_r, flags, rmark);
+      if (v[u].z == cL) ki_flag_one(t, j + 2u, cL, key, st, par, occ_j, occ_r, flags, rmark);
+      if (v[u].w == cL) ki_flag_one(t, j + 3u, cL, key, st, par, occ_j, occ_r, flags, rmark);
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (u32)(N & 3)) {
+    const u32 j = (u32)(N4 << 2) + threadIdx.x;
+    if (t.cls[j] == cL) ki_flag_one(t, j, cL, key, st, par, occ_j, occ_r, flags, rmark);
   }
 }
 
 struct KIGeo { const double* V; i64 ld; const u32* bb; const i64* offsets; const double* f3tab; };
 
+// NeRF coordinates of the window of occurrence j into c (same order of operations as k_window_coords)
+__device__ __forceinline__ void ki_window(const KITok& t, const KIGeo& g, u32 j, int A, double* c) {
+  const i64 r0 = t.pos[j];
+  const i64 ld = g.ld;
+  const double* V = g.V;
+  double nca, cac, tau;
+  if (r0 == g.offsets[g.bb[r0]]) {             // the window starts its backbone: first-residue geometry of the token's class
+    const double* f = g.f3tab + 3 * (i64)t.cls[j];
+    nca = f[0]; cac = f[1]; tau = f[2];
+  } else {
+    nca = V[1 * ld + r0 - 1]; cac = V[2 * ld + r0 - 1]; tau = V[6 * ld + r0 - 1];
+  }
+  gb_v3 p0, p1, p2;
+  gb_first_residue(nca, cac, tau, p0, p1, p2);
+  int na = 0;
+  c[0] = p0.x; c[1] = p0.y; c[2] = p0.z; ++na;
+  if (na < A) { c[3] = p1.x; c[4] = p1.y; c[5] = p1.z; ++na; }
+  if (na < A) { c[6] = p2.x; c[7] = p2.y; c[8] = p2.z; ++na; }
+  for (int k = 0; na < A; ++k) {
+    const i64 r = r0 + k;
+    gb_v3 n = gb_place_dihedral(p0, p1, p2, V[7 * ld + r], V[0 * ld + r], V[4 * ld + r]);
+    c[3 * na] = n.x; c[3 * na + 1] = n.y; c[3 * na + 2] = n.z; ++na;
+    if (na >= A) break;
+    gb_v3 ca = gb_place_dihedral(p1, p2, n, V[8 * ld + r], V[1 * ld + r], V[5 * ld + r]);
+    c[3 * na] = ca.x; c[3 * na + 1] = ca.y; c[3 * na + 2] = ca.z; ++na;
+    if (na >= A) break;
+    gb_v3 cc = gb_place_dihedral(p2, n, ca, V[6 * ld + r], V[2 * ld + r], V[3 * ld + r + 1]);
+    c[3 * na] = cc.x; c[3 * na + 1] = cc.y; c[3 * na + 2] = cc.z; ++na;
+    p0 = n; p1 = ca; p2 = cc;
+  }
+}
+
+// Two shapes of the same arithmetic.  Many occurrences (early merges, short windows): one thread per occurrence, medoids in turn.
+// Few occurrences (late merges, long windows; the latency of one thread walking K Kabsch fits is what a merge then costs): one warp
+// per occurrence -- lane 0 places the atoms into shared memory, the lanes take the medoids, a (distance, index) minimum picks the
+// first smallest like np.argmin.  Each (occurrence, medoid) distance comes from the same gb_kabsch_rmsd call either way.
+#define KI_WARP_BELOW (148 * 8 * 4 * 4)   // up to four occurrences per resident warp
 __global__ void __launch_bounds__(128) ki_assign(KITok t, KIGeo g, const u32* __restrict__ st, int par, const u32* __restrict__ occ_j,
-                                                 int nres, int A, const double* __restrict__ med, int K, u32* __restrict__ aux) {
+                                                 int A, const double* __restrict__ med, int K, u32* __restrict__ aux) {
   const u32 nocc = st[KI_NOCC0 + par];
-  for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < nocc; i += gridDim.x * blockDim.x) {
+  if (nocc >= (u32)KI_WARP_BELOW) {
+    for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < nocc; i += gridDim.x * blockDim.x) {
+      const u32 j = occ_j[i];
+      double c[3 * KI_AMAX];
+      ki_window(t, g, j, A, c);
+      double bv = INFINITY;
+      u32 bi = 0;
+      for (int m = 0; m < K; ++m) {
+        const double d = gb_kabsch_rmsd(c, med + (i64)m * A * 3, A);
+        if (d < bv) { bv = d; bi = (u32)m; }     // strict <: first index on ties (np.argmin)
+      }
+      aux[j] = bi;
+    }
+    return;
+  }
+  __shared__ double sc[4][3 * KI_AMAX];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double* c = sc[w];
+  for (u32 i = blockIdx.x * 4 + w; i < nocc; i += gridDim.x * 4) {
     const u32 j = occ_j[i];
-    const i64 r0 = t.pos[j];
-    const i64 ld = g.ld;
-    const double* V = g.V;
-    double c[3 * KI_AMAX];
-    double nca, cac, tau;
-    if (r0 == g.offsets[g.bb[r0]]) {           // the window starts its backbone: first-residue geometry of the token's class
-      const double* f = g.f3tab + 3 * (i64)t.cls[j];
-      nca = f[0]; cac = f[1]; tau = f[2];
-    } else {
-      nca = V[1 * ld + r0 - 1]; cac = V[2 * ld + r0 - 1]; tau = V[6 * ld + r0 - 1];
-    }
-    gb_v3 p0, p1, p2;
-    gb_first_residue(nca, cac, tau, p0, p1, p2);
-    int na = 0;
-    c[0] = p0.x; c[1] = p0.y; c[2] = p0.z; ++na;
-    if (na < A) { c[3] = p1.x; c[4] = p1.y; c[5] = p1.z; ++na; }
-    if (na < A) { c[6] = p2.x; c[7] = p2.y; c[8] = p2.z; ++na; }
-    for (int k = 0; na < A; ++k) {             // (same order of operations as k_window_coords)
-      const i64 r = r0 + k;
-      gb_v3 n = gb_place_dihedral(p0, p1, p2, V[7 * ld + r], V[0 * ld + r], V[4 * ld + r]);
-      c[3 * na] = n.x; c[3 * na + 1] = n.y; c[3 * na + 2] = n.z; ++na;
-      if (na >= A) break;
-      gb_v3 ca = gb_place_dihedral(p1, p2, n, V[8 * ld + r], V[1 * ld + r], V[5 * ld + r]);
-      c[3 * na] = ca.x; c[3 * na + 1] = ca.y; c[3 * na + 2] = ca.z; ++na;
-      if (na >= A) break;
-      gb_v3 cc = gb_place_dihedral(p2, n, ca, V[6 * ld + r], V[2 * ld + r], V[3 * ld + r + 1]);
-      c[3 * na] = cc.x; c[3 * na + 1] = cc.y; c[3 * na + 2] = cc.z; ++na;
-      p0 = n; p1 = ca; p2 = cc;
-    }
+    if (lane == 0) ki_window(t, g, j, A, c);
+    __syncwarp();
     double bv = INFINITY;
-    u32 bi = 0;
-    for (int m = 0; m < K; ++m) {
+    u32 bi = 0xFFFFFFFFu;
+    for (int m = lane; m < K; m += 32) {
       const double d = gb_kabsch_rmsd(c, med + (i64)m * A * 3, A);
-      if (d < bv) { bv = d; bi = (u32)m; }       // strict <: first index on ties (np.argmin)
+      if (d < bv) { bv = d; bi = (u32)m; }
     }
-    aux[j] = bi;
-    (void)nres;
+    for (int o = 16; o; o >>= 1) {
+      const double ov = __shfl_xor_sync(0xFFFFFFFFu, bv, o);
+      const u32 oi = __shfl_xor_sync(0xFFFFFFFFu, bi, o);
+      if (ov < bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+    }
+    if (lane == 0) aux[j] = bi == 0xFFFFFFFFu ? 0u : bi;
+    __syncwarp();
   }
 }
 
@@ -137,17 +195,18 @@ extern "C" int gb_induce_replay(uint32_t* cls, uint32_t* glue, const uint32_t* p
                                 uint32_t* occ_j, uint32_t* occ_r, uint32_t* ev_left, uint32_t* ev_right, uint32_t* ev_p,
                                 int64_t evcap, uint32_t* st, uint32_t* rep_start, uint32_t* rep_cnt, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
+  (void)mnres_host;
   if (N <= 0 || n_merges <= 0) return 0;
   int sms = gb_sm_count();
   if (sms <= 0) sms = 148;
   KITok t{cls, glue, pos, ls, tid};
   KIGeo g{vals, ld, bb, offsets, f3tab};
-  const int flag_blocks = gb_blocks_for(N, 256 * 8, sms * 8);
+  const int flag_blocks = gb_blocks_for(N, 256 * 16, sms * 8);
   int par = 0;
   for (int m = 0; m < n_merges; ++m) {
     if (mA_host[m] > KI_AMAX || mK_host[m] <= 0) { gb_set_error("gb_induce_replay: merge %d has %d medoids / spans %d atoms (device limit %d)", m, mK_host[m], mA_host[m], KI_AMAX); return -2; }
     ki_flag<<<flag_blocks, 256, 0, s>>>(t, N, (u64)mkey_host[m], st, par, occ_j, occ_r, flags, rmark);
-    ki_assign<<<sms * 8, 128, 0, s>>>(t, g, st, par, occ_j, mnres_host[m], mA_host[m], med + mmed_off_host[m], mK_host[m], aux);
+    ki_assign<<<sms * 8, 128, 0, s>>>(t, g, st, par, occ_j, mA_host[m], med + mmed_off_host[m], mK_host[m], aux);
     ki_apply<<<sms, 128, 0, s>>>(t, st, par, occ_j, flags, rmark, aux, p2cls + mp2_off_host[m], p2tid + mp2_off_host[m], ev_left,
                                  ev_right, ev_p, (u32)evcap);
     ki_unflag<<<sms, 256, 0, s>>>(st, par, occ_j, occ_r, flags, rmark, rep_start, rep_cnt, m, 0u);

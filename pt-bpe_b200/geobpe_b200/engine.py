@@ -2216,10 +2216,13 @@ class Inducer(Learner):
         torch.cuda.synchronize(); t_stage.append(time.perf_counter())
         d = np.diff(t_stage).tolist()
         self.stage_s = dict(zip(("h2d", "k3_quantise", "residue_tokens_k4_k5", "replay_plan_host", "merge_replay"), d))
+        if getattr(self, "replay_s", None):
+            self.stage_s["merge_replay_parts"] = self.replay_s
 
     def _replay_device(self, plan):
         """all vocabulary merges applied on the device without a host round trip (csrc/k_induce.cu)"""
         ts, dev = self.ts, _dev()
+        t0 = time.perf_counter()
         live = [pl for pl in plan if pl is not None]
         R, N = self.bb.R, ts.T
         nm = len(live)
@@ -2260,11 +2263,13 @@ class Inducer(Learner):
         mK, mA, mnres = arr([len(pl[1]) for pl in live], C.c_int), arr([pl[5] for pl in live], C.c_int), arr([pl[4] for pl in live], C.c_int)
         moff, poff = arr(med_off, C.c_int64), arr(p2_off, C.c_int64)
         bb = self.bb
+        torch.cuda.synchronize(); t1 = time.perf_counter()
         _lib.call_n("gb_induce_replay", 4 * nm, ts.p("cls"), ts.p("glue"), ts.p("pos"), ts.p("len"), ts.p("tid"), _lib.ptr(ts.flags),
                     _lib.ptr(rmark), _lib.ptr(ts.aux), N, _lib.ptr(bb.vals), R, _lib.ptr(bb.bb), _lib.ptr(bb.offsets), _lib.ptr(self.f3tab()),
                     nm, mkey, mK, mA, mnres, moff, poff, _lib.ptr(med), _lib.ptr(p2cls), _lib.ptr(p2tid), _lib.ptr(ts.idx), _lib.ptr(occ_r),
                     _lib.ptr(self._evl), _lib.ptr(self._evr), _lib.ptr(self._evp), self._evl.numel(), _lib.ptr(st), _lib.ptr(rep_start),
                     _lib.ptr(rep_cnt))
+        torch.cuda.synchronize(); t2 = time.perf_counter()
         # one compaction at the end: the host sees dense arrays (len = plain residue counts)
         ls = ts.a["len"][:N]
         idx = torch.nonzero(ls != 0).flatten()
@@ -2292,6 +2297,7 @@ class Inducer(Learner):
             at = int(start[k]) + int(cnt[k])
             k += 1
         self.n_steps = int((cnt > 0).sum())
+        self.replay_s = {"medoid_coords_setup": t1 - t0, "kernels": t2 - t1, "compact_sort_readback": time.perf_counter() - t2}
 
     def _replay_host(self, merges, plan):
         """host-driven replay (one K2 compaction and one read-back per merge): windows beyond the device kernel's atom limit"""
