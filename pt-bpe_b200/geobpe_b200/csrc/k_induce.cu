@@ -1,8 +1,8 @@
 // K7: device-resident merge replay of induce (BPE.tokenize, bpe.py:1116-1139 with step_helper 1316-1425): every vocabulary
 // merge of a medoid-mode vocabulary applied, in learned order, to ALL held-out backbones at once without a host round trip.
 // Per merge four launches on the lazily compacted token arrays (ls = len | extra << 16, 0 = dead; see k_hloop2.cu):
-//   flag     one streaming pass (cls: 4 B / entry; glue, ls only where the left class matches): pairs whose packed key equals the
-//            merge's key -> occurrence list
+//   flag     one streaming pass over the class array (4 B / entry; dead entries carry the class ~0, so both classes of a pair
+//            come from the stream; glue, ls only where both match): pairs with the merge's packed key -> occurrence list
 //   assign   per occurrence: NeRF coordinates of the window from the pristine internal coordinates (rmsd_super_res,
 //            tokenizer.py:347-363, nerf.py:84-210) and Kabsch RMSD to the key's medoids (algo.py:8-65); first minimum wins
 //            (np.argmin, bpe.py:655-657)
@@ -21,7 +21,7 @@ struct KITok { u32* cls; u32* glue; const u32* pos; u32* ls; u32* tid; };
 
 __device__ __forceinline__ void ki_flag_one(const KITok& t, u32 j, u32 cL, u64 key, u32* st, int par, u32* occ_j, u32* occ_r, u8* flags,
                                             u8* rmark) {
-  const u32 l = t.ls[j];                         // (a dead entry keeps its class: ls decides)
+  const u32 l = t.ls[j];
   if (l == 0u) return;
   const u32 g = t.glue[j];
   if (g & GB_LAST_FLAG) return;
@@ -32,31 +32,40 @@ __device__ __forceinline__ void ki_flag_one(const KITok& t, u32 j, u32 cL, u64 k
   flags[j] = 1; rmark[r] = 1;
 }
 
-// the class array streams through as 16-byte loads, four in flight per thread (one 4-byte load per thread in flight keeps
-// ~1.2 MB outstanding on 148 SMs, a quarter of what HBM needs); glue / ls are touched only where the left class matches
+// Flag pass.  Dead entries carry the class ~0 (ki_apply), so the class stream alone tells a thread both classes of a pair: the
+// right class of entry j is the next entry of the stream that is not dead.  Each thread takes sixteen consecutive classes
+// (four 16-byte loads in flight), walks them backwards and keeps only entries whose (left, right) classes are the merge's; ls /
+// glue are read for those alone (and for the few whose right neighbour lies beyond the thread's sixteen).  Reading ls / glue
+// wherever the LEFT class matched cost 584 MB of DRAM reads per merge against the 205 MB class array (ncu --set full, merge
+// 1200 of the bench vocabulary) because a frequent left class touches most 32-byte sectors of both arrays.
+#define KI_DEAD 0xFFFFFFFFu
+#define KI_UNKNOWN 0xFFFFFFFEu
 __global__ void __launch_bounds__(256) ki_flag(KITok t, i64 N, u64 key, u32* __restrict__ st, int par, u32* __restrict__ occ_j,
                                                u32* __restrict__ occ_r, u8* __restrict__ flags, u8* __restrict__ rmark) {
-  const u32 cL = (u32)(key >> 45) & 0x3FFFFu;
+  const u32 cL = (u32)(key >> 45) & 0x3FFFFu, cR = (u32)(key >> 27) & 0x3FFFFu;
   const uint4* c4 = reinterpret_cast<const uint4*>(t.cls);
-  const i64 N4 = N >> 2, stride = (i64)gridDim.x * blockDim.x;
-  for (i64 q0 = (i64)blockIdx.x * blockDim.x + threadIdx.x; q0 < N4; q0 += 4 * stride) {
-    uint4 v[4];
+  const i64 N16 = N >> 4, stride = (i64)gridDim.x * blockDim.x;
+  for (i64 q = (i64)blockIdx.x * blockDim.x + threadIdx.x; q < N16; q += stride) {
+    u32 c[16];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const i64 q = q0 + u * stride;
-      v[u] = q < N4 ? __ldg(c4 + q) : make_uint4(~0u, ~0u, ~0u, ~0u);
+      const uint4 v = __ldg(c4 + 4 * q + u);
+      c[4 * u] = v.x; c[4 * u + 1] = v.y; c[4 * u + 2] = v.z; c[4 * u + 3] = v.w;
     }
+    u32 nxt = KI_UNKNOWN, m = 0u;
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const u32 j = (u32)((q0 + u * stride) << 2);
-      if (v[u].x == cL) ki_flag_one(t, j, cL, key, st, par, occ_j, occ_r, flags, rmark);
-      if (v[u].y == cL) ki_flag_one(t, j + 1u, cL, key, st, par, occ_j, occ_r, flags, rmark);
-      if (v[u].z == cL) ki_flag_one(t, j + 2u, cL, key, st, par, occ_j, occ_r, flags, rmark);
-      if (v[u].w == cL) ki_flag_one(t, j + 3u, cL, key, st, par, occ_j, occ_r, flags, rmark);
+    for (int e = 15; e >= 0; --e) {
+      if (c[e] == cL && (nxt == cR || nxt == KI_UNKNOWN)) m |= 1u << e;
+      if (c[e] != KI_DEAD) nxt = c[e];
+    }
+    while (m) {
+      const int e = __ffs(m) - 1;
+      m &= m - 1u;
+      ki_flag_one(t, (u32)(q << 4) + (u32)e, cL, key, st, par, occ_j, occ_r, flags, rmark);
     }
   }
-  if (blockIdx.x == 0 && threadIdx.x < (u32)(N & 3)) {
-    const u32 j = (u32)(N4 << 2) + threadIdx.x;
+  if (blockIdx.x == 0 && threadIdx.x < (u32)(N & 15)) {
+    const u32 j = (u32)(N16 << 4) + threadIdx.x;
     if (t.cls[j] == cL) ki_flag_one(t, j, cL, key, st, par, occ_j, occ_r, flags, rmark);
   }
 }
@@ -162,6 +171,7 @@ __global__ void __launch_bounds__(128) ki_apply(KITok t, u32* __restrict__ st, i
         t.glue[j] = t.glue[r];
         t.ls[j] = ((l & 0xFFFFu) + (lr & 0xFFFFu)) | (((l >> 16) + 1u + (lr >> 16)) << 16);
         t.ls[r] = 0u;
+        t.cls[r] = KI_DEAD;                         // the flag pass works on the class stream alone
       }
       keep = !keep;
       j = r; l = lr;
