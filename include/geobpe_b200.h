@@ -48,6 +48,15 @@ int gb_residue_backbone(const int64_t* offsets, int64_t S, int64_t R, uint32_t* 
 int64_t gb_select_scratch_elems(int64_t n);
 int gb_select_flagged(const uint8_t* flags, int64_t n, uint32_t mask, uint32_t* out_idx,
                       uint32_t* total, uint32_t* scratch, void* stream);
+/* gb_select_flagged for callers that may not allocate (CUDA graph capture, serving loops): the block-sum scratch is a
+ * file-scope device array inside the library (128 KB held by every GPU that loads it), so no scratch argument and no
+ * cudaMalloc / cudaFree anywhere on the call.  No counterpart in the reference.
+ * n above gb_select_flagged_static_max_n() (2^26 entries) is rejected with an error.  All calls share the
+ * array: calls that overlap on the GPU (streams without a dependency between them) race; calls ordered on one stream
+ * do not, and nothing in the array has to be cleared between calls. */
+int64_t gb_select_flagged_static_max_n(void);
+int gb_select_flagged_static(const uint8_t* flags, int64_t n, uint32_t mask, uint32_t* out_idx,
+                             uint32_t* total, void* stream);
 /* same, predicate keys[i] == key (filters the occurrence-set op log, bpe.py:1744 list(set)) */
 int gb_select_eq_u64(const uint64_t* keys, int64_t n, uint64_t key, uint32_t* out_idx,
                      uint32_t* total, uint32_t* scratch, void* stream);

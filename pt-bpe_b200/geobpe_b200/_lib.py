@@ -16,6 +16,8 @@ SIGNATURES = {
     "gb_residue_backbone": [P, I64, I64, P, P],
     "gb_select_flagged": [P, I64, U32, P, P, P, P],
     "gb_select_eq_u64": [P, I64, U64, P, P, P, P],
+    "gb_select_flagged_static": [P, I64, U32, P, P, P],
+    "gb_select_flagged_static_max_n": [],
     "gb_col_minmax": [P, I64, I64, P, P, P],
     "gb_col_hist": [P, I64, I64, P, I32, P, P, P],
     "gb_quantize_residues": [P, I64, I64, P, P, I64, P, I32, P, I32, F64, F64, F64, P, P, P, P, P],
@@ -83,13 +85,13 @@ SIGNATURES = {
     "gb_sm_count": [],
     "gb_select_scratch_elems": [I64],
 }
-_RESTYPES = {"gb_last_error": C.c_char_p, "gb_select_scratch_elems": I64, "gb_h_loop2_delta_bytes": I64,
+_RESTYPES = {"gb_last_error": C.c_char_p, "gb_select_scratch_elems": I64, "gb_select_flagged_static_max_n": I64, "gb_h_loop2_delta_bytes": I64,
              "gb_h_loop2_export_bytes": I64, "gb_h_loop2_flag_bytes": I64, "gb_h_loop_xbuf_elems": I64, "gb_h_loop_sbuf_bytes": I64}
 
 _lib = None
 launches = 0  # kernels launched through the C ABI (bench.py reports it)
 # kernels per entry point (default 1)
-KERNELS = {"gb_select_flagged": 3, "gb_select_eq_u64": 3, "gb_merge_compact": 3, "gb_table_argmax": 2,
+KERNELS = {"gb_select_flagged": 3, "gb_select_flagged_static": 3, "gb_select_eq_u64": 3, "gb_merge_compact": 3, "gb_table_argmax": 2,
            "gb_col_minmax": 3, "gb_first_positions_m": 2, "gb_first_positions_h": 2}
 
 

@@ -2,6 +2,7 @@
 // the token-array merge compaction of K2 (bpe.py:1955-1970 token_pos / bond_to_token update).
 #include "common.cuh"
 #include <stdarg.h>
+#include <mutex>
 
 static thread_local char g_err[512] = "";
 void gb_set_error(const char* fmt, ...) {
@@ -214,4 +215,44 @@ extern "C" int gb_merge_compact(const uint8_t* flags, int64_t T, const uint32_t*
   k_merge_scatter<<<(unsigned)nb, SEL_THREADS, 0, st>>>(a, (i64)T, scratch);
   GB_LAUNCH_CK();
   return 0;
+}
+
+// ---- ordered compaction without any allocation ---------------------------------------------------
+// gb_select_flagged with its block-sum scratch in a file-scope device array instead of a caller buffer, for callers that may
+// not allocate (CUDA graph capture, serving loops).  No counterpart in the reference.
+// The array costs GB_SELECT_STATIC_MAX_N / SEL_CHUNK + 2 words (128 KB) on every GPU that loads the library, until
+// exit.  All calls share it: two calls that overlap on the GPU (different streams, no dependency) race.  Nothing in it has to
+// start at zero -- the count pass overwrites words [0, nb) before the scan reads them -- so stale contents are harmless.
+#define GB_SELECT_STATIC_MAX_N (1ll << 26)
+#define SEL_STATIC_WORDS (GB_SELECT_STATIC_MAX_N / SEL_CHUNK + 2)
+static __device__ __align__(256) u32 g_sel_static[SEL_STATIC_WORDS];
+
+#define SEL_MAX_DEVICES 64
+static u32* g_sel_static_addr[SEL_MAX_DEVICES];   // device address of g_sel_static per device (host code cannot use the name itself)
+static std::mutex g_sel_static_mu;
+
+extern "C" int64_t gb_select_flagged_static_max_n(void) { return GB_SELECT_STATIC_MAX_N; }
+
+extern "C" int gb_select_flagged_static(const uint8_t* flags, int64_t n, uint32_t mask, uint32_t* out_idx, uint32_t* total,
+                                        void* stream) {
+  if (n > GB_SELECT_STATIC_MAX_N) {
+    gb_set_error("gb_select_flagged_static: n = %lld exceeds the static scratch (at most %lld entries); use gb_select_flagged "
+                 "with a caller buffer", (long long)n, (long long)GB_SELECT_STATIC_MAX_N);
+    return -2;
+  }
+  int dev = 0;
+  GB_CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= SEL_MAX_DEVICES) { gb_set_error("gb_select_flagged_static: device ordinal %d out of range", dev); return -2; }
+  u32* scratch;
+  {
+    std::lock_guard<std::mutex> lk(g_sel_static_mu);
+    if (!g_sel_static_addr[dev]) {               // once per device, with that device current
+      u32* p = nullptr;
+      GB_CK(cudaGetSymbolAddress((void**)&p, g_sel_static));
+      g_sel_static_addr[dev] = p;
+    }
+    scratch = g_sel_static_addr[dev];
+  }
+  PredFlag p{flags, mask};
+  return select_impl(p, n, out_idx, total, scratch, (cudaStream_t)stream);
 }
