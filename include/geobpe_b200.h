@@ -345,6 +345,17 @@ int gb_kabsch_assign(const double* P, int64_t Q, int A, const double* Mq, int K,
                      double* best, void* stream);
 /* D f32 [N][N] all-pairs Kabsch RMSD (float64 math, rounded to float32 like algo.py:170) */
 int gb_rmsd_matrix(const double* P, int N, int A, float* D, void* stream);
+/* the k-medoids iterations of algo.py:184-211 on D (one CTA): med_init u32 [k] = the host's rng.choice draw, med_out u32 [k],
+ * st u32 [4] = {status, iterations, float bits of the last total_shift, -}.  status 1 = a cluster came out empty, which
+ * draws rng.integers in the reference (algo.py:199): repeat the call's iterations on the host from med_init (the kernel
+ * uses no random numbers).  Every numpy operation is restated bit for bit: first-minimum argmin, float32 pairwise
+ * row sums (gb_pairwise_sum_host = the same routine compiled for the host, pinned against numpy on the CPU), float32
+ * total_shift.  N <= gb_pam_max_n(), k <= gb_pam_max_k(), else an error (run the host loop). */
+int gb_kmedoids_pam(const float* D, int N, int k, const uint32_t* med_init, int max_iter, uint32_t* med_out,
+                    uint32_t* st, void* stream);
+int gb_pam_max_n(void);
+int gb_pam_max_k(void);
+float gb_pairwise_sum_host(const float* v, int n);
 
 #ifdef __cplusplus
 }

@@ -51,6 +51,10 @@ SIGNATURES = {
     "gb_window_coords": [P, I64, I64, P, P, P, I64, I32, I32, P, P, F64, F64, F64, P, P, I32, P, P],
     "gb_kabsch_assign": [P, I64, I32, P, I32, P, P, P],
     "gb_rmsd_matrix": [P, I32, I32, P, P],
+    "gb_kmedoids_pam": [P, I32, I32, P, I32, P, P, P],
+    "gb_pam_max_n": [],
+    "gb_pam_max_k": [],
+    "gb_pairwise_sum_host": [P, I32],
     "gb_h_loop": [P, I32, I32, I32, I32, I32, P, P],
     "gb_h_loop_nargs": [],
     "gb_h_loop2": [P, I32, I32, I32, P],
@@ -85,7 +89,7 @@ SIGNATURES = {
     "gb_sm_count": [],
     "gb_select_scratch_elems": [I64],
 }
-_RESTYPES = {"gb_last_error": C.c_char_p, "gb_select_scratch_elems": I64, "gb_select_flagged_static_max_n": I64, "gb_h_loop2_delta_bytes": I64,
+_RESTYPES = {"gb_last_error": C.c_char_p, "gb_pairwise_sum_host": C.c_float, "gb_select_scratch_elems": I64, "gb_select_flagged_static_max_n": I64, "gb_h_loop2_delta_bytes": I64,
              "gb_h_loop2_export_bytes": I64, "gb_h_loop2_flag_bytes": I64, "gb_h_loop_xbuf_elems": I64, "gb_h_loop_sbuf_bytes": I64}
 
 _lib = None

@@ -11,7 +11,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(PKG))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libgeobpe_b200.so")
-SOURCES = ["k_select.cu", "k3_binning.cu", "k1_paircount.cu", "k1_slots.cu", "k_hloop.cu", "k_hloop2.cu", "k_induce.cu", "k_export.cu", "k_recon.cu", "k2_merge.cu", "k45_geometry.cu"]
+SOURCES = ["k_select.cu", "k3_binning.cu", "k1_paircount.cu", "k1_slots.cu", "k_hloop.cu", "k_hloop2.cu", "k_induce.cu", "k_export.cu", "k_recon.cu", "k2_merge.cu", "k45_geometry.cu", "k6_pam.cu"]
 
 
 def nvcc_path():

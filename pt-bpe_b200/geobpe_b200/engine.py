@@ -6,6 +6,8 @@ follow Python semantics exactly: the vocabulary dicts, JSON key strings for the 
 (bpe.py:1149,1469), the numpy RNG stream and the k-medoids iterations on the device-computed distance
 matrix (algo.py:184-211).
 """
+import collections
+import itertools
 import ctypes as C
 import os
 import json
@@ -1697,7 +1699,8 @@ class Learner:
         return out.view(Q, A * 3)
 
     def k_medoids(self, coords, k):
-        """algo.py:144-211 on the device-computed float32 distance matrix"""
+        """algo.py:144-211 on the device-computed float32 distance matrix; the update iterations run on the device too
+        (csrc/k6_pam.cu) unless a cluster comes out empty, which draws from the RNG stream (algo.py:199) and so runs on the host"""
         N = coords.shape[0]
         k = min(N, k)
         if k == N:
@@ -1705,9 +1708,21 @@ class Learner:
         A = coords.shape[1] // 3
         D = _empty(N * N, torch.float32)
         _lib.call("gb_rmsd_matrix", _lib.ptr(coords.contiguous()), N, A, _lib.ptr(D))
-        D = D.view(N, N).cpu().numpy()
+        init = self.rng.choice(np.arange(N), size=k, replace=False)
+        lib = _lib.load()
+        if N <= lib.gb_pam_max_n() and k <= lib.gb_pam_max_k() and not os.environ.get("GEOBPE_PAM_HOST"):
+            mi = torch.from_numpy(np.asarray(init, dtype=np.int32)).to(_dev())
+            out = _empty(k + 4, torch.int32)
+            _lib.call("gb_kmedoids_pam", _lib.ptr(D), N, k, _lib.ptr(mi), 10, _lib.ptr(out), out.data_ptr() + 4 * k)
+            r = _u32(out)
+            if int(r[k]) == 0:
+                return [int(m) for m in r[:k]]
+        return self._pam_host(D.view(N, N).cpu().numpy(), init, k)
+
+    def _pam_host(self, D, medoid_indices, k):
+        """the reference's loop in numpy (algo.py:184-211)"""
+        N = D.shape[0]
         rng = self.rng
-        medoid_indices = rng.choice(np.arange(N), size=k, replace=False)
         for _ in range(10):
             assignments = np.argmin(D[:, medoid_indices], axis=1)
             total_shift = 0.0
@@ -1881,11 +1896,12 @@ class Learner:
                   _lib.ptr(self.ts.u32), _lib.ptr(self.log_scratch))
         n = int(self.ts.u32[0].item())
         sel = self.log_sel[:n]
-        idx = _u32(sel)
-        rpos = _u32(self.log_pos[sel.to(torch.int64)])
+        both = _u32(torch.stack((sel, self.log_pos[sel.to(torch.int64)])))      # one read: log indices and their residues
+        idx, rpos = both[0], both[1]
         start = self.key_reset_at.get(key, 0)
-        keep = idx >= start
-        idx, rpos = idx[keep], rpos[keep]
+        if start:
+            keep = idx >= start
+            idx, rpos = idx[keep], rpos[keep]
         offs = self.bb.offsets_host
         bi = np.searchsorted(offs, rpos, side="right") - 1
         index = 3 * (rpos - offs[bi])
@@ -1893,18 +1909,7 @@ class Learner:
         seg = np.searchsorted(bounds, idx, side="right")          # 0 = initial adds, s = step s
         seg_start = np.concatenate([[0], bounds])[seg]
         is_add = (seg == 0) | (((idx - seg_start) % 4) >= 2)
-        s = set()
-        cur = 0
-        for sg, add, i, ix in zip(seg.tolist(), is_add.tolist(), bi.tolist(), index.tolist()):
-            if sg != cur:
-                if not s:
-                    s = set()          # count hit 0 at the end of a step -> _geo_dict.pop(k) (bpe.py:2134-2135)
-                cur = sg
-            if add:
-                s.add((i, ix))
-            else:
-                s.remove((i, ix))
-        return list(s)
+        return replay_set_order(seg, is_add, list(zip(bi.tolist(), index.tolist())))
 
     def m_key_string(self, key):
         """json string of compute_geo_key for a medoid-medoid pair (bpe.py:1248-1256): raw medoid floats,
@@ -1929,14 +1934,35 @@ class Learner:
             mx, ties = self._count_pairs()
             rec = None
             if self.sphere_packed:
-                pk = list(self.sphere_packed)
-                cnts, _ = self.table.lookup(pk)
-                live = [(-c, self.sphere_packed[k], k) for k, c in zip(pk, cnts) if c > 0]
-                if live:
-                    negc, key_str, key = min(live)
+                cnts = self._sphere_counts()
+                nz = np.flatnonzero(cnts)
+                if nz.size:
+                    pk = self._sp_keys
+                    negc, key_str, key = min((-int(cnts[i]), self.sphere_packed[pk[i]], pk[i]) for i in nz.tolist())
                     rec = (-negc, key_str, key)
             self._peek = (mx, ties, rec)
         return self._peek
+
+    def _sphere_counts(self):
+        """current pair count of every key that owns medoids (one kernel, one read); the query array lives on the device and
+        grows by the keys added since the last call"""
+        sp = self.sphere_packed
+        n = len(sp)
+        keys = getattr(self, "_sp_keys", None)
+        if keys is None or len(keys) > n or (keys and next(iter(sp)) != keys[0]):
+            keys, self._sp_q = [], _empty(1024, torch.int64)
+        if len(keys) < n:
+            fresh = list(itertools.islice(sp, len(keys), None))
+            if n > self._sp_q.numel():
+                q = _empty(next_pow2(2 * n), torch.int64)
+                q[:len(keys)] = self._sp_q[:len(keys)]
+                self._sp_q = q
+            self._sp_q[len(keys):n] = torch.from_numpy(np.array(fresh, dtype=np.uint64).view(np.int64)).to(_dev())
+            keys = keys + fresh
+        self._sp_keys = keys
+        out = _empty(2 * n, torch.int32)
+        _lib.call("gb_table_lookup", *self.table.ptrs(), _lib.ptr(self._sp_q), n, _lib.ptr(out), out.data_ptr() + 4 * n)
+        return _u32(out[:n])
 
     def step_m(self):
         """one merge iteration, medoid mode (bpe.py:1792-2166 with rmsd_key = key)"""
@@ -1958,9 +1984,10 @@ class Learner:
         nres = (length + 1) // 3
         A = length + 1
         _lib.call("gb_flag_pairs_m", ts.p("cls"), ts.p("glue"), ts.T, key, _lib.ptr(ts.flags))
-        N = ts.select(1, ts.idx)
-        if N != mx:
-            raise RuntimeError(f"flagged {N} occurrences, histogram counted {mx}")
+        # the occurrence list's length is the count K1 just reported; the list's own total lands in ts.u32[7] and is compared
+        # after the merge, with the read that ends the step (one synchronisation less per iteration)
+        N = mx
+        _lib.call("gb_select_flagged", _lib.ptr(ts.flags), ts.T, 1, _lib.ptr(ts.idx), ts.u32.data_ptr() + 28, _lib.ptr(ts.scratch))
         occ = ts.idx[:N].to(torch.int64)
         r0 = ts.a["pos"][occ].contiguous()
         f3c = ts.a["cls"][occ].contiguous()
@@ -1973,9 +2000,11 @@ class Learner:
             all_pos = self.set_order(key)
             if len(all_pos) != N:
                 raise RuntimeError(f"occurrence-set replay gave {len(all_pos)} entries, expected {N}")
-            rpos = _u32(ts.a["pos"][occ + 1])                     # global residue of the right token, ascending
+            # one read: global residue of the right token (ascending), window start and first-residue class of every occurrence
+            rpos, r0_h, f3c_h = _u32(torch.stack((ts.a["pos"][occ + 1], r0, f3c)))
             offs = self.bb.offsets_host
-            gp = np.array([offs[i] + ix // 3 for i, ix in all_pos], dtype=np.int64)
+            ap = np.fromiter(itertools.chain.from_iterable(all_pos), dtype=np.int64, count=2 * N).reshape(N, 2)
+            gp = offs[ap[:, 0]] + ap[:, 1] // 3                   # global residue of every (backbone, bond index) entry
             rank = np.searchsorted(rpos, gp)                      # occurrence rank of every set entry
             if N > self.max_num_strucs:
                 active = self.rng.choice(N, self.max_num_strucs, replace=False)
@@ -1985,7 +2014,6 @@ class Learner:
             actc = allc[torch.from_numpy(act_rank).to(_dev())].contiguous()
             med = self.k_medoids(actc, self.num_p(length))
             medc = actc[torch.tensor(med, device=_dev(), dtype=torch.int64)].contiguous()
-            r0_h, f3c_h = _u32(r0), _u32(f3c)
             geos = []
             for m in med:
                 q = int(act_rank[m])
@@ -1994,15 +2022,19 @@ class Learner:
             self.sphere_packed[key] = key_str
             n = len(self.tokens)
             self.sphere_n[key_str] = n
+            tid0 = len(self.token_keys)
             for p, geo in enumerate(geos):
                 self.tokens[(n, p)] = geo
                 self.token_keys.append((n, p))
         p2cls = torch.tensor([self.intern_class(g) for g in geos], dtype=torch.int32, device=_dev())
-        tid0 = self.token_keys.index((n, 0))
+        if recurring:
+            tid0 = self.token_keys.index((n, 0))
         p2tid = torch.arange(tid0, tid0 + len(geos), dtype=torch.int32, device=_dev())
         asg = self.assign(allc, medc)
         _lib.call("gb_scatter_u32", _lib.ptr(ts.idx), _lib.ptr(asg), N, _lib.ptr(ts.aux))
-        self._merge(key, n, p2cls, p2tid)
+        r = self._merge(key, n, p2cls, p2tid)
+        if int(r[7]) != mx:
+            raise RuntimeError(f"flagged {int(r[7])} occurrences, histogram counted {mx}")
         self.key_reset_at[key] = self.log_n
         if not recurring:
             self.n_steps += 1
@@ -2078,6 +2110,34 @@ class Learner:
             self.step_h()
             return False
         return self.step_m()
+
+
+def replay_set_order(seg, is_add, items):
+    """iteration order of a CPython set after a history of adds / removes (items[i] added or removed in step seg[i]); a set
+    found empty when a new step begins is replaced by a fresh one (count 0 -> _geo_dict.pop(k), bpe.py:2134-2135).
+    Runs of adds go through set.update and runs of removes through map(set.remove): both walk the items one by one through
+    the same table operations as single calls (set.difference_update would not: it shrinks the table afterwards)."""
+    n = len(items)
+    if n == 0:
+        return []
+    seg = np.asarray(seg)
+    is_add = np.asarray(is_add, dtype=bool)
+    chg = np.flatnonzero((seg[1:] != seg[:-1]) | (is_add[1:] != is_add[:-1])) + 1
+    starts = [0] + chg.tolist()
+    ends = chg.tolist() + [n]
+    segs, adds = seg[starts].tolist(), is_add[starts].tolist()
+    s = set()
+    cur = 0
+    for a, b, sg, add in zip(starts, ends, segs, adds):
+        if sg != cur:
+            if not s:
+                s = set()
+            cur = sg
+        if add:
+            s.update(items[a:b])
+        else:
+            collections.deque(map(s.remove, items[a:b]), maxlen=0)
+    return list(s)
 
 
 def parse_m_key(key_str):
