@@ -448,10 +448,10 @@ class Learner:
     def __init__(self, vals, offsets, bins, bin_strategy="histogram", std_bonds=True, mode="H",
                  rmsd_super_res=True, num_partitions=3, max_num_strucs=500, rng=None, verify=True, comm=None,
                  use_sketch=True, async_steps=True, resume=None):
-        self.comm = comm if (comm is not None and comm.world > 1) else None
-        if self.comm is not None and mode != "H":
-            raise NotImplementedError("multi-GPU medoid mode needs the sampled windows gathered in set order "
-                                      "(SURVEY 8e row 3); histogram mode is distributed this round")
+        # (GEOBPE_FORCE_COMM=1 keeps a one-rank communicator: the sharded code paths then run on a single GPU, for tests)
+        self.comm = comm if (comm is not None and (comm.world > 1 or os.environ.get("GEOBPE_FORCE_COMM") == "1")) else None
+        if self.comm is not None and mode == "M" and resume is not None:
+            raise NotImplementedError("resuming a sharded medoid-mode run is not built (checkpoints are per process)")
         if len(bins) != 1:
             raise NotImplementedError("size-bucketed --bins (more than one bucket) is not built yet: keys would "
                                       "need re-quantisation per bucket (SURVEY 7.2 hard part 2)")
@@ -477,6 +477,7 @@ class Learner:
         self.use_sketch = use_sketch
         self.k1b_events = None
         self.sketch = None
+        self._dist_layout()
         self.th = Thresholds(self.bb, self.bins, bin_strategy, std_bonds, self.comm)
         self.table = PairTable()
         self._tokens = {}           # BPE._tokens
@@ -506,6 +507,38 @@ class Learner:
         if resume is not None:
             self._load_state(resume)
 
+
+    def _dist_layout(self):
+        """where this shard sits in the whole set: the occurrence sets of medoid mode hold GLOBAL (backbone, bond index) pairs and
+        the medoid samples are drawn over the global occurrence order (contiguous shards in rank order = the reference's order)"""
+        offs = self.bb.offsets_host
+        if self.comm is None:
+            self.bb_base, self.r_base, self.g_offsets = 0, 0, np.asarray(offs, dtype=np.int64)
+            return
+        lens = self.comm.all_gather_object(np.diff(offs).astype(np.int64))
+        rk = self.comm.rank
+        self.bb_base = int(sum(len(l) for l in lens[:rk]))
+        self.r_base = int(sum(int(l.sum()) for l in lens[:rk]))
+        self.g_offsets = np.concatenate([[0], np.cumsum(np.concatenate(lens))]).astype(np.int64)
+
+    def _gather_rows(self, rows, mine, n):
+        """[n, width] float64 on every rank from the rows each rank owns (`mine`: their indices in 0..n): every row has exactly
+        one owner, so a sum of the raw bit patterns over the ranks reproduces it exactly (signed zeros included)"""
+        out = torch.zeros((n, rows.shape[1]), dtype=torch.float64, device=_dev())
+        if len(mine):
+            out[torch.from_numpy(np.asarray(mine, dtype=np.int64)).to(_dev())] = rows
+        if self.comm is not None:
+            self.comm.all_reduce(out.view(torch.int64))
+        return out
+
+    def _gather_geos(self, mine, n):
+        """medoid geometries computed by the ranks that hold their raw angles ({index: geo}) -> list of all n on every rank"""
+        merged = {}
+        for part in self.comm.all_gather_object(mine):
+            merged.update(part)
+        if len(merged) != n:
+            raise RuntimeError(f"{len(merged)} of {n} medoid windows were claimed by a rank")
+        return [merged[i] for i in range(n)]
 
     # ---- state that the device-driven loop advances: reading it first drains the loop -------------------------
     def _drain(self):
@@ -1757,35 +1790,49 @@ class Learner:
         is_last = torch.zeros(R, dtype=torch.bool, device=_dev())
         is_last[(bb.offsets[1:] - 1)] = True
         lists = {3: torch.nonzero(~is_last).flatten().to(torch.int32), 2: torch.nonzero(is_last).flatten().to(torch.int32)}
-        order = [3, 2] if bb.lens_host[0] > 1 else [2, 3]
+        comm = self.comm
+        order = [3, 2] if self.g_offsets[1] - self.g_offsets[0] > 1 else [2, 3]      # the FIRST backbone of the whole set decides
         cls_res = _zeros(R, torch.int32)
         tid_res = _zeros(R, torch.int32)
         for n, size in enumerate(order):
             occ = lists[size].contiguous()
-            N = int(occ.numel())
-            if N == 0:
+            N = int(occ.numel())                                   # this shard's windows of the size
+            if comm is None:
+                NG, base = N, 0
+            else:                                                  # the sample is drawn over the windows of all shards, in rank order
+                counts = comm.all_gather_object(N)
+                NG, base = int(sum(counts)), int(sum(counts[:comm.rank]))
+            if NG == 0:
                 continue
             A = size + 1
-            if N > self.max_num_strucs:
-                active = self.rng.choice(N, self.max_num_strucs, replace=False)
+            if NG > self.max_num_strucs:
+                active = self.rng.choice(NG, self.max_num_strucs, replace=False)
             else:
-                active = np.arange(N)
-            allc = self.coords(occ, N, 1, A, None)
-            act_dev = torch.from_numpy(np.asarray(active, dtype=np.int64)).to(_dev())
-            actc = allc[act_dev].contiguous()
+                active = np.arange(NG)
+            allc = self.coords(occ, N, 1, A, None) if N else torch.zeros((0, A * 3), dtype=torch.float64, device=_dev())
+            if comm is None:
+                act_dev = torch.from_numpy(np.asarray(active, dtype=np.int64)).to(_dev())
+                actc = allc[act_dev].contiguous()
+            else:
+                own = np.flatnonzero((active >= base) & (active < base + N))
+                rows = allc[torch.from_numpy(np.asarray(active[own] - base, dtype=np.int64)).to(_dev())]
+                actc = self._gather_rows(rows, own, len(active))
             med = self.k_medoids(actc, self.num_p(size))
             medc = actc[torch.tensor(med, device=_dev(), dtype=torch.int64)].contiguous()
-            asg = self.assign(allc, medc)
+            asg = self.assign(allc, medc) if N else _zeros(0, torch.int32)
             if size == 3:
                 k = '{"N:CA": [0], "CA:C": [0], "0C:1N": [0], "tau": [0], "CA:C:1N": [0], "psi": [0]}'
             else:
                 k = '{"CA:C": [0], "0C:1N": [0], "CA:C:1N": [0]}'
             self.sphere_dict[k] = []
             occ_h = _u32(occ)
+            if comm is None:
+                geos = [self.window_geo(int(occ_h[int(active[m])]), size, self.d_f3) for m in med]
+            else:
+                geos = self._gather_geos({p: self.window_geo(int(occ_h[int(active[m]) - base]), size, self.d_f3)
+                                          for p, m in enumerate(med) if base <= int(active[m]) < base + N}, len(med))
             p2cls, p2tid = [], []
-            for p, m in enumerate(med):
-                r0 = int(occ_h[int(active[m])])
-                geo = self.window_geo(r0, size, self.d_f3)
+            for p, geo in enumerate(geos):
                 self.sphere_dict[k].append(geo)
                 p2tid.append(len(self.token_keys))
                 self.tokens[(n, p)] = geo
@@ -1909,6 +1956,13 @@ class Learner:
         seg = np.searchsorted(bounds, idx, side="right")          # 0 = initial adds, s = step s
         seg_start = np.concatenate([[0], bounds])[seg]
         is_add = (seg == 0) | (((idx - seg_start) % 4) >= 2)
+        if self.comm is not None:
+            # the reference's set saw, step by step, the operations of every backbone in order: shards are contiguous in rank
+            # order, so the whole history is the rank-order concatenation re-grouped by step (stable sort on the step index)
+            parts = self.comm.all_gather_object((seg, is_add, bi + self.bb_base, index))
+            seg, is_add, bi, index = (np.concatenate([pt[c] for pt in parts]) for c in range(4))
+            o = np.argsort(seg, kind="stable")
+            seg, is_add, bi, index = seg[o], is_add[o], bi[o], index[o]
         return replay_set_order(seg, is_add, list(zip(bi.tolist(), index.tolist())))
 
     def m_key_string(self, key):
@@ -1931,7 +1985,7 @@ class Learner:
         """recount (K1) and look at the top of the priority order: (max count, ties, recurring choice or None).
         Keys that already own medoids sort first whatever their count (bpe.py:2121-2127,2164-2166)."""
         if self._peek is None:
-            mx, ties = self._count_pairs()
+            mx, ties = self._count_pairs() if self.comm is None else self._count_pairs_dist_m()
             rec = None
             if self.sphere_packed:
                 cnts = self._sphere_counts()
@@ -1962,7 +2016,46 @@ class Learner:
         self._sp_keys = keys
         out = _empty(2 * n, torch.int32)
         _lib.call("gb_table_lookup", *self.table.ptrs(), _lib.ptr(self._sp_q), n, _lib.ptr(out), out.data_ptr() + 4 * n)
+        if self.comm is not None:                  # the table holds this shard's counts
+            self.comm.all_reduce(out[:n])
         return _u32(out[:n])
+
+    def _count_pairs_dist_m(self):
+        """medoid-mode K1 on a shard: exact local table -> slot counters summed over the ranks -> exact global maximum and every
+        key tied at it (distributed.global_top); the table keeps the LOCAL counts for _sphere_counts"""
+        from .distributed import global_top
+        ts, tab, comm = self.ts, self.table, self.comm
+        want = 4 * max(tab.distinct, 1024) + 4096
+        tab.ensure(2 * max(ts.T, 1) if tab.M == 0 else max(want, 1 << 12))
+        while True:
+            _lib.call("gb_table_clear", *tab.ptrs())
+            tab.overflow.zero_()
+            if ts.T > 1:
+                _lib.call("gb_pair_count_m", ts.p("cls"), ts.p("glue"), ts.T, *tab.ptrs(), _lib.ptr(tab.overflow))
+            _lib.call("gb_table_argmax", *tab.ptrs(), _lib.ptr(tab.out4), _lib.ptr(tab.tie_keys), _lib.ptr(tab.tie_min), tab.TIE_CAP)
+            out4 = _u32(tab.out4)
+            if int(tab.overflow.item()) or int(out4[2]) * 2 > tab.M:
+                tab.ensure(tab.M * 4)
+                continue
+            tab.distinct = int(out4[2])
+            break
+        if not hasattr(self, "_slots"):
+            self._slots = _zeros(self.NS, torch.int32)
+            self._mark = _zeros(self.NS, torch.uint8)
+            self._ck = _empty(1 << 16, torch.int64); self._cc = _empty(1 << 16, torch.int32)
+        _lib.call("gb_table_to_slots", _lib.ptr(tab.keys), _lib.ptr(tab.cnt), tab.M, _lib.ptr(self._slots), self.NS)
+
+        def cand(sel):
+            self._mark.zero_()
+            self._mark[torch.from_numpy(sel).to(_dev())] = 1
+            _lib.call("gb_table_dump_marked", _lib.ptr(tab.keys), _lib.ptr(tab.cnt), tab.M, _lib.ptr(self._mark), self.NS,
+                      _lib.ptr(self._ck), _lib.ptr(self._cc), _lib.ptr(ts.u32), 1 << 16)
+            n = int(ts.u32[0].item())
+            if n > (1 << 16):
+                raise RuntimeError("too many local keys in the top slots")
+            return self._ck[:n].cpu().numpy(), _u32(self._cc[:n])
+        mx, tied = global_top(comm, self._slots, cand, _dev(), cap=1 << 16)
+        return mx, [(int(k) & M64, 0, None, None) for k in sorted(tied)]
 
     def step_m(self):
         """one merge iteration, medoid mode (bpe.py:1792-2166 with rmsd_key = key)"""
@@ -1986,16 +2079,30 @@ class Learner:
         _lib.call("gb_flag_pairs_m", ts.p("cls"), ts.p("glue"), ts.T, key, _lib.ptr(ts.flags))
         # the occurrence list's length is the count K1 just reported; the list's own total lands in ts.u32[7] and is compared
         # after the merge, with the read that ends the step (one synchronisation less per iteration)
-        N = mx
-        _lib.call("gb_select_flagged", _lib.ptr(ts.flags), ts.T, 1, _lib.ptr(ts.idx), ts.u32.data_ptr() + 28, _lib.ptr(ts.scratch))
+        comm = self.comm
+        if comm is None:
+            N = mx
+            _lib.call("gb_select_flagged", _lib.ptr(ts.flags), ts.T, 1, _lib.ptr(ts.idx), ts.u32.data_ptr() + 28, _lib.ptr(ts.scratch))
+        else:
+            N = ts.select(1, ts.idx)                               # this shard's occurrences (mx counts all shards')
         occ = ts.idx[:N].to(torch.int64)
         r0 = ts.a["pos"][occ].contiguous()
         f3c = ts.a["cls"][occ].contiguous()
-        allc = self.coords(r0, N, nres, A, f3c)
+        allc = self.coords(r0, N, nres, A, f3c) if N else torch.zeros((0, A * 3), dtype=torch.float64, device=_dev())
         if recurring:
             geos = self.sphere_dict[key_str]
             n = self.sphere_n[key_str]
             medc = self.geo_coords(geos, A)
+        elif comm is not None:
+            geos, medc = self._new_medoids_dist(key, mx, N, occ, r0, f3c, allc, length)
+            self.sphere_dict[key_str] = geos
+            self.sphere_packed[key] = key_str
+            n = len(self.tokens)
+            self.sphere_n[key_str] = n
+            tid0 = len(self.token_keys)
+            for p, geo in enumerate(geos):
+                self.tokens[(n, p)] = geo
+                self.token_keys.append((n, p))
         else:
             all_pos = self.set_order(key)
             if len(all_pos) != N:
@@ -2030,15 +2137,48 @@ class Learner:
         if recurring:
             tid0 = self.token_keys.index((n, 0))
         p2tid = torch.arange(tid0, tid0 + len(geos), dtype=torch.int32, device=_dev())
-        asg = self.assign(allc, medc)
-        _lib.call("gb_scatter_u32", _lib.ptr(ts.idx), _lib.ptr(asg), N, _lib.ptr(ts.aux))
+        if N:
+            asg = self.assign(allc, medc)
+            _lib.call("gb_scatter_u32", _lib.ptr(ts.idx), _lib.ptr(asg), N, _lib.ptr(ts.aux))
         r = self._merge(key, n, p2cls, p2tid)
-        if int(r[7]) != mx:
+        if comm is None and int(r[7]) != mx:
             raise RuntimeError(f"flagged {int(r[7])} occurrences, histogram counted {mx}")
         self.key_reset_at[key] = self.log_n
         if not recurring:
             self.n_steps += 1
         return recurring
+
+    def _new_medoids_dist(self, key, NG, N, occ, r0, f3c, allc, length):
+        """medoids of a key met for the first time, on a shard (bpe.py:1739-1789 rmsd_partition): the occurrence set's order is
+        replayed from every rank's history, the sample is drawn over it with the shared RNG stream, each sampled window's
+        coordinates come from the rank that holds it, and every rank runs the same k-medoids on the same matrix"""
+        ts = self.ts
+        all_pos = self.set_order(key)
+        if len(all_pos) != NG:
+            raise RuntimeError(f"occurrence-set replay gave {len(all_pos)} entries, expected {NG}")
+        ap = np.fromiter(itertools.chain.from_iterable(all_pos), dtype=np.int64, count=2 * NG).reshape(NG, 2)
+        gp = self.g_offsets[ap[:, 0]] + ap[:, 1] // 3                 # global residue of every entry's right token
+        if NG > self.max_num_strucs:
+            active = self.rng.choice(NG, self.max_num_strucs, replace=False)
+        else:
+            active = np.arange(NG)
+        if N:
+            rpos, r0_h, f3c_h = _u32(torch.stack((ts.a["pos"][occ + 1], r0, f3c)))
+        else:
+            rpos = r0_h = f3c_h = np.zeros(0, dtype=np.int64)
+        lp = gp[active] - self.r_base                                 # local residue where this shard holds the entry
+        own = np.flatnonzero((lp >= 0) & (lp < self.bb.R))
+        loc = np.searchsorted(rpos, lp[own])                          # its rank among this shard's occurrences
+        if own.size and (loc.max() >= N or not np.array_equal(rpos[loc], lp[own])):
+            raise RuntimeError("a sampled set entry is not an occurrence on the shard that holds its backbone")
+        rows = allc[torch.from_numpy(loc.astype(np.int64)).to(_dev())]
+        actc = self._gather_rows(rows, own, len(active))
+        med = self.k_medoids(actc, self.num_p(length))
+        medc = actc[torch.tensor(med, device=_dev(), dtype=torch.int64)].contiguous()
+        where = {int(a): int(q) for a, q in zip(own.tolist(), loc.tolist())}
+        mine = {p: self.window_geo(int(r0_h[where[m]]), length, self.class_f3[int(f3c_h[where[m]])])
+                for p, m in enumerate(med) if m in where}
+        return self._gather_geos(mine, len(med)), medc
 
     def geo_coords(self, geos, A):
         """Tokenizer.key_coords (tokenizer.py:204-230) for medoid geometries: each one placed in its own blank

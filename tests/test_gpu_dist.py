@@ -96,3 +96,106 @@ def test_two_gpu_h_mode_matches_oracle(mode, uneven):
         assert tokens == want_tokens
         for i, seg in enumerate(segs):
             assert seg == [list(x) for x in ora.tokenizers[a + i].bond_to_token.values()]
+
+
+# ---- medoid mode on shards ---------------------------------------------------------------------------------------------
+M_HP = dict(bins={1: 10}, bin_strategy="histogram", std_bonds=False, rmsd_super_res=True,
+            num_partitions={2: 2, 3: 4, 5: 2, 6: 2, 8: 1}, max_num_strucs=50)
+M_GEN = (30, 48, 21)
+M_STEPS = 30
+
+
+def _m_result(L, o, nb):
+    """(pop log, vocabulary, per-backbone segmentation) of a medoid-mode learner holding backbones with local offsets o"""
+    from geobpe_b200 import engine as E
+    ts = L.ts
+    pos, ln, tid, glue = (E._u32(ts.a[f][:ts.T]) for f in ("pos", "len", "tid", "glue"))
+    keys = L.token_keys
+    segs = []
+    for i in range(nb):
+        lo, hi = np.searchsorted(pos, o[i]), np.searchsorted(pos, o[i + 1])
+        segs.append([[int(3 * (pos[j] - o[i])), list(keys[int(tid[j])]), int(3 * ln[j] - (1 if glue[j] & E.LAST else 0))]
+                     for j in range(lo, hi)])
+    return [list(p) for p in L.pop_log], [[list(k), v] for k, v in L.tokens.items()], segs
+
+
+def _m_steps(L):
+    for _ in range(M_STEPS):         # BPE.step: one merge, then every merge whose key already owns medoids (bpe.py:2164-2166)
+        L.step()
+        while L.peek_m()[2] is not None:
+            L.step()
+
+
+def m_worker(rank, world, port, q, uneven):
+    sys.path.insert(0, os.path.join(ROOT, "pt-bpe_b200"))
+    import torch.distributed as dist
+    from geobpe_b200 import engine as E, synthetic
+    from geobpe_b200.distributed import Comm, shard_ranges
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    vals, offs = synthetic.generate(M_GEN[0], M_GEN[1], seed=M_GEN[2], ragged=True)
+    a, b = shard_ranges(np.diff(offs), world)[rank]
+    if uneven:                       # rank 1 holds the last backbone only: most merges have no occurrence there
+        cut = len(offs) - 2
+        a, b = (0, cut) if rank == 0 else (cut, len(offs) - 1)
+    v = vals[:, offs[a]:offs[b]]
+    o = offs[a:b + 1] - offs[a]
+    L = E.Learner(v, o, mode="M", comm=Comm(), rng=np.random.default_rng(0), **M_HP)      # the same RNG stream on every rank
+    _m_steps(L)
+    q.put((rank, a) + _m_result(L, o, b - a))
+    del L
+    dist.destroy_process_group()
+
+
+def _m_oracle():
+    import geobpe_oracle as O
+    from geobpe_b200 import synthetic
+    vals, offs = synthetic.generate(M_GEN[0], M_GEN[1], seed=M_GEN[2], ragged=True)
+    ora = O.BPE(synthetic.to_structures(vals, offs), res_init=True, seed=0, rmsd_partition_min_size=0, **M_HP)
+    ora.initialize(); ora.bin()
+    for _ in range(M_STEPS):
+        ora.step()
+    segs = [[[int(st), list(tok), int(ln)] for st, tok, ln in tk.bond_to_token.values()] for tk in ora.tokenizers]
+    return [list(p) for p in ora.pop_log], [[list(k), v] for k, v in ora._tokens.items()], segs
+
+
+def _check_m(res, want):
+    want_pops, want_tokens, want_segs = want
+    for rank, a, pops, tokens, segs in res:
+        assert pops == want_pops
+        assert tokens == want_tokens
+        for i, seg in enumerate(segs):
+            assert seg == want_segs[a + i], (rank, a + i)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("uneven", [False, True], ids=["balanced-shards", "one-backbone-shard"])
+def test_two_gpu_m_mode_matches_oracle(uneven):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 1000 + 40 + int(uneven)
+    ps = [ctx.Process(target=m_worker, args=(r, 2, port, q, uneven)) for r in range(2)]
+    [p.start() for p in ps]
+    try:
+        res = sorted(q.get(timeout=150) for _ in ps)
+        [p.join(60) for p in ps]
+    finally:
+        for p in ps:
+            if p.is_alive():
+                p.kill()
+    _check_m(res, _m_oracle())
+
+
+def test_m_mode_sharded_code_path_on_one_rank(monkeypatch):
+    """the sharded medoid-mode path with a one-rank communicator (GEOBPE_FORCE_COMM): gathers are identities, everything
+    else -- global top resolution, set-order gather, sample ownership -- runs as on a shard; result = the oracle's"""
+    from geobpe_b200 import engine as E, synthetic
+    from geobpe_b200.distributed import Comm
+    monkeypatch.setenv("GEOBPE_FORCE_COMM", "1")
+    vals, offs = synthetic.generate(M_GEN[0], M_GEN[1], seed=M_GEN[2], ragged=True)
+    L = E.Learner(vals, offs, mode="M", comm=Comm(), rng=np.random.default_rng(0), **M_HP)
+    assert L.comm is not None
+    _m_steps(L)
+    _check_m([(0, 0) + _m_result(L, offs, len(offs) - 1)], _m_oracle())
