@@ -54,6 +54,7 @@ def parse():
     ap.add_argument("--induce-merges", type=int, default=2000)
     ap.add_argument("--medoid-steps", type=int, default=300)
     ap.add_argument("--no-induce", action="store_true")
+    ap.add_argument("--medoid-sharded", action="store_true", help="N > 1: also time medoid mode on shards and self-check it (off by default)")
     ap.add_argument("--no-medoid", action="store_true")
     ap.add_argument("--cpu-steps", type=int, default=2000)
     ap.add_argument("--no-scale-probe", action="store_true")
@@ -246,30 +247,71 @@ def k5_probe(Q=1 << 20, K=500, A=4, reps=5):
             "peak_fp64_tflops_nominal": 40.0, "frac_of_nominal_fp64": Q * K * flop / t / 1e12 / 40.0}
 
 
-def medoid_arm(args):
-    """BASELINE configs[1] in medoid mode (README setting: bins 50, num_p 2-2:3-5:5-1:6-2:8-1, max_num_strucs 500)"""
+def medoid_arm(args, rank=0, world=1, comm=None, barrier=lambda: None):
+    """BASELINE configs[1] in medoid mode (README setting: bins 50, num_p 2-2:3-5:5-1:6-2:8-1, max_num_strucs 500); at N > 1
+    every rank holds its own 10,000 backbones (weak scaling) and the ranks share one RNG stream"""
     import torch
     from geobpe_b200 import engine as E, synthetic
     hp = hparams("M", None)
-    vals, offs = synthetic.generate(args.backbones, args.residues, seed=0)
+    vals, offs = synthetic.generate(args.backbones, args.residues, seed=rank)
+    barrier()
     t0 = time.perf_counter()
-    L = E.Learner(vals, offs, rng=np.random.default_rng(0), verify=True, **hp)
+    L = E.Learner(vals, offs, rng=np.random.default_rng(0), verify=True, comm=comm, **hp)
     torch.cuda.synchronize()
     t1 = time.perf_counter()
     for _ in range(5):
         L.step()
     torch.cuda.synchronize()
+    barrier()
     t2 = time.perf_counter()
     k0 = L.n_steps
     while L.n_steps - k0 < args.medoid_steps:
         L.step()
     torch.cuda.synchronize()
+    barrier()
     t3 = time.perf_counter()
     k = L.n_steps - k0
-    return {"value": k / (t3 - t2), "unit": "merge_iters/s", "steps": k, "initialize_s": t1 - t0, "steps_s": t3 - t2,
-            "config": f"{args.backbones} x {args.residues}, medoid quantisation, bins 50, num_p {NUM_P}, max_num_strucs 500",
-            "vocabulary_tokens": len(L.tokens), "live_tokens_end": int(L.ts.T),
-            "note": "host-driven step: K1 on the device, tie-break / occurrence-set order / k-medoids iterations on the host (numpy RNG stream)"}
+    dt = t3 - t2
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([dt], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    return {"value": k / dt, "unit": "merge_iters/s", "steps": k, "initialize_s": t1 - t0, "steps_s": dt, "n_gpus": world,
+            "config": f"{args.backbones} x {args.residues} per GPU, medoid quantisation, bins 50, num_p {NUM_P}, max_num_strucs 500",
+            "vocabulary_tokens": len(L.tokens), "live_tokens_end_rank0": int(L.ts.T),
+            "note": "host-driven step: K1, window coordinates, distance matrix, k-medoids iterations, assignment and merge on the device; "
+                    "tie-break and the occurrence set's CPython iteration order on the host (numpy RNG stream). N > 1: global maximum "
+                    "through the slot-counter allreduce, set histories and sampled windows gathered per new key"}
+
+
+def parity_check_m(comm, rank, world, steps=20, per_rank=16, n=48):
+    """N>1 self-check of sharded medoid mode against a one-GPU learner on the union (pop log, vocabulary, this rank's tokens)"""
+    import hashlib
+    from geobpe_b200 import engine as E, synthetic
+    vals, offs = synthetic.generate(per_rank * world, n, seed=78, ragged=True)
+    a, b = rank * per_rank, (rank + 1) * per_rank
+    lo, hi = int(offs[a]), int(offs[b])
+    hp = dict(bins={1: 10}, bin_strategy="histogram", std_bonds=False, mode="M", rmsd_super_res=True,
+              num_partitions={2: 2, 3: 4, 5: 2, 6: 2, 8: 1}, max_num_strucs=50)
+    Ls = E.Learner(np.ascontiguousarray(vals[:, lo:hi]), offs[a:b + 1] - offs[a], rng=np.random.default_rng(0), comm=comm, **hp)
+    Lu = E.Learner(vals, offs, rng=np.random.default_rng(0), **hp)
+    for _ in range(steps):
+        Ls.step(); Lu.step()
+    ok = [list(p) for p in Ls.pop_log] == [list(p) for p in Lu.pop_log]
+    ok = ok and json.dumps([[list(k), v] for k, v in Ls.tokens.items()]) == json.dumps([[list(k), v] for k, v in Lu.tokens.items()])
+    ts, tu = Ls.ts, Lu.ts
+    pu, lu, tu_ = E._u32(tu.a["pos"][:tu.T]), E._u32(tu.a["len"][:tu.T]), E._u32(tu.a["tid"][:tu.T])
+    sel = (pu >= lo) & (pu < hi)
+    seg_u = np.stack([pu[sel] - lo, lu[sel], tu_[sel]])
+    seg_s = np.stack([E._u32(ts.a["pos"][:ts.T]), E._u32(ts.a["len"][:ts.T]), E._u32(ts.a["tid"][:ts.T])])
+    ok = ok and seg_u.shape == seg_s.shape and bool((seg_u == seg_s).all())
+    digest = hashlib.sha256(json.dumps([list(p) for p in Lu.pop_log]).encode()).hexdigest()[:16]
+    flags = comm.all_gather_object((bool(ok), digest))
+    return {"ranks": world, "step_calls": steps, "ok": all(f for f, _ in flags) and len({d for _, d in flags}) == 1,
+            "per_rank_ok": [f for f, _ in flags], "pop_log_sha256_16": digest,
+            "what": f"medoid mode: {per_rank * world} ragged backbones x <= {n} residues sharded over {world} ranks vs one-GPU learner on "
+                    f"the union: pop log, vocabulary (medoid geometries) and this rank's segmentation bit-exact"}
 
 
 def induce_arm(args, rank, world, barrier):
@@ -595,6 +637,12 @@ def main():
                         "same_run_as_value": False}
             full["config"] = f"BASELINE configs[1] in full: {args.backbones} x {args.residues}, histogram quantisation, 2,000 merges"
     medoid = induce = k5 = None
+    if world > 1 and args.medoid_sharded and args.mode == "H":   # opt-in: an optional leg must not be able to stall the N > 1 line
+        try:
+            medoid = medoid_arm(args, rank, world, comm, barrier)
+            medoid["parity_check"] = parity_check_m(comm, rank, world)
+        except Exception as ex:
+            medoid = {"error": f"{type(ex).__name__}: {ex}"}
     if rank == 0 and world == 1 and not args.no_medoid and args.mode == "H":
         try:
             medoid = medoid_arm(args)
