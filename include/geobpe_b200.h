@@ -308,6 +308,12 @@ int gb_reconstruction(const uint16_t* rbins, int64_t R, const double* centres, i
                       const double* vals, int64_t ld, const uint32_t* bb, const int64_t* offsets, int64_t S,
                       double i_nca, double i_cac, double i_tau, uint32_t* tok_of, double* slots_cur, double* slots_orig,
                       double* coords_cur, double* coords_orig, double* rmsd, void* stream);
+/* lDDT-C-alpha of every backbone between two coordinate sets laid out like gb_reconstruction's (f64 [R][3 atoms][3], atom 1 =
+ * CA): what bin/encode.py:351-358 and plotting.py:436 take from esm's ProteinChain.lddt_ca(...).mean() per reference tokenizer.
+ * esm is absent from the reference tree and this image; its published compute_lddt is restated (float32, eps 1e-10, inclusion
+ * radius `cutoff` = 15 A in the reference's call, thresholds 0.5 / 1 / 2 / 4 A, per-residue scores averaged).  lddt f64 [S]. */
+int gb_lddt_ca(const double* coords_pred, const double* coords_true, const int64_t* offsets, int64_t S, double cutoff,
+               double* lddt, void* stream);
 
 /* ---- K7: induce merge replay on the device (bpe.py:1116-1139 BPE.tokenize's loop over the learned merges + step_helper
  *      1316-1425, for a whole batch of held-out backbones at once).  Token arrays are the medoid-mode SoA in the lazily

@@ -885,6 +885,24 @@ class BPE:
 
 
 # ----------------------------------------------------------------------------- dump (shared by golden maker and tests)
+def lddt_ca(pred_ca, true_ca, cutoff=15.0, eps=1e-10):
+    """mean per-residue lDDT-C-alpha, as bin/encode.py:351-358 / plotting.py:436 take it from esm's ProteinChain.lddt_ca
+    (esm is absent here: esm.utils.structure.metrics.compute_lddt -- the OpenFold lDDT -- restated; parity unpinned for this metric).
+    float32 throughout, like the atom37 arrays it is called on."""
+    P = np.asarray(pred_ca, dtype=np.float32)
+    Q = np.asarray(true_ca, dtype=np.float32)
+    n = len(P)
+    f = np.float32
+    dt = np.sqrt(f(eps) + ((Q[:, None, :] - Q[None, :, :]) ** 2).sum(-1, dtype=np.float32))
+    dp = np.sqrt(f(eps) + ((P[:, None, :] - P[None, :, :]) ** 2).sum(-1, dtype=np.float32))
+    to_score = (dt < f(cutoff)).astype(np.float32) * (f(1.0) - np.eye(n, dtype=np.float32))
+    l1 = np.abs(dt - dp)
+    score = ((l1 < 0.5).astype(np.float32) + (l1 < 1.0) + (l1 < 2.0) + (l1 < 4.0)).astype(np.float32) * f(0.25)
+    norm = f(1.0) / (f(eps) + to_score.sum(-1, dtype=np.float32))
+    per_res = norm * (f(eps) + (to_score * score).sum(-1, dtype=np.float32))
+    return float(per_res.mean())
+
+
 def _jsonable(x):
     if isinstance(x, dict):
         return {str(k): _jsonable(v) for k, v in x.items()}

@@ -62,6 +62,7 @@ SIGNATURES = {
     "gb_induce_replay": [P] * 8 + [I64, P, I64, P, P, P, I32] + [P] * 6 + [P, P, P] + [P] * 5 + [I64, P, P, P, P],
     "gb_induce_max_atoms": [],
     "gb_reconstruction": [P, I64, P, I32, P, P, P, I64, P, I32, P, I64, P, P, I64, F64, F64, F64, P, P, P, P, P, P, P],
+    "gb_lddt_ca": [P, P, P, I64, F64, P, P],
     "gb_token_stream": [P, P, P, P, I64, U32, U32, U32, U32, P, P],
     "gb_rehash_tokens": [P, P, P, P, I64, U64, P, P],
     "gb_h_loop2_state_words": [],

@@ -668,6 +668,10 @@ class BPE(_View):
         structure, one device pass -- what bin/encode.py:341-359 computes for its reference tokenizers one by one"""
         return self._learner.reconstruction()[0].cpu().numpy()
 
+    def reconstruction_lddt(self):
+        """mean lDDT-C-alpha of every backbone's current geometry against its pristine structure (bin/encode.py:351-358), one device pass"""
+        return self._learner.lddt_ca().cpu().numpy()
+
     def codebook_utility(self):
         """get_codebook_utility (plotting.py:78-95) over the token streams of all backbones, computed on the device"""
         from foldingdiff.plotting import get_codebook_utility

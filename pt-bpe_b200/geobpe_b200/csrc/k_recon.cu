@@ -107,3 +107,78 @@ extern "C" int gb_reconstruction(const uint16_t* rbins, int64_t R, const double*
   GB_LAUNCH_CK();
   return 0;
 }
+
+// ---- lDDT-C-alpha of every backbone (bin/encode.py:351-358, plotting.py:436: chain_recon.lddt_ca(orig_chain).mean()) --------------
+// The reference calls esm's ProteinChain.lddt_ca (esm is a dependency absent from the reference tree and from this image); its
+// published algorithm (esm.utils.structure.metrics.compute_lddt, the OpenFold / AlphaFold lDDT) is restated: float32 coordinates,
+// d = sqrt(1e-10 + |xi - xj|^2) for both chains, pairs j != i with d_true < cutoff are scored 1/4 per threshold 0.5 / 1 / 2 / 4 A that
+// |d_true - d_pred| stays under, residue score = (1e-10 + sum) / (1e-10 + pairs), chain value = mean over its residues.
+// One CTA per backbone; the C-alpha atoms of both chains go through shared memory in tiles.
+#define LD_THREADS 128
+#define LD_TILE 256
+__global__ void __launch_bounds__(LD_THREADS) k_lddt_ca(const double* __restrict__ pred, const double* __restrict__ truth,
+                                                        const i64* __restrict__ offsets, i64 S, float cutoff, double* __restrict__ out) {
+  __shared__ float tp[LD_TILE][3], tt[LD_TILE][3];
+  __shared__ double wsum[LD_THREADS / 32];
+  for (i64 b = blockIdx.x; b < S; b += gridDim.x) {
+    const i64 r0 = offsets[b];
+    const int n = (int)(offsets[b + 1] - r0);
+    double acc = 0.0;                              // this thread's share of the sum of residue scores
+    for (int i0 = 0; i0 < n; i0 += LD_THREADS) {
+      const int i = i0 + threadIdx.x;
+      float px = 0, py = 0, pz = 0, qx = 0, qy = 0, qz = 0;
+      if (i < n) {                                 // atom 1 of a residue's three (N, CA, C)
+        const double* p = pred + 9 * (r0 + i) + 3;
+        const double* q = truth + 9 * (r0 + i) + 3;
+        px = (float)p[0]; py = (float)p[1]; pz = (float)p[2];
+        qx = (float)q[0]; qy = (float)q[1]; qz = (float)q[2];
+      }
+      float cnt = 0.f, sc = 0.f;
+      for (int j0 = 0; j0 < n; j0 += LD_TILE) {
+        __syncthreads();
+        for (int t = threadIdx.x; t < LD_TILE && j0 + t < n; t += LD_THREADS) {
+          const double* p = pred + 9 * (r0 + j0 + t) + 3;
+          const double* q = truth + 9 * (r0 + j0 + t) + 3;
+          tp[t][0] = (float)p[0]; tp[t][1] = (float)p[1]; tp[t][2] = (float)p[2];
+          tt[t][0] = (float)q[0]; tt[t][1] = (float)q[1]; tt[t][2] = (float)q[2];
+        }
+        __syncthreads();
+        if (i < n) {
+          const int m = min(LD_TILE, n - j0);
+          for (int t = 0; t < m; ++t) {
+            if (j0 + t == i) continue;
+            // (no FMA contraction: a distance one ulp off could land on the other side of a threshold)
+            const float ax = qx - tt[t][0], ay = qy - tt[t][1], az = qz - tt[t][2];
+            const float dt = __fsqrt_rn(__fadd_rn(1e-10f, __fadd_rn(__fadd_rn(__fmul_rn(ax, ax), __fmul_rn(ay, ay)), __fmul_rn(az, az))));
+            if (!(dt < cutoff)) continue;
+            const float bx = px - tp[t][0], by = py - tp[t][1], bz = pz - tp[t][2];
+            const float dp = __fsqrt_rn(__fadd_rn(1e-10f, __fadd_rn(__fadd_rn(__fmul_rn(bx, bx), __fmul_rn(by, by)), __fmul_rn(bz, bz))));
+            const float l1 = fabsf(dt - dp);
+            cnt += 1.f;
+            sc += 0.25f * (float)((l1 < 0.5f) + (l1 < 1.0f) + (l1 < 2.0f) + (l1 < 4.0f));
+          }
+        }
+      }
+      if (i < n) acc += (double)((1e-10f + sc) * (1.0f / (1e-10f + cnt)));
+    }
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = 0.0;
+      for (int w = 0; w < LD_THREADS / 32; ++w) t += wsum[w];
+      out[b] = n > 0 ? t / n : 0.0;
+    }
+  }
+}
+
+extern "C" int gb_lddt_ca(const double* coords_pred, const double* coords_true, const int64_t* offsets, int64_t S, double cutoff,
+                          double* lddt, void* stream) {
+  if (S <= 0) return 0;
+  int sms = gb_sm_count();
+  if (sms <= 0) sms = 148;
+  k_lddt_ca<<<gb_blocks_for(S, 1, sms * 16), LD_THREADS, 0, (cudaStream_t)stream>>>(coords_pred, coords_true, offsets, S, (float)cutoff, lddt);
+  GB_LAUNCH_CK();
+  return 0;
+}

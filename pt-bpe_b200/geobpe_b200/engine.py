@@ -2245,6 +2245,16 @@ class Learner:
                     _lib.ptr(rmsd))
         return rmsd, c_cur.view(3 * R, 3), c_org.view(3 * R, 3)
 
+    def lddt_ca(self, cutoff=15.0, coords=None):
+        """f-4: lDDT-C-alpha of every backbone's current quantised geometry against its pristine structure (mean of the per-residue
+        scores, what bin/encode.py:351-358 takes from esm's lddt_ca per reference tokenizer) -- f64 [S] device tensor"""
+        if coords is None:
+            coords = self.reconstruction()[1:]
+        c_cur, c_org = coords
+        out = _empty(self.bb.S, torch.float64)
+        _lib.call("gb_lddt_ca", _lib.ptr(c_cur), _lib.ptr(c_org), _lib.ptr(self.bb.offsets), self.bb.S, float(cutoff), _lib.ptr(out))
+        return out
+
     def step(self):
         if self.mode == "H":
             self.step_h()

@@ -258,3 +258,26 @@ def test_reconstruction_metrics_for_all_backbones(hp):
         want = O.compute_rmsd(cur, org)
         assert abs(rmsd[i] - want) < 1e-7
     assert np.array_equal(bpe.reconstruction_rmsd(), rmsd)
+
+
+@pytest.mark.parametrize("hp", [HP_H, HP_M], ids=["H", "M"])
+def test_lddt_ca_for_all_backbones(hp):
+    """f-4: lDDT-C-alpha of every backbone on the device against the oracle's restatement of esm's compute_lddt on the same
+    coordinates (float32 arithmetic on both sides; summation order differs, so 1e-5 on a value in [0, 1])"""
+    bpe, strucs = learn(hp, S=12, n=70, seed=73, steps=25)
+    L = bpe._learner
+    rmsd, c_cur, c_org = L.reconstruction()
+    got = L.lddt_ca(coords=(c_cur, c_org)).cpu().numpy()
+    c_cur, c_org = c_cur.cpu().numpy(), c_org.cpu().numpy()
+    offs = bpe._offsets
+    assert got.shape == (len(bpe.tokenizers),)
+    for i in range(len(bpe.tokenizers)):
+        a, b = 3 * int(offs[i]), 3 * int(offs[i + 1])
+        want = O.lddt_ca(c_cur[a:b][1::3], c_org[a:b][1::3])
+        assert abs(got[i] - want) < 1e-5, (i, got[i], want)
+    assert 0.0 < got.min() and got.max() <= 1.0 and got.min() < 1.0        # quantisation moved something, nothing is degenerate
+    assert np.array_equal(bpe.reconstruction_lddt(), got)
+    # a tighter inclusion radius changes the pair set (and is honoured)
+    g8 = L.lddt_ca(cutoff=8.0, coords=L.reconstruction()[1:]).cpu().numpy()
+    a, b = 3 * int(offs[0]), 3 * int(offs[1])
+    assert abs(g8[0] - O.lddt_ca(c_cur[a:b][1::3], c_org[a:b][1::3], cutoff=8.0)) < 1e-5
