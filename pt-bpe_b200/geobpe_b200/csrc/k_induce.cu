@@ -5,7 +5,7 @@
 //            come from the stream; glue, ls only where both match): pairs with the merge's packed key -> occurrence list
 //   assign   per occurrence: NeRF coordinates of the window from the pristine internal coordinates (rmsd_super_res,
 //            tokenizer.py:347-363, nerf.py:84-210) and Kabsch RMSD to the key's medoids (algo.py:8-65); first minimum wins
-//            (np.argmin, bpe.py:655-657)
+//            (np.argmin, bpe.py:655-657); skipped for keys with a single medoid (the argmin of one distance is 0)
 //   apply    overlap rule (bpe.py:1909-1914: the head of every run merges the 1st, 3rd, ... occurrence) + in-place merge: the
 //            left entry takes the assigned medoid's class / token id, the right entry dies; merge events appended
 //   unflag   marks removed, per-merge event range recorded
@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(128) ki_assign(KITok t, KIGeo g, const u32* __
 __global__ void __launch_bounds__(128) ki_apply(KITok t, u32* __restrict__ st, int par, const u32* __restrict__ occ_j,
                                                 const u8* __restrict__ flags, const u8* __restrict__ rmark, const u32* __restrict__ aux,
                                                 const u32* __restrict__ p2cls, const u32* __restrict__ p2tid, u32* __restrict__ ev_left,
-                                                u32* __restrict__ ev_right, u32* __restrict__ ev_p, u32 evcap) {
+                                                u32* __restrict__ ev_right, u32* __restrict__ ev_p, u32 evcap, int single) {
   const u32 nocc = st[KI_NOCC0 + par];
   for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < nocc; i += gridDim.x * blockDim.x) {
     u32 j = occ_j[i];
@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(128) ki_apply(KITok t, u32* __restrict__ st, i
     while (flags[j]) {
       const u32 r = j + 1u + (l >> 16), lr = t.ls[r];
       if (keep) {
-        const u32 p = aux[j];
+        const u32 p = single ? 0u : aux[j];        // one medoid: the argmin is 0 whatever the distances (no assignment pass ran)
         const u32 q = atomicAdd(&st[KI_EVN], 1u);
         if (q < evcap) { ev_left[q] = t.pos[j]; ev_right[q] = t.pos[r]; ev_p[q] = p; } else st[KI_ERR] = 1u;
         t.cls[j] = p2cls[p];
@@ -216,9 +216,10 @@ extern "C" int gb_induce_replay(uint32_t* cls, uint32_t* glue, const uint32_t* p
   for (int m = 0; m < n_merges; ++m) {
     if (mA_host[m] > KI_AMAX || mK_host[m] <= 0) { gb_set_error("gb_induce_replay: merge %d has %d medoids / spans %d atoms (device limit %d)", m, mK_host[m], mA_host[m], KI_AMAX); return -2; }
     ki_flag<<<flag_blocks, 256, 0, s>>>(t, N, (u64)mkey_host[m], st, par, occ_j, occ_r, flags, rmark);
-    ki_assign<<<sms * 8, 128, 0, s>>>(t, g, st, par, occ_j, mA_host[m], med + mmed_off_host[m], mK_host[m], aux);
+    const int single = mK_host[m] == 1;
+    if (!single) ki_assign<<<sms * 8, 128, 0, s>>>(t, g, st, par, occ_j, mA_host[m], med + mmed_off_host[m], mK_host[m], aux);
     ki_apply<<<sms, 128, 0, s>>>(t, st, par, occ_j, flags, rmark, aux, p2cls + mp2_off_host[m], p2tid + mp2_off_host[m], ev_left,
-                                 ev_right, ev_p, (u32)evcap);
+                                 ev_right, ev_p, (u32)evcap, single);
     ki_unflag<<<sms, 256, 0, s>>>(st, par, occ_j, occ_r, flags, rmark, rep_start, rep_cnt, m, 0u);
     par ^= 1;
   }

@@ -2088,11 +2088,16 @@ class Learner:
         occ = ts.idx[:N].to(torch.int64)
         r0 = ts.a["pos"][occ].contiguous()
         f3c = ts.a["cls"][occ].contiguous()
-        allc = self.coords(r0, N, nres, A, f3c) if N else torch.zeros((0, A * 3), dtype=torch.float64, device=_dev())
+        # a recurring key with a single medoid needs no geometry at all: the argmin over one distance is 0
+        lone = recurring and len(self.sphere_dict[key_str]) == 1
+        if lone:
+            allc = None
+        else:
+            allc = self.coords(r0, N, nres, A, f3c) if N else torch.zeros((0, A * 3), dtype=torch.float64, device=_dev())
         if recurring:
             geos = self.sphere_dict[key_str]
             n = self.sphere_n[key_str]
-            medc = self.geo_coords(geos, A)
+            medc = None if lone else self.geo_coords(geos, A)
         elif comm is not None:
             geos, medc = self._new_medoids_dist(key, mx, N, occ, r0, f3c, allc, length)
             self.sphere_dict[key_str] = geos
@@ -2138,7 +2143,7 @@ class Learner:
             tid0 = self.token_keys.index((n, 0))
         p2tid = torch.arange(tid0, tid0 + len(geos), dtype=torch.int32, device=_dev())
         if N:
-            asg = self.assign(allc, medc)
+            asg = self.assign(allc, medc) if len(geos) > 1 else _zeros(N, torch.int32)
             _lib.call("gb_scatter_u32", _lib.ptr(ts.idx), _lib.ptr(asg), N, _lib.ptr(ts.aux))
         r = self._merge(key, n, p2cls, p2tid)
         if comm is None and int(r[7]) != mx:
