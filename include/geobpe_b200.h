@@ -323,9 +323,10 @@ int gb_lddt_ca(const double* coords_pred, const double* coords_true, const int64
  *      occurrences flagged in one pass, each assigned to its nearest medoid (NeRF from the pristine coordinates `vals`,
  *      Kabsch RMSD, first minimum), overlap rule, in-place merge, (left, right, medoid) appended to the event log.
  *      st u32 [8] zeroed by the caller except st[2] = first free event slot; rep_start u32 [n_merges + 1] with
- *      rep_start[0] = st[2]; rep_cnt u32 [n_merges] receives the events of every merge.  Nothing is read back. */
+ *      rep_start[0] = st[2]; rep_cnt u32 [n_merges] receives the events of every merge.  Nothing is read back.
+ *      cw u32 [N]: scratch for the flag pass's stream words (class | 14-bit hash of the glue bins), filled here. */
 int gb_induce_replay(uint32_t* cls, uint32_t* glue, const uint32_t* pos, uint32_t* ls, uint32_t* tid, uint8_t* flags,
-                     uint8_t* rmark, uint32_t* aux, int64_t N, const double* vals, int64_t ld, const uint32_t* bb,
+                     uint8_t* rmark, uint32_t* aux, uint32_t* cw, int64_t N, const double* vals, int64_t ld, const uint32_t* bb,
                      const int64_t* offsets, const double* f3tab, int n_merges, const uint64_t* mkey_host,
                      const int* mK_host, const int* mA_host, const int* mnres_host, const int64_t* mmed_off_host,
                      const int64_t* mp2_off_host, const double* med, const uint32_t* p2cls, const uint32_t* p2tid,

@@ -59,7 +59,7 @@ SIGNATURES = {
     "gb_h_loop_nargs": [],
     "gb_h_loop2": [P, I32, I32, I32, P],
     "gb_h_loop2_nargs": [],
-    "gb_induce_replay": [P] * 8 + [I64, P, I64, P, P, P, I32] + [P] * 6 + [P, P, P] + [P] * 5 + [I64, P, P, P, P],
+    "gb_induce_replay": [P] * 9 + [I64, P, I64, P, P, P, I32] + [P] * 6 + [P, P, P] + [P] * 5 + [I64, P, P, P, P],
     "gb_induce_max_atoms": [],
     "gb_reconstruction": [P, I64, P, I32, P, P, P, I64, P, I32, P, I64, P, P, I64, F64, F64, F64, P, P, P, P, P, P, P],
     "gb_lddt_ca": [P, P, P, I64, F64, P, P],

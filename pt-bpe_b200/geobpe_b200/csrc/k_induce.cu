@@ -17,7 +17,12 @@
 
 enum { KI_NOCC0 = 0, KI_NOCC1, KI_EVN, KI_ERR, KI_WORDS = 8 };
 
-struct KITok { u32* cls; u32* glue; const u32* pos; u32* ls; u32* tid; };
+struct KITok { u32* cls; u32* glue; const u32* pos; u32* ls; u32* tid; u32* cw; };
+
+// stream word of an entry: its class (18 bits) and a 14-bit hash of its glue bins -- the flag pass filters on (left class, glue)
+// and on the right class without touching any other array; false positives (1 in 16 k class-level candidates) fall to the exact check
+__device__ __forceinline__ u32 ki_gh(u32 g27) { return (g27 * 0x9E3779B1u) >> 18; }
+__device__ __forceinline__ u32 ki_word(u32 cls, u32 g) { return (cls & 0x3FFFFu) | (ki_gh((u32)gb_key_m(0u, g, 0u)) << 18); }
 
 // a class-level candidate (both classes right, or the right one still unknown): the glue angles decide for most of them -- a frequent
 // class pair comes with many glue bins -- and glue[j] needs no other load first, so it is read before ls (whose extra count locates the
@@ -46,7 +51,8 @@ __device__ __forceinline__ void ki_flag_one(const KITok& t, u32 j, u32 cL, u64 k
 __global__ void __launch_bounds__(256) ki_flag(KITok t, i64 N, u64 key, u32* __restrict__ st, int par, u32* __restrict__ occ_j,
                                                u32* __restrict__ occ_r, u8* __restrict__ flags, u8* __restrict__ rmark) {
   const u32 cL = (u32)(key >> 45) & 0x3FFFFu, cR = (u32)(key >> 27) & 0x3FFFFu;
-  const uint4* c4 = reinterpret_cast<const uint4*>(t.cls);
+  const uint4* c4 = reinterpret_cast<const uint4*>(t.cw);
+  const u32 W = cL | (ki_gh((u32)(key & 0x7FFFFFFull)) << 18);
   const i64 N16 = N >> 4, stride = (i64)gridDim.x * blockDim.x;
   for (i64 q = (i64)blockIdx.x * blockDim.x + threadIdx.x; q < N16; q += stride) {
     u32 c[16];
@@ -58,8 +64,8 @@ __global__ void __launch_bounds__(256) ki_flag(KITok t, i64 N, u64 key, u32* __r
     u32 nxt = KI_UNKNOWN, m = 0u;
 #pragma unroll
     for (int e = 15; e >= 0; --e) {
-      if (c[e] == cL && (nxt == cR || nxt == KI_UNKNOWN)) m |= 1u << e;
-      if (c[e] != KI_DEAD) nxt = c[e];
+      if (c[e] == W && (nxt == cR || nxt == KI_UNKNOWN)) m |= 1u << e;
+      if (c[e] != KI_DEAD) nxt = c[e] & 0x3FFFFu;
     }
     while (m) {
       const int e = __ffs(m) - 1;
@@ -69,7 +75,7 @@ __global__ void __launch_bounds__(256) ki_flag(KITok t, i64 N, u64 key, u32* __r
   }
   if (blockIdx.x == 0 && threadIdx.x < (u32)(N & 15)) {
     const u32 j = (u32)(N16 << 4) + threadIdx.x;
-    if (t.cls[j] == cL) ki_flag_one(t, j, cL, key, st, par, occ_j, occ_r, flags, rmark);
+    if (t.cw[j] == W) ki_flag_one(t, j, cL, key, st, par, occ_j, occ_r, flags, rmark);
   }
 }
 
@@ -170,11 +176,12 @@ __global__ void __launch_bounds__(128) ki_apply(KITok t, u32* __restrict__ st, i
         const u32 q = atomicAdd(&st[KI_EVN], 1u);
         if (q < evcap) { ev_left[q] = t.pos[j]; ev_right[q] = t.pos[r]; ev_p[q] = p; } else st[KI_ERR] = 1u;
         t.cls[j] = p2cls[p];
+        t.cw[j] = ki_word(p2cls[p], t.glue[r]);
+        t.cw[r] = KI_DEAD;
         t.tid[j] = p2tid[p];
         t.glue[j] = t.glue[r];
         t.ls[j] = ((l & 0xFFFFu) + (lr & 0xFFFFu)) | (((l >> 16) + 1u + (lr >> 16)) << 16);
         t.ls[r] = 0u;
-        t.cls[r] = KI_DEAD;                         // the flag pass works on the class stream alone
       }
       keep = !keep;
       j = r; l = lr;
@@ -200,8 +207,13 @@ __global__ void __launch_bounds__(256) ki_unflag(u32* __restrict__ st, int par, 
 }
 
 // merges with host-side parameters (the caller leaves out merges whose key cannot occur); rep_start[0] = first free event slot
+__global__ void __launch_bounds__(256) ki_words(KITok t, i64 N, i64 cap) {
+  for (i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x; j < cap; j += (i64)gridDim.x * blockDim.x)
+    t.cw[j] = j < N && t.ls[j] != 0u ? ki_word(t.cls[j], t.glue[j]) : KI_DEAD;
+}
+
 extern "C" int gb_induce_replay(uint32_t* cls, uint32_t* glue, const uint32_t* pos, uint32_t* ls, uint32_t* tid, uint8_t* flags,
-                                uint8_t* rmark, uint32_t* aux, int64_t N, const double* vals, int64_t ld, const uint32_t* bb,
+                                uint8_t* rmark, uint32_t* aux, uint32_t* cw, int64_t N, const double* vals, int64_t ld, const uint32_t* bb,
                                 const int64_t* offsets, const double* f3tab, int n_merges, const uint64_t* mkey_host,
                                 const int* mK_host, const int* mA_host, const int* mnres_host, const int64_t* mmed_off_host,
                                 const int64_t* mp2_off_host, const double* med, const uint32_t* p2cls, const uint32_t* p2tid,
@@ -212,7 +224,8 @@ extern "C" int gb_induce_replay(uint32_t* cls, uint32_t* glue, const uint32_t* p
   if (N <= 0 || n_merges <= 0) return 0;
   int sms = gb_sm_count();
   if (sms <= 0) sms = 148;
-  KITok t{cls, glue, pos, ls, tid};
+  KITok t{cls, glue, pos, ls, tid, cw};
+  ki_words<<<gb_blocks_for(N, 256 * 8, sms * 8), 256, 0, s>>>(t, N, N);
   KIGeo g{vals, ld, bb, offsets, f3tab};
   const int flag_blocks = gb_blocks_for(N, 256 * 16, sms * 8);
   int par = 0;

@@ -2472,6 +2472,7 @@ class Inducer(Learner):
         rep_cnt = _zeros(nm, torch.int32)
         rmark = _zeros(ts.cap, torch.uint8)
         occ_r = _empty(ts.cap, torch.int32)
+        cw = _empty(ts.cap, torch.int32)               # the flag pass's stream words
         ts.flags.zero_()
         arr = lambda xs, ct: (ct * nm)(*xs)
         mkey = arr([pl[0] for pl in live], C.c_uint64)
@@ -2479,8 +2480,8 @@ class Inducer(Learner):
         moff, poff = arr(med_off, C.c_int64), arr(p2_off, C.c_int64)
         bb = self.bb
         torch.cuda.synchronize(); t1 = time.perf_counter()
-        _lib.call_n("gb_induce_replay", 4 * nm, ts.p("cls"), ts.p("glue"), ts.p("pos"), ts.p("len"), ts.p("tid"), _lib.ptr(ts.flags),
-                    _lib.ptr(rmark), _lib.ptr(ts.aux), N, _lib.ptr(bb.vals), R, _lib.ptr(bb.bb), _lib.ptr(bb.offsets), _lib.ptr(self.f3tab()),
+        _lib.call_n("gb_induce_replay", 4 * nm + 1, ts.p("cls"), ts.p("glue"), ts.p("pos"), ts.p("len"), ts.p("tid"), _lib.ptr(ts.flags),
+                    _lib.ptr(rmark), _lib.ptr(ts.aux), _lib.ptr(cw), N, _lib.ptr(bb.vals), R, _lib.ptr(bb.bb), _lib.ptr(bb.offsets), _lib.ptr(self.f3tab()),
                     nm, mkey, mK, mA, mnres, moff, poff, _lib.ptr(med), _lib.ptr(p2cls), _lib.ptr(p2tid), _lib.ptr(ts.idx), _lib.ptr(occ_r),
                     _lib.ptr(self._evl), _lib.ptr(self._evr), _lib.ptr(self._evp), self._evl.numel(), _lib.ptr(st), _lib.ptr(rep_start),
                     _lib.ptr(rep_cnt))
