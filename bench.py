@@ -20,6 +20,7 @@ Prints ONE JSON line on rank 0.
   medoid / induce / k5 / cpu_baseline / parity_check (N>1)   see DESIGN.md 6
 """
 import argparse
+import gc
 import json
 import os
 import subprocess
@@ -484,6 +485,7 @@ def main():
 
     def e2e_run(nsteps):
         """host arrays -> Learner -> nsteps merges -> D2H of step log, vocabulary, segmentation, merge events"""
+        gc.collect()                                   # the previous repetition's garbage is not this one's cost
         barrier()
         t0 = time.perf_counter()
         L2 = mk()
@@ -513,6 +515,7 @@ def main():
         row = min(rows, key=lambda r: abs(r[0] + r[1] - med))
         return {"value": nsteps / med, "unit": "merge_iters/s", "h2d_bytes_per_step": row[2] / nsteps, "d2h_bytes_per_step": row[3] / nsteps,
                 "seconds": med, "setup_s": row[0], "steps_s": row[1], "reps": reps, "values_all_reps": [nsteps / t for t in tot],
+                "setup_steps_s_by_rep": [[round(r[0], 5), round(r[1], 5)] for r in rows],
                 "spread": (tot[-1] - tot[0]) / med,
                 "note": "Learner(host arrays): H2D of 72 B/residue, K3 thresholds + binning, residue tokens (setup_s); K merges, D2H of the "
                         "step log, vocabulary entries formatted on the host, D2H of segmentation + merge events (steps_s); median repetition"}
