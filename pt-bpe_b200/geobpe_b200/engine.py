@@ -1970,10 +1970,7 @@ class Learner:
         if self.comm is not None:
             # the reference's set saw, step by step, the operations of every backbone in order: shards are contiguous in rank
             # order, so the whole history is the rank-order concatenation re-grouped by step (stable sort on the step index)
-            parts = self.comm.all_gather_object((seg, is_add, bi + self.bb_base, index))
-            seg, is_add, bi, index = (np.concatenate([pt[c] for pt in parts]) for c in range(4))
-            o = np.argsort(seg, kind="stable")
-            seg, is_add, bi, index = seg[o], is_add[o], bi[o], index[o]
+            seg, is_add, bi, index = merge_shard_histories(self.comm.all_gather_object((seg, is_add, bi + self.bb_base, index)))
         return replay_set_order(seg, is_add, list(zip(bi.tolist(), index.tolist())))
 
     def m_key_string(self, key):
@@ -2276,6 +2273,15 @@ class Learner:
             self.step_h()
             return False
         return self.step_m()
+
+
+def merge_shard_histories(parts):
+    """per-rank (step, is_add, global backbone, bond index) histories of one key, each in its rank's own order -> the order a single
+    process would have logged them in: inside a step the operations follow the backbones, and shards are contiguous in rank order,
+    so the ranks' lists are concatenated and stably re-grouped by step"""
+    seg, is_add, bi, index = (np.concatenate([np.asarray(pt[c]) for pt in parts]) for c in range(4))
+    o = np.argsort(seg, kind="stable")
+    return seg[o], is_add[o], bi[o], index[o]
 
 
 def replay_set_order(seg, is_add, items):
